@@ -1,0 +1,24 @@
+"""CPU oracle for the Ape-X prioritized-replay / learner data path.
+
+TEST INFRASTRUCTURE ONLY.  Nothing under ``oracle/`` is part of the product:
+only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline /
+``--impl reference`` legs may import it, and there only as the checker or as
+the timed CPU baseline.  The product path (``ape-x-dqn_b200/``) never imports
+this package and fails loudly when the CUDA library is missing.
+
+Parity status ("pinned" vs "unpinned"), per function:
+
+* n-step assembly (``nstep_oracle.LiteralExperienceBuffer``), initial priority
+  (``nstep_oracle.initial_priority``) and the proportional sampling law
+  (``replay_oracle.reference_law_sample``) are PINNED against outputs of the
+  reference itself, generated in the build container by
+  ``tests/golden/make_golden.py`` (imports /root/reference, writes
+  ``tests/golden/*.json|npz``).
+* The learner arithmetic (``td_oracle``) follows learner.py:43-52, which raises
+  ``TypeError`` on this container's torch/numpy and therefore
+  cannot be executed: that part is a restatement with PARITY UNPINNED by the
+  reference (it is cross-checked against an independent torch fp64 evaluation).
+* The reference ships no tests, so there are no upstream golden vectors.
+"""
+
+from . import replay_oracle, td_oracle, nstep_oracle  # noqa: F401

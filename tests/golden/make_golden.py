@@ -1,0 +1,137 @@
+#!/usr/bin/env python
+"""Generate the golden vectors under tests/golden/ by EXECUTING the reference.
+
+Run in the build container only (it imports /root/reference, which does not
+exist on the GPU box):   python tests/golden/make_golden.py
+
+The reference ships no tests or fixtures, so these files are the
+only pinned outputs: every value below is produced by the unmodified reference
+classes (replay.ReplayMemory, actor.ExperienceBuffer, Actor.compute_priorities)
+or by the numpy routine the reference calls (np.random.choice, replay.py:52).
+"""
+import json
+import os
+import sys
+import types
+
+import numpy as np
+
+REF = "/root/reference"
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.dont_write_bytecode = True
+sys.path.insert(0, REF)
+sys.modules.setdefault("gym", types.ModuleType("gym"))      # env.py:1 imports gym; never called here
+if not hasattr(np, "int"):
+    np.int = int                                            # actor.py:133
+
+import replay as ref_replay          # noqa: E402
+import actor as ref_actor            # noqa: E402
+
+
+def nstep_cases():
+    cases = []
+    specs = [
+        dict(n=3, actor_id=1, steps=9, done_at=None),
+        dict(n=3, actor_id=7, steps=1, done_at=0),
+        dict(n=1, actor_id=0, steps=6, done_at=None),
+        dict(n=5, actor_id=12, steps=20, done_at=13),
+        dict(n=3, actor_id=3, steps=14, done_at=4),
+        dict(n=2, actor_id=5, steps=11, done_at=10),
+    ]
+    for sp in specs:
+        buf = ref_actor.ExperienceBuffer(sp["n"], sp["actor_id"])
+        feed = []
+        for t in range(sp["steps"]):
+            r = float(10 ** (t % 4)) if sp["n"] == 3 and sp["actor_id"] == 1 else float((t * 7) % 5 - 2) * 0.5
+            q = (np.arange(4, dtype=np.float32) + t).tolist()
+            feed.append(dict(S=t, A=t % 4, R=r, Gamma=0.99, q=q, done=(sp["done_at"] == t)))
+            buf.add(ref_actor.Transition(t, t % 4, r, 0.99, np.array(q, np.float32)))
+            if sp["done_at"] == t:     # actor.py:172-174: flush with (next obs, reward 0, stale q)
+                buf.construct_nstep_transition(ref_actor.Transition(1000 + t, t % 4, 0, 0.99, np.array(q, np.float32)))
+        out = [dict(S_t=x.S_t, A_t=x.A_t, R=float(x.R_ttpB), Gamma=float(x.Gamma_ttpB),
+                    qS_t=np.asarray(x.qS_t).tolist(), S_tpn=x.S_tpn, qS_tpn=np.asarray(x.qS_tpn).tolist(),
+                    key=x.key) for x in buf.local_nstep_buffer]
+        cases.append(dict(spec=sp, feed=feed, emitted=out))
+    return cases
+
+
+def priority_cases():
+    rng = np.random.RandomState(7)
+    NT = ref_actor.N_Step_Transition
+    actor_cls = ref_actor.Actor
+    stub = types.SimpleNamespace()                       # compute_priorities uses no instance state
+    cases = []
+    for case in range(4):
+        m = [2, 5, 5, 17][case]
+        recs = []
+        for i in range(m):
+            recs.append(NT(None, int(rng.randint(4)), float(rng.randn()), float(0.99 ** 3 if rng.rand() > .2 else 0.0),
+                           rng.randn(4).astype(np.float32), None, rng.randn(4).astype(np.float32), "k%d" % i))
+        if case == 0:   # SURVEY §8(c) vector (3)
+            recs = [NT(None, 1, 1.0, .9801, np.array([1, 2, 3, 4], np.float32), None, np.array([0, 5, 1, 1], np.float32), "10"),
+                    NT(None, 2, 0.0, .9801, np.array([1, 2, 3, 4], np.float32), None, np.array([0, 1, 1, 1], np.float32), "11")]
+        literal = actor_cls.compute_priorities(stub, recs)            # every key -> last |TD| (Q12)
+        per_row = [float(list(actor_cls.compute_priorities(stub, [r]).values())[0]) for r in recs]
+        cases.append(dict(A=[r.A_t for r in recs], R=[r.R_ttpB for r in recs], Gamma=[r.Gamma_ttpB for r in recs],
+                          q_t=[r.qS_t.tolist() for r in recs], q_tpn=[r.qS_tpn.tolist() for r in recs],
+                          keys=[r.key for r in recs],
+                          literal={k: float(v) for k, v in literal.items()}, per_row_abs_td=per_row))
+    return cases
+
+
+def replay_cases():
+    NT = ref_replay.N_Step_Transition
+    out = {}
+    # (4) literal probabilities are uniform; (6) trimmed keys stay sampleable.
+    mem = ref_replay.ReplayMemory(5, {"priority_exponent": 0.6})
+    mem.set_priorities({"a": np.float64(1), "b": np.float64(2), "c": np.float64(4)})
+    out["literal_probs_1_2_4"] = [float(mem.sample_probabilities[k]) for k in "abc"]
+    mem = ref_replay.ReplayMemory(5, {"priority_exponent": 0.6})
+    recs = [NT(i, i % 4, float(i), 0.97, None, i + 3, None, "k%d" % i) for i in range(8)]
+    mem.add({r.key: np.float64(1 + r.S_t) for r in recs}, recs)
+    out["size_after_add8"] = mem.size()
+    mem.remove_to_fit()
+    out["size_after_trim"] = mem.size()
+    out["priorities_after_trim"] = len(mem.priorities)
+    np.random.seed(11)
+    out["sample6_after_trim_keys"] = [r.key for r in mem.sample(6)]
+    # choice mechanism through the real ReplayMemory.sample: same stream, same picks
+    mem = ref_replay.ReplayMemory(100, {"priority_exponent": 0.6})
+    recs = [NT(i, 0, 0.0, 0.97, None, i, None, "k%d" % i) for i in range(37)]
+    mem.add({r.key: np.float64(1 + (i % 5)) for i, r in enumerate(recs)}, recs)
+    np.random.seed(5)
+    picked = [int(r.key[1:]) for r in mem.sample(64)]
+    np.random.seed(5)
+    u = np.random.random_sample(64)
+    out["literal_sample"] = dict(n=37, picked=picked, u=u.tolist(),
+                                 probs=[float(v) for v in mem.sample_probabilities.values()])
+    return out
+
+
+def choice_law():
+    """np.random.choice(K, p=P) for intended P = p^alpha / sum, with the uniform stream it consumed."""
+    rs = np.random.RandomState(123)
+    K, B, alpha = 5000, 4096, 0.6
+    pri = np.abs(rs.randn(K)) + 1e-3
+    P = pri ** alpha
+    P /= P.sum()
+    np.random.seed(99)
+    picks = np.array([np.random.choice(K, p=P) for _ in range(B)], np.int64)   # replay.py:52 call shape
+    np.random.seed(99)
+    u = np.random.random_sample(B)
+    np.savez_compressed(os.path.join(HERE, "choice_law.npz"), priorities=pri, alpha=alpha, u=u, picks=picks)
+
+
+def main():
+    with open(os.path.join(HERE, "nstep_literal.json"), "w") as f:
+        json.dump(nstep_cases(), f, indent=1)
+    with open(os.path.join(HERE, "initial_priority.json"), "w") as f:
+        json.dump(priority_cases(), f, indent=1)
+    with open(os.path.join(HERE, "replay_literal.json"), "w") as f:
+        json.dump(replay_cases(), f, indent=1)
+    choice_law()
+    print("golden vectors written to", HERE)
+
+
+if __name__ == "__main__":
+    main()
