@@ -1,0 +1,15 @@
+"""apex_b200 — B200-native prioritized replay + learner data path for Ape-X DQN.
+
+Host-side mirror of the reference's replay.py / learner.py / actor.py classes
+over the C-ABI CUDA library libapexb200.so (include/apexb200.h).  The directory
+is called ``ape-x-dqn_b200``; import it as ``apex_b200`` through the loader at
+the repository root (``import apex_b200``).
+"""
+from . import _C                                              # noqa: F401
+from .replay import ReplayMemory, N_Step_Transition, Batch, KeyIndex, stream_offsets   # noqa: F401
+from .actor import ExperienceBuffer, Actor, Transition        # noqa: F401
+from .learner import Learner, td_loss                         # noqa: F401
+from . import ops                                             # noqa: F401
+
+__all__ = ["ReplayMemory", "Learner", "Actor", "ExperienceBuffer", "N_Step_Transition", "Transition", "Batch",
+           "KeyIndex", "stream_offsets", "td_loss", "ops"]

@@ -1,0 +1,299 @@
+// Replay shard lifetime, ring insert (K6) and raw buffer access.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "common.cuh"
+
+namespace apexb200 {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char *what) {
+    set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+    return e == cudaErrorMemoryAllocation ? APEXB200_ENOMEM : APEXB200_ECUDA;
+}
+
+// ---------------------------------------------------------------------------
+// K6a: stream the new frames into their ring slots (16-byte vectors, coalesced;
+// source is contiguous, destination is contiguous up to the ring wrap).
+__global__ void __launch_bounds__(256)
+insert_frames_kernel(uint4 *__restrict__ ring_frames, const uint4 *__restrict__ src,
+                     long long total_vecs, int vecs_per_record, long long lane_base,
+                     long long head, long long lane_cap) {
+    long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < total_vecs; v += stride) {
+        long long j = v / vecs_per_record;
+        int within = (int)(v - j * vecs_per_record);
+        long long slot = lane_base + (head + j) % lane_cap;
+        uint4 x = __ldcs(src + v);                               // staging data is read once
+        ring_frames[slot * vecs_per_record + within] = x;
+    }
+}
+
+// K6b: metadata, frame-index rows, initial priority (actor.py:138-140), leaf write
+// and ancestor update for the `count` new records, plus invalidation of the
+// `lookback` records behind the new head.
+__global__ void __launch_bounds__(128)
+insert_meta_kernel(RingView rv, TreeView tv, int lane, long long head, int count,
+                   const int32_t *__restrict__ rel, const int32_t *__restrict__ A,
+                   const float *__restrict__ R, const float *__restrict__ G,
+                   const float *__restrict__ prio, const float *__restrict__ q_t,
+                   const float *__restrict__ q_tpn, int32_t *status) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= count + rv.lookback) return;
+    long long p = (head + j) % rv.lane_cap;
+    long long s = (long long)lane * rv.lane_cap + p;
+    unsigned long long new_leaf = 0ull;
+    if (j < count) {
+        const int twoC = 2 * rv.C;
+        const long long lane_frames = rv.lane_cap * rv.fpr;
+        const long long lane_frame_base = (long long)lane * lane_frames;
+        const long long last = p * rv.fpr + rv.fpr - 1;
+        const long long reach = (long long)rv.lookback * rv.fpr + rv.fpr - 1;
+        for (int k = 0; k < twoC; ++k) {
+            long long r = rel[(long long)j * twoC + k];
+            if (r > 0 || -r > reach) { atomicOr(status, APEXB200_ST_BAD_INDEX); r = 0; }
+            long long f = (last + r) % lane_frames;
+            if (f < 0) f += lane_frames;
+            rv.fidx[s * twoC + k] = (int32_t)(lane_frame_base + f);
+        }
+        int a = A[j];
+        float r = R[j], g = G[j];
+        rv.A[s] = a; rv.R[s] = r; rv.G[s] = g;
+        float p0;
+        if (prio != nullptr) {
+            p0 = fabsf(prio[j]);
+        } else {
+            const float *qa = q_t + (long long)j * rv.nA, *qb = q_tpn + (long long)j * rv.nA;
+            float mx = qb[0];
+            for (int k = 1; k < rv.nA; ++k) mx = fmaxf(mx, qb[k]);
+            if (a < 0 || a >= rv.nA) { atomicOr(status, APEXB200_ST_BAD_ACTION); a = 0; }
+            p0 = fabsf(__fadd_rn(__fadd_rn(r, __fmul_rn(g, mx)), -qa[a]));
+        }
+        if (rv.q_t != nullptr && q_t != nullptr) {
+            for (int k = 0; k < rv.nA; ++k) {
+                rv.q_t[s * rv.nA + k] = q_t[(long long)j * rv.nA + k];
+                rv.q_tpn[s * rv.nA + k] = q_tpn[(long long)j * rv.nA + k];
+            }
+        }
+        new_leaf = leaf_from_prio(prio_pow(p0, rv.alpha, 0.0f));
+    }
+    unsigned long long old = tv.lvl[0][s];
+    tv.lvl[0][s] = new_leaf;
+    unsigned long long d = new_leaf - old;
+    if (d != 0ull) propagate_delta(tv, s, d);
+}
+
+}  // namespace apexb200
+
+using namespace apexb200;
+
+extern "C" {
+
+int apexb200_version(void) { return APEXB200_VERSION; }
+
+const char *apexb200_strerror(int code) {
+    switch (code) {
+        case APEXB200_OK: return "ok";
+        case APEXB200_EINVAL: return "invalid argument";
+        case APEXB200_ECUDA: return "CUDA runtime error";
+        case APEXB200_ENOMEM: return "out of device memory";
+        case APEXB200_ERANGE: return "size beyond supported limit";
+        default: return "unknown error";
+    }
+}
+
+const char *apexb200_last_error(void) { return g_err; }
+
+int apexb200_replay_create(apexb200_replay_t *out, const apexb200_replay_config *cfg) {
+    APEX_REQUIRE(out && cfg, APEXB200_EINVAL, "replay_create: null argument");
+    *out = nullptr;
+    APEX_REQUIRE(cfg->capacity > 0 && cfg->lanes > 0 && cfg->capacity % cfg->lanes == 0, APEXB200_EINVAL,
+                 "replay_create: capacity %lld must be a positive multiple of lanes %d",
+                 (long long)cfg->capacity, cfg->lanes);
+    APEX_REQUIRE(cfg->capacity <= APEXB200_MAX_CAPACITY, APEXB200_ERANGE,
+                 "replay_create: capacity %lld > %lld records per shard", (long long)cfg->capacity,
+                 (long long)APEXB200_MAX_CAPACITY);
+    APEX_REQUIRE(cfg->frames_per_record >= 1 && cfg->frames_per_state >= 1 && cfg->lookback >= 0,
+                 APEXB200_EINVAL, "replay_create: bad frames_per_record/frames_per_state/lookback");
+    APEX_REQUIRE(cfg->frame_bytes > 0 && cfg->frame_bytes % 16 == 0, APEXB200_EINVAL,
+                 "replay_create: frame_bytes %d must be a positive multiple of 16", cfg->frame_bytes);
+    APEX_REQUIRE(cfg->num_actions >= 0 && cfg->num_actions <= APEXB200_MAX_ACTIONS, APEXB200_ERANGE,
+                 "replay_create: num_actions %d outside [0, %d]", cfg->num_actions, APEXB200_MAX_ACTIONS);
+    APEX_REQUIRE(cfg->alpha >= 0.0f, APEXB200_EINVAL, "replay_create: alpha must be >= 0");
+    const long long lane_cap = cfg->capacity / cfg->lanes;
+    APEX_REQUIRE(cfg->lookback < lane_cap, APEXB200_EINVAL, "replay_create: lookback %d >= lane capacity %lld",
+                 cfg->lookback, lane_cap);
+    APEX_REQUIRE((long long)cfg->capacity * cfg->frames_per_record < (1ll << 31), APEXB200_ERANGE,
+                 "replay_create: frame slot count overflows int32");
+    APEX_CUDA(cudaSetDevice(cfg->device));
+
+    apexb200_replay *h = new (std::nothrow) apexb200_replay();
+    APEX_REQUIRE(h, APEXB200_ENOMEM, "replay_create: host allocation failed");
+    h->cfg = *cfg;
+    h->lane_count.assign(cfg->lanes, 0);
+    const long long N = cfg->capacity;
+    const int C = cfg->frames_per_state, nA = cfg->num_actions;
+
+    // tree geometry
+    TreeView &tv = h->tree;
+    memset(&tv, 0, sizeof(tv));
+    long long sz = N, padded_total = 0;
+    int nl = 0;
+    long long offs[kMaxLevels];
+    for (;;) {
+        tv.size[nl] = sz;
+        offs[nl] = padded_total;
+        padded_total += (sz + kFanout - 1) / kFanout * kFanout;
+        ++nl;
+        if (sz <= kFanout) break;
+        sz = (sz + kFanout - 1) / kFanout;
+    }
+    tv.n_levels = nl;
+
+    int rc = APEXB200_OK;
+    auto alloc = [&](void **p, size_t bytes, bool zero) -> bool {
+        cudaError_t e = cudaMalloc(p, bytes);
+        if (e != cudaSuccess) { rc = cuda_fail(e, "cudaMalloc"); return false; }
+        h->device_bytes += (int64_t)bytes;
+        if (zero) {
+            e = cudaMemset(*p, 0, bytes);
+            if (e != cudaSuccess) { rc = cuda_fail(e, "cudaMemset"); return false; }
+        }
+        return true;
+    };
+    RingView &rv = h->ring;
+    memset(&rv, 0, sizeof(rv));
+    rv.N = N; rv.lane_cap = lane_cap; rv.lanes = cfg->lanes; rv.fpr = cfg->frames_per_record;
+    rv.lookback = cfg->lookback; rv.C = C; rv.F = cfg->frame_bytes; rv.nA = nA; rv.alpha = cfg->alpha;
+    bool ok = alloc(&h->tree_block, (size_t)padded_total * 8, true) &&
+              alloc((void **)&h->stamp, (size_t)N * 4, true) &&
+              alloc((void **)&h->status, 256, true) &&
+              alloc((void **)&rv.frames, (size_t)N * rv.fpr * rv.F, false) &&
+              alloc((void **)&rv.fidx, (size_t)N * 2 * C * 4, true) &&
+              alloc((void **)&rv.A, (size_t)N * 4, true) &&
+              alloc((void **)&rv.R, (size_t)N * 4, true) &&
+              alloc((void **)&rv.G, (size_t)N * 4, true);
+    if (ok && nA > 0)
+        ok = alloc((void **)&rv.q_t, (size_t)N * nA * 4, true) && alloc((void **)&rv.q_tpn, (size_t)N * nA * 4, true);
+    if (!ok) { apexb200_replay_destroy(h); return rc; }
+    for (int l = 0; l < nl; ++l) tv.lvl[l] = (unsigned long long *)h->tree_block + offs[l];
+    *out = h;
+    return APEXB200_OK;
+}
+
+int apexb200_replay_destroy(apexb200_replay_t h) {
+    if (!h) return APEXB200_OK;
+    cudaSetDevice(h->cfg.device);
+    void *ptrs[] = {h->tree_block, h->stamp, h->status, h->ring.frames, h->ring.fidx, h->ring.A,
+                    h->ring.R, h->ring.G, h->ring.q_t, h->ring.q_tpn};
+    for (void *p : ptrs) if (p) cudaFree(p);
+    delete h;
+    return APEXB200_OK;
+}
+
+int apexb200_replay_size(apexb200_replay_t h, int64_t *size_host) {
+    APEX_REQUIRE(h && size_host, APEXB200_EINVAL, "replay_size: null argument");
+    long long s = 0;
+    for (long long c : h->lane_count) s += c < h->ring.lane_cap ? c : h->ring.lane_cap;
+    *size_host = s;
+    return APEXB200_OK;
+}
+
+int apexb200_replay_device_bytes(apexb200_replay_t h, int64_t *bytes_host) {
+    APEX_REQUIRE(h && bytes_host, APEXB200_EINVAL, "replay_device_bytes: null argument");
+    *bytes_host = h->device_bytes;
+    return APEXB200_OK;
+}
+
+int apexb200_replay_status(apexb200_replay_t h, int32_t *status_host, void *stream) {
+    APEX_REQUIRE(h && status_host, APEXB200_EINVAL, "replay_status: null argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    APEX_CUDA(cudaMemcpyAsync(status_host, h->status, 4, cudaMemcpyDeviceToHost, st));
+    APEX_CUDA(cudaMemsetAsync(h->status, 0, 4, st));
+    APEX_CUDA(cudaStreamSynchronize(st));
+    return APEXB200_OK;
+}
+
+int apexb200_replay_insert(apexb200_replay_t h, int32_t lane, int32_t count, const uint8_t *frames,
+                           const int32_t *rel, const int32_t *A, const float *R, const float *Gamma,
+                           const float *prio, const float *q_t, const float *q_tpn,
+                           int64_t *first_slot_host, void *stream) {
+    APEX_REQUIRE(h, APEXB200_EINVAL, "replay_insert: null handle");
+    const RingView &rv = h->ring;
+    APEX_REQUIRE(lane >= 0 && lane < rv.lanes, APEXB200_EINVAL, "replay_insert: lane %d outside [0,%d)", lane, rv.lanes);
+    APEX_REQUIRE(count >= 0, APEXB200_EINVAL, "replay_insert: negative count");
+    const long long head = h->lane_count[lane] % rv.lane_cap;
+    if (first_slot_host) *first_slot_host = (long long)lane * rv.lane_cap + head;
+    if (count == 0) return APEXB200_OK;
+    APEX_REQUIRE((long long)count + rv.lookback <= rv.lane_cap, APEXB200_ERANGE,
+                 "replay_insert: count %d + lookback %d exceeds lane capacity %lld", count, rv.lookback, rv.lane_cap);
+    APEX_REQUIRE(frames && rel && A && R && Gamma, APEXB200_EINVAL, "replay_insert: null input");
+    APEX_REQUIRE(prio || (q_t && q_tpn && rv.nA > 0), APEXB200_EINVAL,
+                 "replay_insert: need prio, or q_t/q_tpn on a handle created with num_actions > 0");
+    APEX_REQUIRE(((uintptr_t)frames & 15) == 0, APEXB200_EINVAL, "replay_insert: frames must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int vpr = rv.fpr * rv.F / 16;
+    const long long total_vecs = (long long)count * vpr;
+    long long blocks = (total_vecs + 255) / 256;
+    const long long max_blocks = (long long)kNumSMs * 16;
+    if (blocks > max_blocks) blocks = max_blocks;
+    insert_frames_kernel<<<(unsigned)blocks, 256, 0, st>>>((uint4 *)rv.frames, (const uint4 *)frames, total_vecs,
+                                                           vpr, (long long)lane * rv.lane_cap, head, rv.lane_cap);
+    int rc = launch_check("insert_frames_kernel");
+    if (rc) return rc;
+    const int nmeta = count + rv.lookback;
+    insert_meta_kernel<<<(nmeta + 127) / 128, 128, 0, st>>>(rv, h->tree, lane, head, count, rel, A, R, Gamma, prio,
+                                                            q_t, q_tpn, h->status);
+    rc = launch_check("insert_meta_kernel");
+    if (rc) return rc;
+    h->lane_count[lane] += count;
+    return APEXB200_OK;
+}
+
+int apexb200_replay_buffer(apexb200_replay_t h, int32_t which, void **ptr_host, int64_t *bytes_host) {
+    APEX_REQUIRE(h && ptr_host && bytes_host, APEXB200_EINVAL, "replay_buffer: null argument");
+    const RingView &rv = h->ring;
+    void *p = nullptr;
+    int64_t b = 0;
+    switch (which) {
+        case APEXB200_BUF_FRAMES: p = rv.frames; b = rv.N * rv.fpr * rv.F; break;
+        case APEXB200_BUF_FIDX: p = rv.fidx; b = rv.N * 2 * rv.C * 4; break;
+        case APEXB200_BUF_ACTION: p = rv.A; b = rv.N * 4; break;
+        case APEXB200_BUF_REWARD: p = rv.R; b = rv.N * 4; break;
+        case APEXB200_BUF_GAMMA: p = rv.G; b = rv.N * 4; break;
+        case APEXB200_BUF_QT: p = rv.q_t; b = rv.q_t ? rv.N * rv.nA * 4 : 0; break;
+        case APEXB200_BUF_QTPN: p = rv.q_tpn; b = rv.q_tpn ? rv.N * rv.nA * 4 : 0; break;
+        case APEXB200_BUF_LEAVES: p = h->tree.lvl[0]; b = rv.N * 8; break;
+        default: set_error("replay_buffer: unknown buffer id %d", which); return APEXB200_EINVAL;
+    }
+    *ptr_host = p;
+    *bytes_host = b;
+    return APEXB200_OK;
+}
+
+int apexb200_replay_get_heads(apexb200_replay_t h, int64_t *lane_count_host) {
+    APEX_REQUIRE(h && lane_count_host, APEXB200_EINVAL, "replay_get_heads: null argument");
+    for (int i = 0; i < h->ring.lanes; ++i) lane_count_host[i] = h->lane_count[i];
+    return APEXB200_OK;
+}
+
+int apexb200_replay_set_heads(apexb200_replay_t h, const int64_t *lane_count_host) {
+    APEX_REQUIRE(h && lane_count_host, APEXB200_EINVAL, "replay_set_heads: null argument");
+    for (int i = 0; i < h->ring.lanes; ++i) {
+        APEX_REQUIRE(lane_count_host[i] >= 0, APEXB200_EINVAL, "replay_set_heads: negative head");
+        h->lane_count[i] = lane_count_host[i];
+    }
+    return APEXB200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,280 @@
+// K5: fused n-step double-DQN target / TD error / |delta|^alpha priority / loss
+// (+ backward, + in-place priority write-back), K7 n-step returns, and the actor's
+// initial priority.  All fp32, one thread per record; these kernels move a few
+// hundred bytes per record and are launch/latency bound, not bandwidth bound.
+#include "common.cuh"
+
+namespace apexb200 {
+
+int run_tree_update(apexb200_replay *h, const int32_t *idx, const void *values, int mode, int count,
+                    const int32_t *count_dev, float eps, cudaStream_t st);
+int run_tree_apply(apexb200_replay *h, const int32_t *idx, const void *values, int mode, int count,
+                   cudaStream_t st);
+
+struct TdArgs {
+    const float *q_on_t, *q_on_tpn, *q_tg_tpn;
+    const int32_t *A;
+    const float *R, *G;
+    float *delta, *prio, *loss, *loss_mean;
+    int B, nA, loss_kind;
+    float alpha, eps, kappa;
+};
+
+// learner.py:43-50 for one record.  Explicit _rn intrinsics keep the compiler from
+// contracting R + Gamma*q into an FMA, so delta/loss equal a plain fp32 evaluation.
+__device__ __forceinline__ float td_one(const TdArgs &a, int b, float *loss_out) {
+    const float *row_t = a.q_on_t + (long long)b * a.nA;
+    const float *row_n = a.q_on_tpn + (long long)b * a.nA;
+    const float *row_g = a.q_tg_tpn + (long long)b * a.nA;
+    int arg = 0;
+    float best = row_n[0];
+    for (int k = 1; k < a.nA; ++k) {
+        float q = row_n[k];
+        if (q > best) { best = q; arg = k; }                 // first maximum on ties (argmax, learner.py:45)
+    }
+    int act = a.A[b];
+    act = act < 0 ? 0 : (act >= a.nA ? a.nA - 1 : act);
+    const float target = __fadd_rn(a.R[b], __fmul_rn(a.G[b], row_g[arg]));     // learner.py:44
+    const float d = __fsub_rn(target, row_t[act]);                              // learner.py:47
+    const float ad = fabsf(d);
+    float l;
+    if (a.loss_kind == APEXB200_LOSS_HALF_SQ) l = __fmul_rn(__fmul_rn(0.5f, d), d);   // learner.py:48
+    else l = ad <= a.kappa ? __fmul_rn(__fmul_rn(0.5f, d), d) : __fmul_rn(a.kappa, __fsub_rn(ad, 0.5f * a.kappa));
+    a.delta[b] = d;
+    a.prio[b] = prio_pow(ad, a.alpha, a.eps);                                   // learner.py:50 + replay.py:24
+    a.loss[b] = l;
+    *loss_out = l;
+    return d;
+}
+
+// Fixed-shape block sum: xor-shuffle tree inside each warp, then warp partials
+// added in warp order by thread 0 -> the same association for a given blockDim.
+__device__ __forceinline__ float block_sum_fixed(float v, float *warp_part) {
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) warp_part[wid] = v;
+    __syncthreads();
+    float s = 0.0f;
+    if (threadIdx.x == 0) {
+        const int nw = (blockDim.x + 31) >> 5;
+        for (int k = 0; k < nw; ++k) s += warp_part[k];
+    }
+    return s;                                               // valid in thread 0
+}
+
+// ---- B <= 1024: one CTA, no scratch; optionally also the priority write-back.
+__global__ void __launch_bounds__(1024)
+td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t *__restrict__ stamp,
+                int32_t *status) {
+    __shared__ float warp_part[32];
+    const int b = threadIdx.x;
+    float l = 0.0f;
+    long long i = -1;
+    if (b < a.B) {
+        td_one(a, b, &l);
+        if (idx != nullptr) {
+            i = idx[b];
+            if (i < 0 || i >= tv.size[0]) { atomicOr(status, APEXB200_ST_BAD_INDEX); i = -1; }
+            else atomicMax(stamp + i, (uint32_t)b + 1u);
+        }
+    }
+    float s = block_sum_fixed(l, warp_part);                // contains the __syncthreads that orders the stamps
+    if (threadIdx.x == 0) *a.loss_mean = s / (float)a.B;
+    if (i < 0) return;
+    if (__ldcg(stamp + i) != (uint32_t)b + 1u) return;      // a later duplicate wins (replay.py:40)
+    stamp[i] = 0u;
+    unsigned long long nl = leaf_from_prio(a.prio[b]);
+    unsigned long long old = tv.lvl[0][i];
+    tv.lvl[0][i] = nl;
+    unsigned long long d = nl - old;
+    if (d != 0ull) propagate_delta(tv, i, d);
+}
+
+// ---- any B: 256 records per CTA; per-CTA loss partials go to scratch and the last
+// CTA to finish (ticket counter in scratch) adds them in CTA order.
+// scratch layout: [0] u32 ticket (zeroed by the host before launch), [64..] float partials.
+__global__ void __launch_bounds__(256)
+td_multi_kernel(TdArgs a, const int32_t *__restrict__ idx, uint32_t *__restrict__ stamp, long long N,
+                int32_t *status, unsigned int *__restrict__ ticket, float *__restrict__ partials) {
+    __shared__ float warp_part[8];
+    __shared__ bool is_last;
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    float l = 0.0f;
+    if (b < a.B) {
+        td_one(a, b, &l);
+        if (idx != nullptr) {
+            long long i = idx[b];
+            if (i < 0 || i >= N) atomicOr(status, APEXB200_ST_BAD_INDEX);
+            else atomicMax(stamp + i, (uint32_t)b + 1u);
+        }
+    }
+    float s = block_sum_fixed(l, warp_part);
+    if (threadIdx.x == 0) {
+        partials[blockIdx.x] = s;
+        __threadfence();
+        unsigned int t = atomicAdd(ticket, 1u);
+        is_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (is_last && threadIdx.x == 0) {
+        __threadfence();
+        float tot = 0.0f;
+        for (unsigned k = 0; k < gridDim.x; ++k) tot += __ldcg(partials + k);
+        *a.loss_mean = tot / (float)a.B;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+td_bwd_kernel(const float *__restrict__ delta, const int32_t *__restrict__ A, const float *__restrict__ grad_out,
+              int B, int nA, int loss_kind, float kappa, float *__restrict__ grad_q) {
+    long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (long long)B * nA) return;
+    int b = (int)(e / nA), k = (int)(e - (long long)b * nA);
+    float g = 0.0f;
+    if (k == A[b]) {
+        float d = delta[b];
+        if (loss_kind == APEXB200_LOSS_HUBER) d = fminf(fmaxf(d, -kappa), kappa);
+        g = -d * (*grad_out) / (float)B;                    // d(mean loss)/dQ(S_t)[b, A_b]
+    }
+    grad_q[e] = g;
+}
+
+// ---- K7
+__global__ void __launch_bounds__(256)
+nstep_kernel(const float *__restrict__ rewards, const uint8_t *__restrict__ dones, int E, int T, int n, float gamma,
+             float *__restrict__ R, float *__restrict__ G, int32_t *__restrict__ span) {
+    long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (long long)E * T) return;
+    const int t = (int)(e % T);
+    float acc = 0.0f, disc = 1.0f;
+    int m = 0;
+    bool term = false;
+    for (int k = 0; k < n && t + k < T; ++k) {
+        acc = __fadd_rn(acc, __fmul_rn(disc, rewards[e + k]));
+        disc = __fmul_rn(disc, gamma);
+        ++m;
+        if (dones[e + k]) { term = true; break; }
+    }
+    const bool valid = term || m == n;
+    R[e] = valid ? acc : 0.0f;
+    G[e] = valid ? (term ? 0.0f : disc) : 0.0f;
+    span[e] = valid ? m : 0;
+}
+
+__global__ void __launch_bounds__(256)
+initial_priority_kernel(const float *__restrict__ q_t, const float *__restrict__ q_tpn, const int32_t *__restrict__ A,
+                        const float *__restrict__ R, const float *__restrict__ G, int count, int nA,
+                        float *__restrict__ abs_td) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= count) return;
+    const float *qa = q_t + (long long)j * nA, *qb = q_tpn + (long long)j * nA;
+    float mx = qb[0];
+    for (int k = 1; k < nA; ++k) mx = fmaxf(mx, qb[k]);
+    int a = A[j];
+    a = a < 0 ? 0 : (a >= nA ? nA - 1 : a);
+    abs_td[j] = fabsf(__fsub_rn(__fadd_rn(R[j], __fmul_rn(G[j], mx)), qa[a]));   // actor.py:138-140
+}
+
+static int td_check(const float *q1, const float *q2, const float *q3, const int32_t *A, const float *R,
+                    const float *G, int32_t B, int32_t nA, float *d, float *p, float *l, float *lm) {
+    APEX_REQUIRE(q1 && q2 && q3 && A && R && G && d && p && l && lm, APEXB200_EINVAL, "td_fwd: null argument");
+    APEX_REQUIRE(B > 0, APEXB200_EINVAL, "td_fwd: B must be positive");
+    APEX_REQUIRE(nA >= 1 && nA <= APEXB200_MAX_ACTIONS, APEXB200_ERANGE, "td_fwd: num_actions %d outside [1,%d]", nA,
+                 APEXB200_MAX_ACTIONS);
+    return APEXB200_OK;
+}
+
+static int64_t td_ws_bytes(int B) {
+    int64_t blocks = (B + 255) / 256;
+    return 256 + (blocks * 4 + 255) / 256 * 256;
+}
+
+static int td_launch(apexb200_replay *h, const int32_t *idx, const TdArgs &a, void *workspace, int64_t ws_bytes,
+                     cudaStream_t st) {
+    TreeView tv_none{};
+    if (a.B <= 1024) {
+        td_small_kernel<<<1, ((a.B + 31) / 32) * 32, 0, st>>>(a, h ? h->tree : tv_none, idx, h ? h->stamp : nullptr,
+                                                             h ? h->status : nullptr);
+        return launch_check("td_small_kernel");
+    }
+    APEX_REQUIRE(workspace && ws_bytes >= td_ws_bytes(a.B), APEXB200_EINVAL,
+                 "td_fwd: B=%d needs %lld bytes of workspace (got %lld)", a.B, (long long)td_ws_bytes(a.B),
+                 (long long)ws_bytes);
+    APEX_REQUIRE(((uintptr_t)workspace & 255) == 0, APEXB200_EINVAL, "td_fwd: workspace must be 256-byte aligned");
+    APEX_CUDA(cudaMemsetAsync(workspace, 0, 256, st));
+    const int blocks = (a.B + 255) / 256;
+    td_multi_kernel<<<blocks, 256, 0, st>>>(a, idx, h ? h->stamp : nullptr, h ? h->ring.N : 0,
+                                            h ? h->status : nullptr, (unsigned int *)workspace,
+                                            (float *)((char *)workspace + 256));
+    int rc = launch_check("td_multi_kernel");
+    if (rc || !h) return rc;
+    return run_tree_apply(h, idx, a.prio, 2, a.B, st);            // stamps were taken inside td_multi_kernel
+}
+
+}  // namespace apexb200
+
+using namespace apexb200;
+
+extern "C" {
+
+int apexb200_td_workspace_bytes(int32_t B, int64_t *bytes_host) {
+    APEX_REQUIRE(bytes_host && B > 0, APEXB200_EINVAL, "td_workspace_bytes: bad argument");
+    *bytes_host = td_ws_bytes(B);
+    return APEXB200_OK;
+}
+
+int apexb200_td_fwd(const float *q_on_t, const float *q_on_tpn, const float *q_tg_tpn, const int32_t *A,
+                    const float *R, const float *Gamma, int32_t B, int32_t num_actions, float alpha, float eps,
+                    int32_t loss_kind, float kappa, float *delta, float *prio, float *loss, float *loss_mean,
+                    void *workspace, int64_t workspace_bytes, void *stream) {
+    int rc = td_check(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, B, num_actions, delta, prio, loss, loss_mean);
+    if (rc) return rc;
+    TdArgs a{q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, delta, prio, loss, loss_mean, B, num_actions, loss_kind,
+             alpha, eps, kappa};
+    return td_launch(nullptr, nullptr, a, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int apexb200_td_fwd_update(apexb200_replay_t h, const int32_t *idx, const float *q_on_t, const float *q_on_tpn,
+                           const float *q_tg_tpn, const int32_t *A, const float *R, const float *Gamma, int32_t B,
+                           int32_t num_actions, float eps, int32_t loss_kind, float kappa, float *delta,
+                           float *prio, float *loss, float *loss_mean, void *workspace, int64_t workspace_bytes,
+                           void *stream) {
+    APEX_REQUIRE(h && idx, APEXB200_EINVAL, "td_fwd_update: null handle/idx");
+    int rc = td_check(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, B, num_actions, delta, prio, loss, loss_mean);
+    if (rc) return rc;
+    TdArgs a{q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, delta, prio, loss, loss_mean, B, num_actions, loss_kind,
+             h->ring.alpha, eps, kappa};
+    return td_launch(h, idx, a, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int apexb200_td_bwd(const float *delta, const int32_t *A, const float *grad_loss_mean, int32_t B,
+                    int32_t num_actions, int32_t loss_kind, float kappa, float *grad_q, void *stream) {
+    APEX_REQUIRE(delta && A && grad_loss_mean && grad_q && B > 0 && num_actions >= 1, APEXB200_EINVAL,
+                 "td_bwd: bad argument");
+    long long n = (long long)B * num_actions;
+    td_bwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(delta, A, grad_loss_mean, B,
+                                                                                 num_actions, loss_kind, kappa, grad_q);
+    return launch_check("td_bwd_kernel");
+}
+
+int apexb200_nstep(const float *rewards, const uint8_t *dones, int32_t E, int32_t T, int32_t n, float gamma,
+                   float *R, float *Gamma, int32_t *span, void *stream) {
+    APEX_REQUIRE(rewards && dones && R && Gamma && span, APEXB200_EINVAL, "nstep: null argument");
+    APEX_REQUIRE(E > 0 && T > 0 && n >= 1, APEXB200_EINVAL, "nstep: bad E/T/n");
+    long long tot = (long long)E * T;
+    nstep_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, (cudaStream_t)stream>>>(rewards, dones, E, T, n, gamma, R,
+                                                                                  Gamma, span);
+    return launch_check("nstep_kernel");
+}
+
+int apexb200_initial_priority(const float *q_t, const float *q_tpn, const int32_t *A, const float *R,
+                              const float *Gamma, int32_t count, int32_t num_actions, float *abs_td, void *stream) {
+    APEX_REQUIRE(q_t && q_tpn && A && R && Gamma && abs_td, APEXB200_EINVAL, "initial_priority: null argument");
+    APEX_REQUIRE(count > 0 && num_actions >= 1, APEXB200_EINVAL, "initial_priority: bad count/num_actions");
+    initial_priority_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>(q_t, q_tpn, A, R, Gamma, count,
+                                                                                   num_actions, abs_td);
+    return launch_check("initial_priority_kernel");
+}
+
+}  // extern "C"

@@ -1,0 +1,161 @@
+"""Learner with the reference's interface over the fused TD/priority kernels.
+
+Mirror of /root/reference/learner.py:10-80.  The duelling conv/MLP forward and
+backward stay on PyTorch/cuDNN (the model class is used unchanged when
+``duelling_network.DuellingDQN`` is importable, otherwise an equivalent module
+from qnet.py); everything between the model outputs and the replay — n-step
+double-DQN target, TD error, loss, |delta|^alpha priority and its write-back —
+runs in libapexb200 kernels (K5 + K2).
+"""
+from __future__ import annotations
+
+import time
+
+import numpy as np
+import torch
+
+from . import _C, ops
+from .replay import N_Step_Transition, ReplayMemory
+
+
+def make_q_network(state_shape, action_dim):
+    try:
+        from duelling_network import DuellingDQN          # the reference's model file, unchanged
+        return DuellingDQN(state_shape, action_dim)
+    except ImportError:
+        from .qnet import DuellingQNet
+        return DuellingQNet(state_shape, action_dim)
+
+
+class _TDLoss(torch.autograd.Function):
+    """loss_mean = mean_b loss(R + Gamma*Q_tgt(S_tpn)[argmax Q(S_tpn)] - Q(S_t)[A]); grad flows to Q(S_t) only
+    (learner.py:43-48: the target is built under no_grad)."""
+
+    @staticmethod
+    def forward(ctx, q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, replay, idx, alpha, eps, loss_kind, kappa):
+        q_on_t, q_on_tpn, q_tg_tpn = (x.detach().contiguous().float() for x in (q_on_t, q_on_tpn, q_tg_tpn))
+        if replay is not None:
+            delta, prio, loss, mean = replay.td_update(idx, q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, loss_kind, kappa)
+        else:
+            delta, prio, loss, mean = ops.td_forward(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, alpha, eps, loss_kind, kappa)
+        ctx.save_for_backward(delta, A)
+        ctx.meta = (q_on_t.shape[1], loss_kind, kappa)
+        ctx.mark_non_differentiable(delta, prio, loss)
+        return mean.reshape(()), delta, prio, loss
+
+    @staticmethod
+    def backward(ctx, g_mean, _gd, _gp, _gl):
+        delta, A = ctx.saved_tensors
+        nA, loss_kind, kappa = ctx.meta
+        g = g_mean.detach().reshape(1).float().contiguous()
+        return (ops.td_backward(delta, A, g, nA, loss_kind, kappa),) + (None,) * 11
+
+
+def td_loss(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, alpha=0.6, eps=0.0, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0,
+            replay=None, idx=None):
+    """Differentiable fused loss.  Returns (loss_mean, delta, prio, loss).  With `replay` and `idx`
+    the new priorities are also written into the replay's sum tree in the same call."""
+    return _TDLoss.apply(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, replay, idx, alpha, eps, loss_kind, kappa)
+
+
+class Learner(object):
+    def __init__(self, env_conf, learner_params, shared_state, shared_replay_memory):
+        # learner.py:11-27.  Networks are built on the CPU here; they move to the GPU on first use
+        # inside the process that runs learn() (main.py:45-47 forks after construction).
+        self.state_shape = env_conf["state_shape"]
+        action_dim = env_conf["action_dim"]
+        self.action_dim = action_dim
+        self.params = learner_params
+        self.shared_state = shared_state
+        self.Q = make_q_network(self.state_shape, action_dim)
+        self.Q_double = make_q_network(self.state_shape, action_dim)
+        if self.params.get("load_saved_state"):
+            try:
+                self.Q.load_state_dict(torch.load(self.params["load_saved_state"])["Q_state"])
+            except FileNotFoundError:
+                print("WARNING: No trained model found. Training from scratch")
+        self.shared_state["Q_state_dict"] = self.Q.state_dict()
+        self.replay_memory = shared_replay_memory
+        self.optimizer = torch.optim.RMSprop(self.Q.parameters(), lr=0.00025 / 4, weight_decay=0.95, eps=1.5e-7)
+        self.num_q_updates = 0
+        self.loss_kind = _C.LOSS_HUBER if self.params.get("loss", "half_sq") == "huber" else _C.LOSS_HALF_SQ
+        self.kappa = float(self.params.get("huber_kappa", 1.0))
+        self.alpha = float(self.params.get("priority_exponent", getattr(shared_replay_memory, "alpha", 0.6)))
+        self.device = None
+
+    # ------------------------------------------------------------------ helpers
+    def _to_device(self):
+        if self.device is None:
+            if not torch.cuda.is_available():
+                raise RuntimeError("apex_b200.Learner needs a CUDA device (no CPU fallback)")
+            self.device = torch.device("cuda", torch.cuda.current_device())
+            self.Q.to(self.device)
+            self.Q_double.to(self.device)
+            # optimizer state is created lazily by torch, after the move
+        return self.device
+
+    def _fast(self):
+        return isinstance(self.replay_memory, ReplayMemory)
+
+    def _loss_from_tensors(self, S_t, S_tpn, A, R, Gamma, replay=None, idx=None):
+        with torch.no_grad():                                                  # learner.py:43-45
+            q_tg_tpn = self.Q_double(S_tpn)[2]
+            q_on_tpn = self.Q(S_tpn)[2]
+        q_on_t = self.Q(S_t)[2]                                                # learner.py:46
+        return td_loss(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, self.alpha, 0.0, self.loss_kind, self.kappa,
+                       replay=replay, idx=idx)
+
+    # ------------------------------------------------------------- reference API
+    def compute_loss_and_priorities(self, xp_batch):
+        """learner.py:29-52: list of records -> (loss.mean(), {key: |delta|})."""
+        dev = self._to_device()
+        n = N_Step_Transition(*zip(*xp_batch))
+        S_t = torch.from_numpy(np.array(n.S_t)).to(dev).float()
+        S_tpn = torch.from_numpy(np.array(n.S_tpn)).to(dev).float()
+        R = torch.tensor(np.array(n.R_ttpB, dtype=np.float32), device=dev)
+        G = torch.tensor(np.array(n.Gamma_ttpB, dtype=np.float32), device=dev)
+        A = torch.tensor(np.array(n.A_t, dtype=np.int32), device=dev)
+        loss, delta, _prio, _ = self._loss_from_tensors(S_t, S_tpn, A, R, G)
+        abs_td = delta.abs().cpu().numpy()
+        return loss, {k: abs_td[i] for i, k in enumerate(n.key)}                # per-record |delta|
+
+    def update_Q(self, loss):
+        """learner.py:54-61."""
+        self.optimizer.zero_grad()
+        loss.backward()
+        self.optimizer.step()
+        self.num_q_updates += 1
+        freq = self.params["q_target_sync_freq"]
+        literal = bool(self.params.get("literal_target_sync", False))
+        if (self.num_q_updates % freq != 0) if literal else (self.num_q_updates % freq == 0):
+            self.Q_double.load_state_dict(self.Q.state_dict())
+
+    def step_fast(self, u=None):
+        """One learner step with the batch resident in HBM: K3 -> K4 -> model -> K5+K2 -> optimiser."""
+        self._to_device()
+        B = int(self.params["replay_sample_size"])
+        b = self.replay_memory.sample_tensors(B, u=u)
+        shape = (B,) + tuple(self.state_shape)
+        S_t, S_tpn = b.S_t.view(shape).float(), b.S_tpn.view(shape).float()
+        loss, delta, prio, _ = self._loss_from_tensors(S_t, S_tpn, b.A, b.R, b.Gamma, replay=self.replay_memory, idx=b.idx)
+        self.update_Q(loss)
+        return loss
+
+    def learn(self, T):
+        """learner.py:63-80."""
+        while self.replay_memory.size() <= self.params["min_replay_mem_size"]:
+            time.sleep(1)
+        fast = self._fast()
+        publish = int(self.params.get("weight_publish_freq", 500 if fast else 1))
+        for t in range(T):
+            if fast:
+                self.step_fast()
+            else:
+                batch = self.replay_memory.sample(int(self.params["replay_sample_size"]))
+                loss, priorities = self.compute_loss_and_priorities(batch)
+                self.update_Q(loss)
+                self.replay_memory.set_priorities(priorities)
+            if t % publish == 0:
+                self.shared_state["Q_state_dict"] = {k: v.detach().cpu() for k, v in self.Q.state_dict().items()}
+            if t % self.params["remove_old_xp_freq"] == 0:
+                self.replay_memory.remove_to_fit()

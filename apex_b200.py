@@ -1,0 +1,12 @@
+"""Import shim: ``import apex_b200`` loads the package directory ``ape-x-dqn_b200/``
+(whose name is not a valid Python identifier) under the module name apex_b200."""
+import importlib.util
+import os
+import sys
+
+_dir = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ape-x-dqn_b200")
+_spec = importlib.util.spec_from_file_location("apex_b200", os.path.join(_dir, "__init__.py"),
+                                               submodule_search_locations=[_dir])
+_mod = importlib.util.module_from_spec(_spec)
+sys.modules["apex_b200"] = _mod
+_spec.loader.exec_module(_mod)

@@ -1,0 +1,238 @@
+/*
+ * apexb200.h — C ABI of libapexb200.so: B200 (sm_100a) prioritized experience
+ * replay and learner data path for Ape-X DQN.
+ *
+ * The reference (lefarov/Ape-X-DQN) is pure Python and has no FFI; the boundary
+ * this library sits behind is the Python class surface of replay.py / learner.py
+ * / actor.py.  Each entry point below names the reference code it replaces
+ * (file:line in the reference repository).  The host-side mirror classes in
+ * ape-x-dqn_b200/ bind these symbols with ctypes.
+ *
+ * Conventions
+ *   - every function returns 0 (APEXB200_OK) or a negative APEXB200_E* code and
+ *     never throws; apexb200_last_error() gives a per-thread message;
+ *   - pointers are DEVICE pointers unless the name ends in _host; the caller
+ *     (PyTorch) owns every input/output buffer and keeps it alive until the
+ *     stream has run past the call;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *     no entry point synchronises or allocates except replay_create/destroy,
+ *     replay_status and the *_host accessors;
+ *   - one replay handle is driven from one host thread at a time; calls on one
+ *     stream are totally ordered, which is what gives add/sample/set_priorities
+ *     their reference (sequential) semantics.
+ *
+ * Fixed-point priorities: a leaf of the sum tree is the unsigned 64-bit integer
+ *     leaf = min(floor(double(float(priority^alpha)) * 2^24), 2^36 - 1)
+ * so every tree sum is exact and independent of reduction order (deterministic),
+ * and the proportional search is bit-exact against an integer
+ * searchsorted(cumsum(leaves), target, side='right').
+ */
+#ifndef APEXB200_H_
+#define APEXB200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define APEXB200_VERSION 100            /* 0.1.0 */
+
+#define APEXB200_OK        0
+#define APEXB200_EINVAL   -1            /* bad argument (null pointer, size, alignment) */
+#define APEXB200_ECUDA    -2            /* CUDA runtime error (see last_error) */
+#define APEXB200_ENOMEM   -3            /* device allocation failed */
+#define APEXB200_ERANGE   -4            /* size beyond a documented limit */
+
+#define APEXB200_FRAC_BITS   24
+#define APEXB200_LEAF_MAX    ((1ull << 36) - 1)
+#define APEXB200_MAX_CAPACITY (1ll << 24)   /* records per handle (shard) */
+#define APEXB200_MAX_ACTIONS 64
+
+#define APEXB200_LOSS_HALF_SQ 0         /* 1/2 delta^2, learner.py:48 */
+#define APEXB200_LOSS_HUBER   1         /* Huber(kappa) */
+
+/* device-side status bits, accumulated in the handle (replay_status) */
+#define APEXB200_ST_EMPTY_TREE   1      /* sample on a tree whose total is zero */
+#define APEXB200_ST_BAD_INDEX    2      /* record index outside [0, capacity) */
+#define APEXB200_ST_BAD_TARGET   4      /* target >= total in sample_targets */
+#define APEXB200_ST_BAD_ACTION   8      /* action outside [0, num_actions) */
+
+typedef struct apexb200_replay *apexb200_replay_t;
+
+/* Layout of one replay shard in HBM.  capacity records are split into `lanes`
+ * equal rings (one per actor group); each record owns `frames_per_record`
+ * consecutive frame slots and may also reference frames of up to `lookback`
+ * earlier records of its lane (stream layout: frames_per_record = 1, lookback =
+ * frames_per_state - 1 + n_step; materialised layout used by the reference-shaped
+ * add(): frames_per_record = 2 * frames_per_state, lookback = 0).
+ * Replaces the python list/dicts of ReplayMemory.__init__ (replay.py:9-16) and
+ * the N_Step_Transition record (replay.py:5). */
+typedef struct apexb200_replay_config {
+    int64_t capacity;            /* records; multiple of lanes; <= APEXB200_MAX_CAPACITY */
+    int32_t lanes;
+    int32_t frames_per_record;
+    int32_t lookback;            /* records */
+    int32_t frames_per_state;    /* C */
+    int32_t frame_bytes;         /* 7056 for 84x84 uint8; multiple of 16 */
+    int32_t num_actions;         /* >0: also store the actor's qS_t/qS_tpn rows */
+    float   alpha;               /* priority exponent, params['priority_exponent'] replay.py:14 */
+    int32_t device;              /* CUDA device ordinal */
+} apexb200_replay_config;
+
+int         apexb200_version(void);
+const char *apexb200_strerror(int code);
+const char *apexb200_last_error(void);
+
+/* ---- lifetime: ReplayMemory.__init__ (replay.py:9-16) ------------------- */
+int apexb200_replay_create(apexb200_replay_t *out, const apexb200_replay_config *cfg);
+int apexb200_replay_destroy(apexb200_replay_t h);
+/* ReplayMemory.size (replay.py:82-83): records held, min(inserted, capacity) per lane. */
+int apexb200_replay_size(apexb200_replay_t h, int64_t *size_host);
+int apexb200_replay_device_bytes(apexb200_replay_t h, int64_t *bytes_host);
+/* Reads and clears the device status word (synchronises `stream`). */
+int apexb200_replay_status(apexb200_replay_t h, int32_t *status_host, void *stream);
+
+/* ---- K6 insert: ReplayMemory.add (replay.py:59-69) + Actor.compute_priorities
+ * (actor.py:127-143) + FIFO eviction (replay.py:71-80, as ring overwrite) ------
+ * Appends `count` records to ring `lane`.  frames [count*frames_per_record,
+ * frame_bytes] u8; rel [count, 2C] int32 offsets (<= 0, frame units, relative to
+ * the record's own last frame, wrapping inside the lane) naming the C frames of
+ * S_t then the C frames of S_tpn; A/R/Gamma [count].  prio = raw |TD| priorities
+ * [count] or NULL, in which case |R + Gamma*max_a q_tpn - q_t[A]| is computed from
+ * q_t/q_tpn [count, num_actions] (which are also stored when the handle was
+ * created with num_actions > 0).  The `lookback` records after the new head are
+ * invalidated (leaf = 0) because frames they reference were overwritten.
+ * first_slot_host (nullable) receives the record index of the first new record. */
+int apexb200_replay_insert(apexb200_replay_t h, int32_t lane, int32_t count,
+                           const uint8_t *frames, const int32_t *rel,
+                           const int32_t *A, const float *R, const float *Gamma,
+                           const float *prio, const float *q_t, const float *q_tpn,
+                           int64_t *first_slot_host, void *stream);
+
+/* ---- K1 build: ReplayMemory.update_sample_probabilities (replay.py:18-30) --
+ * Recomputes every inner level from the leaves, level by level. */
+int apexb200_tree_build(apexb200_replay_t h, void *stream);
+
+/* ---- K2 point update: ReplayMemory.set_priorities (replay.py:32-42) -------
+ * idx [count] record indices; duplicates resolve as "last in batch order wins"
+ * (dict.update, replay.py:40).  tree_update takes raw priorities |delta| and
+ * stores max(|delta|, eps)^alpha; tree_set_leaves stores exact u64 leaves. */
+int apexb200_tree_update(apexb200_replay_t h, const int32_t *idx, const float *prio,
+                         int32_t count, float eps, void *stream);
+int apexb200_tree_set_leaves(apexb200_replay_t h, const int32_t *idx, const uint64_t *leaves,
+                             int32_t count, void *stream);
+/* Sum of all leaves (the normaliser of replay.py:24) -> *total (device u64). */
+int apexb200_tree_total(apexb200_replay_t h, uint64_t *total, void *stream);
+/* Tree geometry: number of levels (leaves = level 0) and entries per level. */
+int apexb200_tree_geometry(apexb200_replay_t h, int32_t *n_levels_host, int64_t *sizes_host /*[8]*/);
+/* Copy `count` nodes of `level` starting at `offset` to out (device or host). */
+int apexb200_tree_read(apexb200_replay_t h, int32_t level, int64_t offset, int64_t count,
+                       uint64_t *out, void *stream);
+/* Bulk restore: overwrite leaves [offset, offset+count) (then call tree_build). */
+int apexb200_tree_load_leaves(apexb200_replay_t h, const uint64_t *leaves, int64_t offset,
+                              int64_t count, void *stream);
+
+/* ---- K3 proportional search: the np.random.choice call of ReplayMemory.sample
+ * (replay.py:52-53) ---------------------------------------------------------
+ * u [count] fp64 uniform draws in [0,1) (supplied by the caller so that both
+ * sides consume the same stream); one warp per draw descends the 32-ary tree.
+ * idx_out[j] = #{i : cumsum(leaves)[i] <= target_j}, target_j =
+ * min(trunc(u_j * double(total)), total-1).  leaf_out (nullable) = the selected
+ * leaf, total_out (nullable, 1 element) = tree total (for importance weights).
+ * fsel_out (nullable) [count, 2C] = the frame slots of the selected records. */
+int apexb200_sample(apexb200_replay_t h, const double *u, int32_t count, int32_t *idx_out,
+                    uint64_t *leaf_out, uint64_t *total_out, int32_t *fsel_out, void *stream);
+/* K3 with the PER stratification done in the kernel (the reference draws i.i.d. from
+ * numpy's global RNG, replay.py:52; stratified draws are the Ape-X/PER paper's variant
+ * of the same law): u_j = (j + v_j)/count, v_j = splitmix64(seed, call counter, j) *
+ * 2^-53.  The handle keeps the call counter on the device and advances it by one per
+ * call, so the launch can be replayed from a CUDA graph.  u_out (nullable) [count]
+ * receives the draws so that a checker can replay them. */
+int apexb200_sample_stratified(apexb200_replay_t h, uint64_t seed, int32_t count, int32_t *idx_out,
+                               uint64_t *leaf_out, uint64_t *total_out, int32_t *fsel_out, double *u_out,
+                               void *stream);
+/* Same search from explicit integer targets (sharded sampling); count_dev
+ * (nullable) is a device int32 holding the live count <= max_count. */
+int apexb200_sample_targets(apexb200_replay_t h, const uint64_t *targets, const int32_t *count_dev,
+                            int32_t max_count, int32_t *idx_out, uint64_t *leaf_out,
+                            int32_t *fsel_out, void *stream);
+
+/* ---- K4 gather: the batch assembly of ReplayMemory.sample (replay.py:54-56)
+ * and the np.array stacking of learner.py:35-41 -----------------------------
+ * Copies, for each of `count` record indices (row order preserved), the C frames
+ * of S_t and of S_tpn into S_t/S_tpn [count, C, frame_bytes] u8 and A/R/Gamma
+ * (and q_t/q_tpn if stored and non-NULL).  fsel (nullable) = frame slots from
+ * apexb200_sample, which saves one dependent lookup.  count_dev as above. */
+int apexb200_gather(apexb200_replay_t h, const int32_t *idx, const int32_t *fsel, int32_t count,
+                    const int32_t *count_dev, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R,
+                    float *Gamma, float *q_t, float *q_tpn, void *stream);
+/* 0 = per-warp 16-byte vector copy, 1 = TMA bulk copy staged through shared memory. */
+int apexb200_set_gather_variant(int32_t variant);
+
+/* ---- K5 loss / TD / priority: Learner.compute_loss_and_priorities
+ * (learner.py:43-52) ---------------------------------------------------------
+ * Inputs are the three Q tensors the unchanged model produced, [B, num_actions]
+ * fp32 row-major: q_on_t = Q(S_t), q_on_tpn = Q(S_tpn), q_tg_tpn = Q_target(S_tpn).
+ * Outputs [B]: delta, prio = max(|delta|, eps)^alpha, loss; loss_mean [1] summed
+ * in a fixed order.  workspace: apexb200_td_workspace_bytes(B) bytes of device
+ * scratch owned by the caller (256-byte aligned), contents need not be preserved. */
+int apexb200_td_workspace_bytes(int32_t B, int64_t *bytes_host);
+int apexb200_td_fwd(const float *q_on_t, const float *q_on_tpn, const float *q_tg_tpn,
+                    const int32_t *A, const float *R, const float *Gamma, int32_t B,
+                    int32_t num_actions, float alpha, float eps, int32_t loss_kind, float kappa,
+                    float *delta, float *prio, float *loss, float *loss_mean,
+                    void *workspace, int64_t workspace_bytes, void *stream);
+/* Gradient of loss_mean w.r.t. q_on_t (loss.backward() through learner.py:46-48):
+ * grad_q [B, num_actions], zero except column A_b. grad_loss_mean: device scalar. */
+int apexb200_td_bwd(const float *delta, const int32_t *A, const float *grad_loss_mean, int32_t B,
+                    int32_t num_actions, int32_t loss_kind, float kappa, float *grad_q, void *stream);
+/* K5 + K2 fused: td_fwd, then the new priorities are written into the leaves of
+ * idx [B] and their ancestors refreshed (learner.py:70 + :76 in one call). */
+int apexb200_td_fwd_update(apexb200_replay_t h, const int32_t *idx,
+                           const float *q_on_t, const float *q_on_tpn, const float *q_tg_tpn,
+                           const int32_t *A, const float *R, const float *Gamma, int32_t B,
+                           int32_t num_actions, float eps, int32_t loss_kind, float kappa,
+                           float *delta, float *prio, float *loss, float *loss_mean,
+                           void *workspace, int64_t workspace_bytes, void *stream);
+
+/* ---- K7 n-step return: ExperienceBuffer.update_buffer (actor.py:29-43),
+ * intended semantics, vectorised over E actors x T steps --------
+ * R[e,t] = sum_{k<m} gamma^k r[e,t+k], Gamma = gamma^m, or 0 when a terminal lies
+ * in the window; span = m, or 0 while the window is still incomplete. */
+int apexb200_nstep(const float *rewards, const uint8_t *dones, int32_t E, int32_t T, int32_t n,
+                   float gamma, float *R, float *Gamma, int32_t *span, void *stream);
+/* Actor.compute_priorities (actor.py:127-143): |R + Gamma*max_a q_tpn - q_t[A]|. */
+int apexb200_initial_priority(const float *q_t, const float *q_tpn, const int32_t *A,
+                              const float *R, const float *Gamma, int32_t count,
+                              int32_t num_actions, float *abs_td, void *stream);
+
+/* ---- K8 shard routing (no reference counterpart: the reference is single
+ * process; this is the multi-GPU split of ReplayMemory.sample) ----
+ * totals [G] = all-gathered shard totals.  For each draw u_j the global target is
+ * min(trunc(u_j*double(T)), T-1); this rank keeps the draws whose target falls in
+ * its prefix interval, in increasing j: local_targets/local_pos [count] (target
+ * minus the rank's prefix, and j), local_count [1]. */
+int apexb200_shard_targets(const uint64_t *totals, int32_t G, int32_t rank, const double *u,
+                           int32_t count, uint64_t *local_targets, int32_t *local_pos,
+                           int32_t *local_count, void *stream);
+
+/* ---- raw access for checkpoint / tests (learner.py:18-23 is load-only; the
+ * replay itself is never persisted by the reference) ---------------------- */
+#define APEXB200_BUF_FRAMES 0
+#define APEXB200_BUF_FIDX   1
+#define APEXB200_BUF_ACTION 2
+#define APEXB200_BUF_REWARD 3
+#define APEXB200_BUF_GAMMA  4
+#define APEXB200_BUF_QT     5
+#define APEXB200_BUF_QTPN   6
+#define APEXB200_BUF_LEAVES 7
+int apexb200_replay_buffer(apexb200_replay_t h, int32_t which, void **ptr_host, int64_t *bytes_host);
+/* Host-side ring heads: total records ever inserted per lane ([lanes] int64). */
+int apexb200_replay_get_heads(apexb200_replay_t h, int64_t *lane_count_host);
+int apexb200_replay_set_heads(apexb200_replay_t h, const int64_t *lane_count_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* APEXB200_H_ */

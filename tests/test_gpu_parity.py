@@ -1,0 +1,507 @@
+"""GPU parity tests (run on the B200 box with -m gpu): every CUDA entry point, called
+through the C ABI (ctypes), against the CPU oracle on the same seeded inputs.
+
+Bars: record indices bit-exact, gathered batches byte-exact, tree nodes bit-exact,
+delta / priority / loss within 1e-5 relative (fp32).
+"""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+
+from oracle import nstep_oracle as no            # noqa: E402
+from oracle import replay_oracle as ro           # noqa: E402
+from oracle import td_oracle as to               # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def apex():
+    import apex_b200
+    apex_b200._C.lib()
+    torch.cuda.set_device(0)
+    return apex_b200
+
+
+def dev(x, dtype=None):
+    t = torch.as_tensor(np.ascontiguousarray(x))
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.cuda()
+
+
+def u64(t):
+    return t.cpu().numpy().view(np.uint64) if t.dtype == torch.int64 else t.cpu().numpy()
+
+
+def make_mem(apex, N, C=1, F=16, layout="materialised", lanes=1, n=3, nA=0, alpha=0.6):
+    mem = apex.ReplayMemory(N, {"priority_exponent": alpha, "layout": layout, "lanes": lanes, "n_step": n,
+                                "state_shape": (C, 1, F), "num_actions": nA})
+    mem._ensure()
+    return mem
+
+
+def load_leaves(apex, mem, leaves):
+    t = dev(np.asarray(leaves, np.uint64).view(np.int64))
+    apex._C.call("apexb200_tree_load_leaves", mem._h, apex._C.ptr(t), 0, int(t.numel()), apex._C.stream_ptr())
+    mem.update_sample_probabilities()          # K1
+
+
+def read_levels(apex, mem):
+    nl, sizes = C.c_int32(), (C.c_int64 * 8)()
+    apex._C.call("apexb200_tree_geometry", mem._h, C.byref(nl), sizes)
+    out = []
+    for l in range(nl.value):
+        t = torch.empty(sizes[l], dtype=torch.int64, device="cuda")
+        apex._C.call("apexb200_tree_read", mem._h, l, 0, sizes[l], apex._C.ptr(t), apex._C.stream_ptr())
+        out.append(u64(t))
+    return out
+
+
+# ------------------------------------------------------------------ K1 / K2 tree
+@pytest.mark.parametrize("N", [1, 31, 32, 33, 1000, 1 << 15, (1 << 20) + 17])
+def test_tree_build_bit_exact(apex, N):
+    rng = np.random.default_rng(N)
+    leaves = rng.integers(0, ro.LEAF_MAX, N, dtype=np.uint64)
+    leaves[rng.random(N) < 0.3] = 0
+    mem = make_mem(apex, N)
+    load_leaves(apex, mem, leaves)
+    got, want = read_levels(apex, mem), ro.build_levels(leaves)
+    assert [len(x) for x in got] == ro.level_sizes(N)
+    for g, w in zip(got, want):
+        np.testing.assert_array_equal(g, w)
+    assert mem.total() == int(leaves.sum(dtype=np.uint64))
+
+
+@pytest.mark.parametrize("N,count", [(1000, 7), (1000, 1024), (1 << 16, 1025), (1 << 16, 4096), (1 << 21, 512)])
+def test_tree_update_last_writer_wins_and_matches_rebuild(apex, N, count):
+    rng = np.random.default_rng(count)
+    leaves = rng.integers(0, 1 << 30, N, dtype=np.uint64)
+    mem = make_mem(apex, N)
+    load_leaves(apex, mem, leaves)
+    ring_leaves = leaves.copy()
+    for rep in range(3):
+        idx = rng.integers(0, N, count).astype(np.int32)
+        idx[: count // 3] = idx[count // 3: 2 * (count // 3)][: count // 3]      # force duplicates
+        vals = rng.integers(0, 1 << 34, count, dtype=np.uint64)
+        mem.set_leaves(dev(idx), dev(vals.view(np.int64)))
+        for i, v in zip(idx.tolist(), vals.tolist()):
+            ring_leaves[i] = v                                                    # sequential = last writer wins
+        got = read_levels(apex, mem)
+        for g, w in zip(got, ro.build_levels(ring_leaves)):
+            np.testing.assert_array_equal(g, w)
+    mem.check_status()
+
+
+def test_tree_update_priority_conversion(apex):
+    rng = np.random.default_rng(2)
+    N, count = 5000, 700
+    mem = make_mem(apex, N, alpha=0.6)
+    idx = rng.permutation(N)[:count].astype(np.int32)
+    td = (np.abs(rng.standard_normal(count)) * 3).astype(np.float32)
+    td[:5] = [0.0, 1.0, 1e-8, 1e7, 2.5]
+    mem.update_priorities(dev(idx), dev(td))
+    got = u64(mem.buffer(apex._C.BUF_LEAVES))[idx].astype(np.float64)
+    want = ro.priority_to_leaf(ro.pow_priority(td, 0.6)).astype(np.float64)
+    np.testing.assert_allclose(got, want, rtol=RTOL, atol=2)
+    assert got[0] == 0 and got[1] == 1 << 24 and got[3] == ro.LEAF_MAX
+    # the leaf is an exact function of the fp32 priority the kernel computed
+    levels = read_levels(apex, mem)
+    np.testing.assert_array_equal(levels[-1].sum(dtype=np.uint64), levels[0].sum(dtype=np.uint64))
+
+
+# ---------------------------------------------------------------- K3 descent
+@pytest.mark.parametrize("N", [1, 5, 32, 33, 1024, 1000, 40000, 1 << 20, (1 << 21) + 3])
+@pytest.mark.parametrize("strat", [False, True])
+def test_sample_indices_bit_exact(apex, N, strat):
+    rng = np.random.default_rng(N + strat)
+    pri = np.abs(rng.standard_normal(N)) + 1e-3
+    leaves = ro.priority_to_leaf(ro.pow_priority(pri, 0.6))
+    leaves[rng.random(N) < 0.2] = 0
+    if leaves.sum() == 0:
+        leaves[0] = 5
+    mem = make_mem(apex, N)
+    load_leaves(apex, mem, leaves)
+    B = 2048
+    u = ro.stratified_uniforms(B, rng) if strat else rng.random(B)
+    u[:4] = [0.0, 1.0 - 2 ** -53, 0.5, 2 ** -60]
+    leaf_out = torch.empty(B, dtype=torch.int64, device="cuda")
+    total_out = torch.empty(1, dtype=torch.int64, device="cuda")
+    idx = mem.sample_indices(dev(u), leaf_out=leaf_out, total_out=total_out).cpu().numpy()
+    want = ro.tree_sample(leaves, u)
+    np.testing.assert_array_equal(idx, want)
+    np.testing.assert_array_equal(u64(leaf_out), leaves[want])
+    assert int(u64(total_out)[0]) == int(leaves.sum(dtype=np.uint64))
+    assert (leaves[idx] > 0).all()
+    mem.check_status()
+
+
+def test_sample_matches_reference_choice_law(apex, golden_dir):
+    """Same priorities, same uniform draws as np.random.choice consumed (replay.py:52)."""
+    z = np.load(os.path.join(golden_dir, "choice_law.npz"))
+    pri = z["priorities"].astype(np.float32)
+    mem = make_mem(apex, len(pri), alpha=float(z["alpha"]))
+    mem.update_priorities(dev(np.arange(len(pri), dtype=np.int32)), dev(pri))
+    idx = mem.sample_indices(dev(z["u"])).cpu().numpy()
+    assert int((idx != z["picks"]).sum()) == 0
+
+
+def test_stratified_draws_generated_in_kernel(apex):
+    rng = np.random.default_rng(21)
+    N, B = 50000, 512
+    leaves = ro.priority_to_leaf(ro.pow_priority(np.abs(rng.standard_normal(N)) + 1e-3, 0.6))
+    mem = make_mem(apex, N)
+    mem.seed = 0xC0FFEE
+    load_leaves(apex, mem, leaves)
+    for call in range(3):                                    # the device call counter advances by one per call
+        u_out = torch.empty(B, dtype=torch.float64, device="cuda")
+        idx = mem.sample_stratified(B, u_out=u_out).cpu().numpy()
+        u = u_out.cpu().numpy()
+        np.testing.assert_array_equal(u, ro.kernel_stratified_uniforms(0xC0FFEE, call, B))
+        assert ((u >= np.arange(B) / B) & (u < (np.arange(B) + 1) / B)).all()
+        np.testing.assert_array_equal(idx, ro.tree_sample(leaves, u))
+    mem.check_status()
+
+
+def test_sample_targets_and_device_count(apex):
+    rng = np.random.default_rng(9)
+    N = 3000
+    leaves = rng.integers(1, 1 << 28, N, dtype=np.uint64)
+    mem = make_mem(apex, N)
+    load_leaves(apex, mem, leaves)
+    total = int(leaves.sum(dtype=np.uint64))
+    targets = rng.integers(0, total, 500, dtype=np.uint64)
+    idx = torch.full((500,), -7, dtype=torch.int32, device="cuda")
+    cnt = dev(np.array([321], np.int32))
+    apex._C.call("apexb200_sample_targets", mem._h, apex._C.ptr(dev(targets.view(np.int64))), apex._C.ptr(cnt), 500,
+                 apex._C.ptr(idx), None, None, apex._C.stream_ptr())
+    got = idx.cpu().numpy()
+    np.testing.assert_array_equal(got[:321], ro.descend(leaves, targets[:321]))
+    assert (got[321:] == -7).all()
+
+
+def test_empty_tree_sets_status(apex):
+    mem = make_mem(apex, 100)
+    idx = mem.sample_indices(dev(np.array([0.3, 0.6])))
+    assert (idx.cpu().numpy() == -1).all()
+    with pytest.raises(apex._C.ApexError, match="empty tree"):
+        mem.check_status()
+    mem.check_status()            # cleared
+
+
+# ------------------------------------------------------- K6 insert + K4 gather
+@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("C_,F", [(1, 7056), (4, 7056), (4, 64)])
+def test_stream_insert_and_gather_byte_exact(apex, variant, C_, F):
+    rng = np.random.default_rng(10 * C_ + variant)
+    n, lanes, N, nA = 3, 4, 4 * 96, 4
+    W = C_ - 1 + n
+    mem = make_mem(apex, N, C=C_, F=F, layout="stream", lanes=lanes, n=n, nA=nA)
+    ring = ro.RingOracle(N, C_, F, lanes=lanes, fpr=1, lookback=W, alpha=0.6, num_actions=nA)
+    apex._C.call("apexb200_set_gather_variant", variant)
+    try:
+        age0 = np.zeros(lanes, np.int64)
+        for it in range(14):                                   # 14 * 20 = 280 records per lane of 96: wraps twice
+            for lane in range(lanes):
+                m = 20 if it % 3 else 11
+                frames = rng.integers(0, 256, (m, F), dtype=np.uint8)
+                age = age0[lane] + np.arange(m)
+                reset = rng.integers(0, m)
+                age[reset:] -= age[reset]                      # an episode boundary inside the chunk
+                age0[lane] = age[-1] + 1
+                span = rng.integers(1, n + 1, m)
+                rel = apex.stream_offsets(C_, span, age)
+                A = rng.integers(0, nA, m).astype(np.int32)
+                R = rng.standard_normal(m).astype(np.float32)
+                G = np.where(rng.random(m) < 0.2, 0, 0.97).astype(np.float32)
+                q_t, q_tpn = rng.standard_normal((m, nA)).astype(np.float32), rng.standard_normal((m, nA)).astype(np.float32)
+                if it % 2:
+                    prio = (np.abs(rng.standard_normal(m)) + 0.01).astype(np.float32)
+                    s1 = mem.insert(lane, frames, rel, A, R, G, prio=prio, q_t=q_t, q_tpn=q_tpn)
+                    s2 = ring.insert(lane, frames, rel, A, R, G, prio=prio, q_t=q_t, q_tpn=q_tpn)
+                else:                                          # priorities from the actor's q-values (actor.py:138-142)
+                    s1 = mem.insert(lane, frames, rel, A, R, G, q_t=q_t, q_tpn=q_tpn)
+                    s2 = ring.insert(lane, frames, rel, A, R, G, q_t=q_t, q_tpn=q_tpn)
+                np.testing.assert_array_equal(s1, s2)
+        assert mem.size() == ring.size()
+        np.testing.assert_array_equal(mem.buffer(apex._C.BUF_FRAMES).cpu().numpy().reshape(-1, F), ring.frames)
+        np.testing.assert_array_equal(mem.buffer(apex._C.BUF_FIDX).cpu().numpy().reshape(N, 2 * C_), ring.fidx)
+        leaves = u64(mem.buffer(apex._C.BUF_LEAVES))
+        np.testing.assert_allclose(leaves.astype(np.float64), ring.leaves.astype(np.float64), rtol=1e-5, atol=4)
+        assert ((leaves == 0) == (ring.leaves == 0)).all()     # dead zone behind each head
+        for g, w in zip(read_levels(apex, mem), ro.build_levels(leaves)):
+            np.testing.assert_array_equal(g, w)
+        ring.leaves[:] = leaves
+        for B in (1, 33, 512):
+            u = rng.random(B)
+            b = mem.sample_tensors(B, u=dev(u), with_q=True)
+            want = ring.sample(u)
+            np.testing.assert_array_equal(b.idx.cpu().numpy(), want)
+            g = ring.gather(want)
+            np.testing.assert_array_equal(b.fsel.cpu().numpy(), ring.fidx[want])
+            np.testing.assert_array_equal(b.S_t.cpu().numpy(), g["S_t"])
+            np.testing.assert_array_equal(b.S_tpn.cpu().numpy(), g["S_tpn"])
+            np.testing.assert_array_equal(b.A.cpu().numpy(), g["A"])
+            np.testing.assert_array_equal(b.R.cpu().numpy(), g["R"])
+            np.testing.assert_array_equal(b.Gamma.cpu().numpy(), g["G"])
+            np.testing.assert_array_equal(mem._last_q[0].cpu().numpy(), g["q_t"])
+            np.testing.assert_array_equal(mem._last_q[1].cpu().numpy(), g["q_tpn"])
+            # without the pre-resolved frame slots (one more dependent lookup) the bytes are the same
+            b2 = mem.gather(b.idx.clone(), fsel=None, out={k: (torch.empty_like(v) if v is not None else None)
+                                                           for k, v in mem._outputs(B, True).items()})
+            np.testing.assert_array_equal(b2.S_t.cpu().numpy(), g["S_t"])
+            np.testing.assert_array_equal(b2.S_tpn.cpu().numpy(), g["S_tpn"])
+        mem.check_status()
+    finally:
+        apex._C.call("apexb200_set_gather_variant", 0)
+
+
+def test_compat_api_matches_reference_semantics(apex, golden_dir):
+    """add / sample / set_priorities / size with reference-shaped records (replay.py:32-83)."""
+    z = np.load(os.path.join(golden_dir, "choice_law.npz"))
+    K = 600
+    pri = z["priorities"][:K]
+    NT = apex.N_Step_Transition
+    mem = apex.ReplayMemory(K, {"priority_exponent": float(z["alpha"])})
+    rng = np.random.default_rng(4)
+    S = rng.integers(0, 256, (K + 1, 1, 84, 84)).astype(np.float64)            # reference stores float64 (Q20)
+    recs = [NT(S[i], i % 4, float(i), 0.97, None, S[i + 1], None, "k%d" % i) for i in range(K)]
+    for c in range(0, K, 5):                                                   # parameters.json:15 batches of 5
+        chunk = recs[c:c + 5]
+        mem.add({r.key: np.float64(pri[c + j]) for j, r in enumerate(chunk)}, chunk)
+    assert mem.size() == K
+    np.random.seed(99)
+    u = np.random.random_sample(256)
+    want = ro.reference_law_sample(pri, float(z["alpha"]), u)                  # fp64 np.random.choice law
+    np.random.seed(99)
+    got = mem.sample(256)
+    assert [r.key for r in got] == ["k%d" % i for i in want]
+    for r, i in zip(got, want):
+        assert r.S_t.dtype == np.uint8 and r.S_t.shape == (1, 84, 84)
+        np.testing.assert_array_equal(r.S_t, S[i].astype(np.uint8))
+        np.testing.assert_array_equal(r.S_tpn, S[i + 1].astype(np.uint8))
+        assert (r.A_t, r.R_ttpB) == (i % 4, float(i)) and r.Gamma_ttpB == pytest.approx(0.97)
+    # overwrite priorities: only k7 and k9 keep mass
+    mem.set_priorities({"k%d" % i: 0.0 for i in range(K)})
+    mem.set_priorities({"k7": 1.0, "k9": 3.0, "k7 ": 2.0})                     # unknown key is remembered, not an error
+    keys = {r.key for r in mem.sample(64)}
+    assert keys == {"k7", "k9"}
+    # ring eviction: 5 more records overwrite k0..k4 and their priorities
+    more = [NT(S[i], 0, 0.0, 0.0, None, S[i], None, "new%d" % i) for i in range(5)]
+    mem.add({r.key: 1e6 for r in more}, more)
+    assert mem.size() == K
+    assert {r.key for r in mem.sample(64)} <= {"k7", "k9"} | {r.key for r in more}
+    mem.remove_to_fit()
+    mem.update_sample_probabilities()
+    assert mem.size() == K
+
+
+def test_checkpoint_round_trip(apex):
+    rng = np.random.default_rng(12)
+    mem = make_mem(apex, 256, C=2, F=32, layout="stream", lanes=2, n=2)
+    for lane in range(2):
+        m = 100
+        mem.insert(lane, rng.integers(0, 256, (m, 32), dtype=np.uint8), apex.stream_offsets(2, np.full(m, 2), np.arange(m)),
+                   np.zeros(m, np.int32), np.ones(m, np.float32), np.ones(m, np.float32), prio=np.ones(m, np.float32))
+    sd = mem.state_dict()
+    mem2 = apex.ReplayMemory(256, {"priority_exponent": 0.6, "layout": "stream", "lanes": 2, "n_step": 2})
+    mem2.load_state_dict(sd)
+    u = dev(rng.random(64))
+    a, b = mem.sample_tensors(64, u=u), mem2.sample_tensors(64, u=u)
+    assert torch.equal(a.idx, b.idx) and torch.equal(a.S_t, b.S_t) and torch.equal(a.S_tpn, b.S_tpn)
+    assert mem2.size() == mem.size() and mem2.total() == mem.total()
+
+
+# ------------------------------------------------------------------ K5 TD / loss
+@pytest.mark.parametrize("B", [1, 32, 512, 1024, 1025, 4096, 10000])
+@pytest.mark.parametrize("kind", [to.LOSS_HALF_SQ, to.LOSS_HUBER])
+@pytest.mark.parametrize("nA", [4, 18])
+def test_td_forward_backward(apex, B, kind, nA):
+    rng = np.random.default_rng(B + kind + nA)
+    q = [rng.standard_normal((B, nA)).astype(np.float32) * 2 for _ in range(3)]
+    q[1][::7, 1] = q[1][::7].max(axis=1) + 0.0                 # ties: first maximum must win
+    A = rng.integers(0, nA, B).astype(np.int32)
+    R = np.clip(rng.standard_normal(B), -1, 1).astype(np.float32)
+    G = np.where(rng.random(B) < 0.05, 0, 0.970299).astype(np.float32)
+    o = to.td_forward(q[0], q[1], q[2], A, R, G, alpha=0.6, loss_kind=kind, kappa=1.0)
+    delta, prio, loss, mean = apex.ops.td_forward(dev(q[0]), dev(q[1]), dev(q[2]), dev(A), dev(R), dev(G), 0.6, 0.0, kind, 1.0)
+    np.testing.assert_allclose(delta.cpu().numpy(), o["delta"], rtol=RTOL, atol=1e-6)
+    np.testing.assert_allclose(loss.cpu().numpy(), o["loss"], rtol=RTOL, atol=1e-7)
+    np.testing.assert_allclose(prio.cpu().numpy(), o["prio"], rtol=RTOL, atol=1e-7)
+    np.testing.assert_allclose(mean.item(), o["loss_mean"], rtol=RTOL)
+    gq = apex.ops.td_backward(delta, dev(A), dev(np.array([1.5], np.float32)), nA, kind, 1.0)
+    np.testing.assert_allclose(gq.cpu().numpy(), to.td_backward(o["delta"], A, nA, 1.5, kind, 1.0), rtol=RTOL, atol=1e-9)
+    # determinism of the fixed-order mean
+    again = apex.ops.td_forward(dev(q[0]), dev(q[1]), dev(q[2]), dev(A), dev(R), dev(G), 0.6, 0.0, kind, 1.0)[3]
+    assert again.item() == mean.item()
+
+
+def test_td_loss_autograd_matches_torch(apex):
+    torch.manual_seed(0)
+    B, nA = 300, 6
+    q1 = torch.randn(B, nA, device="cuda", requires_grad=True)
+    q2, q3 = torch.randn(B, nA, device="cuda"), torch.randn(B, nA, device="cuda")
+    A = torch.randint(0, nA, (B,), device="cuda", dtype=torch.int32)
+    R, G = torch.randn(B, device="cuda"), torch.full((B,), 0.97, device="cuda")
+    loss, delta, prio, _ = apex.td_loss(q1, q2, q3, A, R, G, alpha=0.6)
+    (loss * 2).backward()
+    r1 = q1.detach().clone().requires_grad_(True)
+    with torch.no_grad():                                                          # learner.py:43-45
+        tgt = R + G * q3.gather(1, torch.argmax(q2, 1).view(-1, 1)).squeeze()
+    qsa = r1.gather(1, A.long().view(-1, 1)).squeeze()                             # learner.py:46
+    ref = (0.5 * (tgt - qsa) ** 2).mean()                                          # learner.py:48,52
+    (ref * 2).backward()
+    torch.testing.assert_close(loss, ref, rtol=RTOL, atol=1e-7)
+    torch.testing.assert_close(q1.grad, r1.grad, rtol=RTOL, atol=1e-9)
+    torch.testing.assert_close(prio, (tgt - qsa).abs().pow(0.6), rtol=RTOL, atol=1e-7)
+
+
+@pytest.mark.parametrize("B", [64, 512, 1024, 3000])
+def test_td_update_writes_priorities_in_place(apex, B):
+    rng = np.random.default_rng(B)
+    N, nA = 1 << 16, 4
+    mem = make_mem(apex, N)
+    leaves = rng.integers(1, 1 << 26, N, dtype=np.uint64)
+    load_leaves(apex, mem, leaves)
+    idx = rng.integers(0, N, B).astype(np.int32)
+    idx[1::9] = idx[0]                                                             # duplicates: last row wins
+    q = [rng.standard_normal((B, nA)).astype(np.float32) for _ in range(3)]
+    A = rng.integers(0, nA, B).astype(np.int32)
+    R, G = rng.standard_normal(B).astype(np.float32), np.full(B, 0.97, np.float32)
+    delta, prio, loss, mean = mem.td_update(dev(idx), dev(q[0]), dev(q[1]), dev(q[2]), dev(A), dev(R), dev(G))
+    o = to.td_forward(q[0], q[1], q[2], A, R, G, alpha=0.6)
+    np.testing.assert_allclose(prio.cpu().numpy(), o["prio"], rtol=RTOL, atol=1e-7)
+    np.testing.assert_allclose(mean.item(), o["loss_mean"], rtol=RTOL)
+    new = ro.priority_to_leaf(prio.cpu().numpy())                                  # exact function of the kernel's fp32 prio
+    for i, v in zip(idx.tolist(), new.tolist()):
+        leaves[i] = v
+    for g, w in zip(read_levels(apex, mem), ro.build_levels(leaves)):
+        np.testing.assert_array_equal(g, w)
+    mem.check_status()
+
+
+# ---------------------------------------------------------------- K7 / a11 / K8
+def test_nstep_kernel(apex):
+    rng = np.random.default_rng(3)
+    for (E, T, n) in [(1, 6, 3), (7, 50, 3), (64, 129, 5), (3, 10, 1)]:
+        r = rng.standard_normal((E, T)).astype(np.float32)
+        d = (rng.random((E, T)) < 0.1)
+        R, G, span = apex.ops.nstep_returns(dev(r), dev(d.astype(np.uint8)), n, 0.99)
+        wR, wG, wspan = no.nstep_intended(r, d, n, 0.99)
+        np.testing.assert_array_equal(span.cpu().numpy(), wspan)
+        np.testing.assert_allclose(R.cpu().numpy(), wR, rtol=RTOL, atol=1e-7)
+        np.testing.assert_allclose(G.cpu().numpy(), wG, rtol=RTOL, atol=0)
+
+
+def test_initial_priority_against_reference_vectors(apex, golden_dir):
+    with open(os.path.join(golden_dir, "initial_priority.json")) as f:
+        cases = json.load(f)
+    for c in cases:
+        got = apex.ops.initial_priority(dev(np.array(c["q_t"], np.float32)), dev(np.array(c["q_tpn"], np.float32)),
+                                        dev(np.array(c["A"], np.int32)), dev(np.array(c["R"], np.float32)),
+                                        dev(np.array(c["Gamma"], np.float32))).cpu().numpy()
+        np.testing.assert_allclose(got, c["per_row_abs_td"], rtol=RTOL, atol=1e-6)
+
+
+def test_shard_routing_equals_single_tree(apex):
+    """§8(e) on one GPU: G shard handles + K8 routing == one tree over the concatenated leaves."""
+    rng = np.random.default_rng(8)
+    G_, n_per, B = 4, 5000, 1024
+    shards = [rng.integers(0, 1 << 28, n_per, dtype=np.uint64) for _ in range(G_)]
+    shards[2][:] = 0                                                               # an empty shard owns no draw
+    mems = []
+    for s in shards:
+        m = make_mem(apex, n_per)
+        load_leaves(apex, m, s)
+        mems.append(m)
+    totals = torch.stack([torch.tensor(m.total() - (1 << 64) if m.total() >= 1 << 63 else m.total()) for m in mems]).cuda()
+    u = rng.random(B)
+    whole = ro.tree_sample(np.concatenate(shards), u)
+    t, shard, local_t = ro.shard_split([int(s.sum(dtype=np.uint64)) for s in shards], u)
+    got = np.full(B, -1, np.int64)
+    for g in range(G_):
+        lt, lp, lc = apex.ops.shard_targets(totals, g, dev(u))
+        cnt = int(lc.item())
+        assert cnt == int((shard == g).sum())
+        np.testing.assert_array_equal(lp.cpu().numpy()[:cnt], np.nonzero(shard == g)[0])
+        np.testing.assert_array_equal(u64(lt)[:cnt], local_t[shard == g])
+        idx = torch.full((B,), -1, dtype=torch.int32, device="cuda")
+        apex._C.call("apexb200_sample_targets", mems[g]._h, apex._C.ptr(lt), apex._C.ptr(lc), B, apex._C.ptr(idx), None,
+                     None, apex._C.stream_ptr())
+        got[lp.cpu().numpy()[:cnt]] = g * n_per + idx.cpu().numpy()[:cnt]
+    np.testing.assert_array_equal(got, whole)
+
+
+# --------------------------------------------------------------- error behaviour
+def test_argument_errors(apex):
+    _C = apex._C
+    h = C.c_void_p()
+    bad = _C.ReplayConfig(100, 3, 1, 0, 1, 7056, 0, 0.6, 0)
+    assert _C.lib().apexb200_replay_create(C.byref(h), C.byref(bad)) == _C.EINVAL          # capacity % lanes
+    bad = _C.ReplayConfig((1 << 24) + 32, 1, 1, 0, 1, 16, 0, 0.6, 0)
+    assert _C.lib().apexb200_replay_create(C.byref(h), C.byref(bad)) == _C.ERANGE
+    bad = _C.ReplayConfig(100, 1, 1, 0, 1, 7050, 0, 0.6, 0)
+    assert _C.lib().apexb200_replay_create(C.byref(h), C.byref(bad)) == _C.EINVAL          # frame_bytes % 16
+    mem = make_mem(apex, 64, layout="stream", lanes=1, n=3, C=4)
+    with pytest.raises(_C.ApexError, match="exceeds lane capacity"):
+        mem.insert(0, np.zeros((60, 16), np.uint8), np.zeros((60, 8), np.int32), np.zeros(60, np.int32),
+                   np.zeros(60, np.float32), np.zeros(60, np.float32), prio=np.ones(60, np.float32))
+    with pytest.raises(_C.ApexError):
+        apex.ops.td_forward(torch.zeros(2000, 4).cuda(), torch.zeros(2000, 4).cuda(), torch.zeros(2000, 4).cuda(),
+                            torch.zeros(2000, dtype=torch.int32).cuda(), torch.zeros(2000).cuda(), torch.zeros(2000).cuda(),
+                            0.6, workspace=torch.empty(256, dtype=torch.uint8, device="cuda"))   # workspace too small
+
+
+# -------------------------------------------- full-size properties (BASELINE sizes)
+def test_full_size_properties_2m(apex):
+    """2M-record shard, B=512: sortedness of indices for sorted draws, gather round trip of
+    self-identifying frames, tree == rebuild after many fused updates (size-independent checks)."""
+    N, C_, F, B, nA = 1 << 21, 4, 7056, 512, 4
+    mem = apex.ReplayMemory(N, {"priority_exponent": 0.6, "layout": "stream", "lanes": 32, "n_step": 3,
+                                "state_shape": (C_, 84, 84)})
+    mem._ensure()
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    lane_cap = N // 32
+    chunk = 8192
+    rel = dev(apex.stream_offsets(C_, np.full(chunk, 3), np.minimum(np.arange(chunk) + 100, 1000)))
+    for lane in range(32):
+        for c in range(lane_cap // chunk):
+            frames = torch.randint(0, 256, (chunk, F), dtype=torch.uint8, device="cuda", generator=g)
+            base = lane * lane_cap + c * chunk
+            tag = (base + torch.arange(chunk, device="cuda", dtype=torch.int64))
+            frames[:, :8] = tag.view(-1, 1).bitwise_right_shift(torch.arange(0, 64, 8, device="cuda")).bitwise_and(255).to(torch.uint8)
+            A = torch.randint(0, nA, (chunk,), dtype=torch.int32, device="cuda", generator=g)
+            R = torch.randn(chunk, device="cuda", generator=g).clamp(-1, 1)
+            G = torch.full((chunk,), 0.970299, device="cuda")
+            prio = torch.randn(chunk, device="cuda", generator=g).abs() + 1e-3
+            mem.insert(lane, frames, rel, A, R, G, prio=prio)
+    assert mem.size() == N
+    rng = np.random.default_rng(4321)
+    leaves = u64(mem.buffer(apex._C.BUF_LEAVES))
+    for step in range(20):
+        u = ro.stratified_uniforms(B, rng)
+        b = mem.sample_tensors(B, u=dev(u))
+        idx = b.idx.cpu().numpy()
+        assert (np.diff(idx) >= 0).all()                                           # sorted draws -> sorted indices
+        if step % 5 == 0:
+            np.testing.assert_array_equal(idx, ro.tree_sample(leaves, u))          # and bit-exact vs the oracle
+        fsel = b.fsel.cpu().numpy().astype(np.int64)
+        tags = b.S_tpn.cpu().numpy()[:, :, :8].astype(np.uint64)
+        got = sum(tags[:, :, k] << np.uint64(8 * k) for k in range(8))
+        np.testing.assert_array_equal(got, fsel[:, C_:].astype(np.uint64))         # each gathered frame names its slot
+        np.testing.assert_array_equal(fsel[:, -1], idx)                            # newest S_tpn frame = the record's own
+        q = [torch.randn(B, nA, device="cuda", generator=g) for _ in range(3)]
+        _, prio, _, _ = mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma)
+        new = ro.priority_to_leaf(prio.cpu().numpy())
+        for i, v in zip(idx.tolist(), new.tolist()):
+            leaves[i] = v
+    for gl, w in zip(read_levels(apex, mem), ro.build_levels(leaves)):
+        np.testing.assert_array_equal(gl, w)
+    mem.check_status()
