@@ -203,3 +203,33 @@ def test_shard_split_equals_single_tree():
     t, shard, local_t = ro.shard_split([int(s.sum(dtype=np.uint64)) for s in shards], u)
     got = np.array([g * 1000 + ro.descend(shards[g], np.array([lt]))[0] for g, lt in zip(shard, local_t)])
     np.testing.assert_array_equal(got, whole)
+
+
+def test_c_oracle_matches_numpy_oracle():
+    """oracle/apex_oracle.c (the timed CPU baseline) == the numpy oracle, bit for bit on indices/bytes."""
+    from oracle.c_oracle import CpuReplay
+    rng = np.random.default_rng(17)
+    N, C_, F, B, nA = 200_000, 2, 64, 256, 4
+    ring = ro.RingOracle(N, C_, F, lanes=4, fpr=1, lookback=C_ - 1 + 3, alpha=0.6)
+    for lane in range(4):
+        m = 40_000
+        rel = np.tile(np.array([[-4, -3, -1, 0]], np.int32), (m, 1))
+        ring.insert(lane, rng.integers(0, 256, (m, F), dtype=np.uint8), rel, rng.integers(0, nA, m), rng.standard_normal(m),
+                    np.full(m, 0.97), prio=np.abs(rng.standard_normal(m)) + 1e-3)
+    cpu = CpuReplay(ring.leaves.copy(), ring.frames, ring.fidx, ring.A, ring.R, ring.G, C_, F, 0.6)
+    assert cpu.threads >= 1
+    for step in range(4):
+        u = ro.stratified_uniforms(B, rng) if step % 2 else rng.random(B)
+        q = [rng.standard_normal((B, nA)).astype(np.float32) for _ in range(3)]
+        want_idx = ring.sample(u)
+        g = ring.gather(want_idx)
+        o = cpu.step(u, *q)
+        np.testing.assert_array_equal(o["idx"], want_idx)
+        np.testing.assert_array_equal(o["S_t"], g["S_t"])
+        np.testing.assert_array_equal(o["S_tpn"], g["S_tpn"])
+        t = to.td_forward(q[0], q[1], q[2], g["A"], g["R"], g["G"], alpha=0.6)
+        np.testing.assert_array_equal(o["delta"], t["delta"])
+        np.testing.assert_allclose(o["prio"], t["prio"], rtol=1e-6)
+        np.testing.assert_allclose(o["loss_mean"], t["loss_mean"], rtol=1e-6)
+        ring.set_leaves(want_idx, ro.priority_to_leaf(o["prio"]))
+        np.testing.assert_array_equal(cpu.leaves, ring.leaves)
