@@ -10,6 +10,7 @@ from .replay import ReplayMemory, N_Step_Transition, Batch, KeyIndex, stream_off
 from .actor import ExperienceBuffer, Actor, Transition        # noqa: F401
 from .learner import Learner, td_loss                         # noqa: F401
 from . import ops                                             # noqa: F401
+from .sharded import ShardedSampler                           # noqa: F401
 
 __all__ = ["ReplayMemory", "Learner", "Actor", "ExperienceBuffer", "N_Step_Transition", "Transition", "Batch",
-           "KeyIndex", "stream_offsets", "td_loss", "ops"]
+           "KeyIndex", "stream_offsets", "td_loss", "ops", "ShardedSampler"]

@@ -35,6 +35,7 @@ struct RingView {
 
 void set_error(const char *fmt, ...);
 int cuda_fail(cudaError_t e, const char *what);
+extern int g_pdl;                            // programmatic dependent launch for the step kernels (default on)
 
 #define APEX_CUDA(call)                                                    \
     do {                                                                   \
@@ -49,6 +50,34 @@ int cuda_fail(cudaError_t e, const char *what);
 
 inline int launch_check(const char *what) {
     cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, what);
+    return APEXB200_OK;
+}
+
+// Programmatic dependent launch (sm_90+): a kernel launched through launch_step() may be
+// scheduled while its predecessor in the stream is still running; it must execute
+// pdl_prologue() as its first statement, which blocks until the predecessor grid has
+// completed and its writes are visible, and lets the *next* kernel start its own ramp-up.
+// At 10-20 us per step the ~2 us launch ramp of every kernel is otherwise exposed.
+__device__ __forceinline__ void pdl_prologue() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+template <typename... KArgs, typename... Args>
+inline int launch_step(const char *what, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                       cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = g_pdl ? 1 : 0;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
     if (e != cudaSuccess) return cuda_fail(e, what);
     return APEXB200_OK;
 }
@@ -74,6 +103,61 @@ __device__ __forceinline__ void propagate_delta(const TreeView &tv, long long i,
         i >>= 5;
         atomicAdd(tv.lvl[l] + i, d);
     }
+}
+
+// Counter-based uniform for the in-kernel stratified draws: splitmix64 finaliser over
+// (seed, call counter, draw position) -> 53 random bits -> [0,1).
+__device__ __forceinline__ double strat_uniform(unsigned long long seed, unsigned long long counter, int j, int count) {
+    unsigned long long z = seed ^ (counter * 0xD1342543DE82EF95ull);
+    z += (unsigned long long)(j + 1) * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    const double v = (double)(z >> 11) * 0x1.0p-53;
+    return ((double)j + v) / (double)count;                 // u_j = (j + v_j) / B
+}
+
+// K3 core.  One warp per draw.  At each level the warp loads the 32 children of the
+// current node (one 256-byte line pair), forms their inclusive prefix sums with
+// shuffles, and the number of prefixes <= target is the child to enter — exactly
+// searchsorted(cumsum, target, side='right') restricted to that node.  The chosen
+// child and the remaining target are broadcast by shuffle; no shared memory.
+__device__ __forceinline__ long long warp_descend(const TreeView &tv, unsigned long long t, bool from_u, double u,
+                                                  unsigned long long *leaf, unsigned long long *total,
+                                                  int32_t *status) {
+    const int lane = threadIdx.x & 31;
+    const int top = tv.n_levels - 1;
+    long long node = 0;
+    unsigned long long lf = 0ull;
+    for (int l = top; l >= 0; --l) {
+        unsigned long long v = tv.lvl[l][node * kFanout + lane];        // padded levels: always in bounds
+        unsigned long long incl = v;
+        #pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned long long n = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += n;
+        }
+        if (l == top) {
+            unsigned long long tot = __shfl_sync(0xffffffffu, incl, 31);
+            *total = tot;
+            if (tot == 0ull) { if (lane == 0) atomicOr(status, APEXB200_ST_EMPTY_TREE); return -1; }
+            if (from_u) {
+                t = (unsigned long long)(u * (double)tot);              // one fp64 multiply, truncation
+                if (t >= tot) t = tot - 1ull;
+            } else if (t >= tot) {
+                if (lane == 0) atomicOr(status, APEXB200_ST_BAD_TARGET);
+                t = tot - 1ull;
+            }
+        }
+        int c = __popc(__ballot_sync(0xffffffffu, incl <= t));
+        c = min(c, 31);
+        unsigned long long excl = __shfl_sync(0xffffffffu, incl - v, c);
+        if (l == 0) lf = __shfl_sync(0xffffffffu, v, c);
+        t -= excl;
+        node = node * kFanout + c;
+    }
+    *leaf = lf;
+    return node;
 }
 
 }  // namespace apexb200

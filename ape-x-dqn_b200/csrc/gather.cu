@@ -1,11 +1,14 @@
 // K4: gather of the sampled stacked frames (+ n-step metadata) straight into the
-// learner's batch tensors.  HBM-bound byte movement: 2C frames of `F` bytes per
-// record are read from random ring slots and written to dense [B, C, F] outputs.
+// learner's batch tensors, and the fused K3+K4 kernel (proportional search + gather in
+// one launch).  Byte movement only: 2C frames of F bytes per record are read from
+// random ring slots and written to dense [B, C, F] outputs.  The frame reads come from
+// HBM (the frame store is far larger than L2); the batch that is written stays in the
+// 126 MB L2 for its consumer.
 #include "common.cuh"
 
 namespace apexb200 {
 
-static int g_gather_variant = 0;
+static int g_gather_variant = 1;
 
 __device__ __forceinline__ uint4 ld_stream(const uint4 *p) {
     uint4 r;
@@ -14,8 +17,6 @@ __device__ __forceinline__ uint4 ld_stream(const uint4 *p) {
     return r;
 }
 
-// Resolve work item -> (source frame slot, destination pointer).  Item it in
-// [0, count*2C): row b = it / 2C, k = it % 2C; k < C is frame k of S_t, else of S_tpn.
 struct GatherArgs {
     const int32_t *idx, *fsel, *count_dev;
     uint8_t *S_t, *S_tpn;
@@ -23,6 +24,22 @@ struct GatherArgs {
     float *R, *G, *q_t, *q_tpn;
     int count;
 };
+
+struct SampleArgs {
+    const double *u;                 // caller's draws, or null -> stratified draws generated here
+    unsigned long long seed;
+    int32_t *idx_out, *fsel_out;
+    unsigned long long *leaf_out, *total_out;
+    double *u_out;
+};
+
+// Work item `it` in [0, count*2C): row b = it / 2C, k = it % 2C; k < C is frame k of S_t,
+// else frame k-C of S_tpn.
+__device__ __forceinline__ uint8_t *item_dst(const RingView &rv, const GatherArgs &ga, long long b, int k) {
+    uint8_t *base = k < rv.C ? ga.S_t : ga.S_tpn;
+    int kk = k < rv.C ? k : k - rv.C;
+    return base + (b * rv.C + kk) * (long long)rv.F;
+}
 
 __device__ __forceinline__ bool resolve_item(const RingView &rv, const GatherArgs &ga, long long it, int count,
                                              const uint8_t **src, uint8_t **dst, int32_t *status) {
@@ -40,16 +57,11 @@ __device__ __forceinline__ bool resolve_item(const RingView &rv, const GatherArg
     }
     if (f < 0 || f >= rv.N * rv.fpr) { atomicOr(status, APEXB200_ST_BAD_INDEX); return false; }
     *src = rv.frames + f * rv.F;
-    uint8_t *base = k < rv.C ? ga.S_t : ga.S_tpn;
-    int kk = k < rv.C ? k : k - rv.C;
-    *dst = base + (b * rv.C + kk) * (long long)rv.F;
+    *dst = item_dst(rv, ga, b, k);
     return true;
 }
 
-__device__ __forceinline__ void gather_meta(const RingView &rv, const GatherArgs &ga, int b, int count, int32_t *status) {
-    if (b >= count) return;
-    long long slot = ga.idx[b];
-    if (slot < 0 || slot >= rv.N) { atomicOr(status, APEXB200_ST_BAD_INDEX); return; }
+__device__ __forceinline__ void copy_meta_row(const RingView &rv, const GatherArgs &ga, int b, long long slot) {
     if (ga.A) ga.A[b] = rv.A[slot];
     if (ga.R) ga.R[b] = rv.R[slot];
     if (ga.G) ga.G[b] = rv.G[slot];
@@ -59,11 +71,49 @@ __device__ __forceinline__ void gather_meta(const RingView &rv, const GatherArgs
         for (int a = 0; a < rv.nA; ++a) ga.q_tpn[(long long)b * rv.nA + a] = rv.q_tpn[slot * rv.nA + a];
 }
 
-// ---- variant 0: one warp per frame, 16-byte vectors, all loads of a frame in
-// flight before the first store (UNROLL x 512 B per warp per round).
+__device__ __forceinline__ void gather_meta(const RingView &rv, const GatherArgs &ga, int b, int count, int32_t *status) {
+    if (b >= count) return;
+    long long slot = ga.idx[b];
+    if (slot < 0 || slot >= rv.N) { atomicOr(status, APEXB200_ST_BAD_INDEX); return; }
+    copy_meta_row(rv, ga, b, slot);
+}
+
+// One frame through shared memory with the TMA (bulk async-copy) engine: global -> shared
+// completes on an mbarrier, shared -> global drains it; the bytes never enter registers.
+// Frame reads are single-use (evict_first) so that they do not push the sum tree or the
+// freshly written batch out of L2.
+__device__ __forceinline__ void tma_load_frame(const uint8_t *src, uint8_t *stage, unsigned long long *bar, unsigned bytes) {
+    const unsigned bar_s = (unsigned)__cvta_generic_to_shared(bar);
+    const unsigned buf_s = (unsigned)__cvta_generic_to_shared(stage);
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 ::"r"(buf_s), "l"(src), "r"(bytes), "r"(bar_s), "l"(pol) : "memory");
+}
+
+__device__ __forceinline__ void tma_store_frame(uint8_t *dst, uint8_t *stage, unsigned long long *bar, unsigned bytes) {
+    const unsigned bar_s = (unsigned)__cvta_generic_to_shared(bar);
+    const unsigned buf_s = (unsigned)__cvta_generic_to_shared(stage);
+    unsigned done = 0;
+    while (!done) {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n"
+                     " selp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(bar_s) : "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(buf_s), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+// ---- variant 0: one warp per frame, 16-byte vectors, all loads of a frame in flight
+// before the first store.  Kept as the non-TMA comparison point.
 template <int UNROLL>
 __global__ void __launch_bounds__(256)
 gather_vec_kernel(RingView rv, GatherArgs ga, int32_t *status) {
+    pdl_prologue();
     const int lane = threadIdx.x & 31;
     const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     int count = ga.count;
@@ -93,22 +143,24 @@ gather_vec_kernel(RingView rv, GatherArgs ga, int32_t *status) {
     }
 }
 
-// ---- variant 1: TMA bulk copies staged through shared memory.  One lane owns one
-// frame: cp.async.bulk global->shared completes on an mbarrier, then
-// cp.async.bulk shared->global drains it; the bytes never enter registers.
-constexpr int kTmaItemsPerCta = 4;
+// ---- variant 1: TMA.  One lane owns one frame; 2 frames per 32-thread CTA keeps
+// 15 CTAs (30 frames, ~210 KB of staging) resident per SM, so a B=512, C=4 gather
+// (4096 frames) is a single wave on 148 SMs.
+constexpr int kTmaItemsPerCta = 2;
 
 __global__ void __launch_bounds__(32)
 gather_tma_kernel(RingView rv, GatherArgs ga, int32_t *status) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) unsigned long long bars[kTmaItemsPerCta];
+    pdl_prologue();
     const int lane = threadIdx.x;
     int count = ga.count;
     if (ga.count_dev) count = min(count, *ga.count_dev);
     const long long n_items = (long long)count * 2 * rv.C;
+    const long long host_items = (long long)ga.count * 2 * rv.C;
     const long long first = (long long)blockIdx.x * kTmaItemsPerCta;
-    if (first >= (long long)ga.count * 2 * rv.C) {          // trailing CTAs: metadata
-        long long mb = blockIdx.x - ((long long)ga.count * 2 * rv.C + kTmaItemsPerCta - 1) / kTmaItemsPerCta;
+    if (first >= host_items) {                              // trailing CTAs: metadata
+        long long mb = blockIdx.x - (host_items + kTmaItemsPerCta - 1) / kTmaItemsPerCta;
         gather_meta(rv, ga, (int)(mb * 32 + lane), count, status);
         return;
     }
@@ -116,26 +168,70 @@ gather_tma_kernel(RingView rv, GatherArgs ga, int32_t *status) {
         const long long it = first + lane;
         const uint8_t *src; uint8_t *dst;
         if (it < n_items && resolve_item(rv, ga, it, count, &src, &dst, status)) {
-            const unsigned bar = (unsigned)__cvta_generic_to_shared(&bars[lane]);
-            const unsigned buf = (unsigned)__cvta_generic_to_shared(smem + (size_t)lane * rv.F);
-            const unsigned bytes = (unsigned)rv.F;
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
-            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                         ::"r"(buf), "l"(src), "r"(bytes), "r"(bar) : "memory");
-            unsigned done = 0;
-            while (!done) {
-                asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n"
-                             " selp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(bar) : "memory");
-            }
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(buf), "r"(bytes)
-                         : "memory");
-            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            tma_load_frame(src, smem + (size_t)lane * rv.F, &bars[lane], (unsigned)rv.F);
+            tma_store_frame(dst, smem + (size_t)lane * rv.F, &bars[lane], (unsigned)rv.F);
         }
     }
+}
+
+// ---- fused K3 + K4: one 32-thread CTA per draw.  The warp descends the tree, lanes
+// 0..2C-1 read the record's frame slots and each moves one frame with the TMA engine
+// while lanes 16.. copy the metadata row.  2C*F bytes of staging per CTA (56 KB at C=4)
+// -> 4 CTAs per SM, 592 resident draws: a B=512 batch is a single wave.
+__global__ void __launch_bounds__(32)
+sample_gather_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int32_t *ctrl) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ __align__(8) unsigned long long bars[16];
+    pdl_prologue();
+    const int lane = threadIdx.x;
+    const int w = blockIdx.x;
+    const int count = ga.count;
+    const int twoC = 2 * rv.C;
+    const bool strat = (sa.u == nullptr);
+    double uw;
+    if (strat) {
+        const unsigned long long counter = *(volatile unsigned long long *)(ctrl + 4);
+        uw = strat_uniform(sa.seed, counter, w, count);
+        if (sa.u_out && lane == 0) sa.u_out[w] = uw;
+    } else {
+        uw = sa.u[w];
+    }
+    unsigned long long leaf, total;
+    const long long node = warp_descend(tv, 0ull, true, uw, &leaf, &total, ctrl);
+    long long f = -1;
+    if (node >= 0 && lane < twoC) f = rv.fidx[node * twoC + lane];
+    if (lane < twoC && sa.fsel_out) sa.fsel_out[(long long)w * twoC + lane] = (int32_t)f;
+    if (lane == 0) {
+        sa.idx_out[w] = (int32_t)node;
+        if (sa.leaf_out) sa.leaf_out[w] = node >= 0 ? leaf : 0ull;
+        if (sa.total_out && w == 0) *sa.total_out = total;
+    }
+    bool moving = false;
+    if (node >= 0 && lane < twoC) {
+        if (f < 0 || f >= rv.N * rv.fpr) atomicOr(ctrl, APEXB200_ST_BAD_INDEX);
+        else { moving = true; tma_load_frame(rv.frames + f * rv.F, smem + (size_t)lane * rv.F, &bars[lane], (unsigned)rv.F); }
+    }
+    if (node >= 0 && lane == 16) copy_meta_row(rv, ga, w, node);        // overlaps the frame loads
+    if (moving) tma_store_frame(item_dst(rv, ga, w, lane), smem + (size_t)lane * rv.F, &bars[lane], (unsigned)rv.F);
+    if (strat && lane == 0) {
+        // the last CTA to finish (every CTA has read the counter by then) advances it
+        __threadfence();
+        unsigned int t = atomicAdd((unsigned int *)(ctrl + 2), 1u);
+        if (t == (unsigned int)count - 1u) {
+            *(volatile unsigned long long *)(ctrl + 4) += 1ull;
+            *(volatile unsigned int *)(ctrl + 2) = 0u;
+        }
+    }
+}
+
+static int ensure_smem(const void *fn, size_t smem, int device) {
+    static size_t configured[2][64] = {};
+    const int which = (fn == (const void *)gather_tma_kernel) ? 0 : 1;
+    if (smem > 48 * 1024 && device >= 0 && device < 64 && smem > configured[which][device]) {
+        APEX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[which][device] = smem;
+    }
+    return APEXB200_OK;
 }
 
 }  // namespace apexb200
@@ -163,22 +259,45 @@ int apexb200_gather(apexb200_replay_t h, const int32_t *idx, const int32_t *fsel
     cudaStream_t st = (cudaStream_t)stream;
     const long long items = (long long)count * 2 * rv.C;
     const long long meta_warps = (count + 31) / 32;
-    if (g_gather_variant == 1) {
-        const size_t smem = (size_t)kTmaItemsPerCta * rv.F;
-        APEX_REQUIRE(smem <= 200 * 1024, APEXB200_ERANGE, "gather: frame too large for the TMA variant");
-        static size_t configured = 0;
-        if (smem > 48 * 1024 && smem > configured) {
-            APEX_CUDA(cudaFuncSetAttribute(gather_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            configured = smem;
-        }
+    const size_t smem = (size_t)kTmaItemsPerCta * rv.F;
+    if (g_gather_variant == 1 && smem <= 200 * 1024) {
+        int rc = ensure_smem((const void *)gather_tma_kernel, smem, h->cfg.device);
+        if (rc) return rc;
         const long long blocks = (items + kTmaItemsPerCta - 1) / kTmaItemsPerCta + meta_warps;
-        gather_tma_kernel<<<(unsigned)blocks, 32, smem, st>>>(rv, ga, h->status);
-        return launch_check("gather_tma_kernel");
+        return launch_step("gather_tma_kernel", gather_tma_kernel, dim3((unsigned)blocks), dim3(32), smem, st, rv, ga,
+                           h->status);
     }
     const long long warps = items + meta_warps;
-    const long long blocks = (warps + 7) / 8;
-    gather_vec_kernel<14><<<(unsigned)blocks, 256, 0, st>>>(rv, ga, h->status);
-    return launch_check("gather_vec_kernel");
+    return launch_step("gather_vec_kernel", gather_vec_kernel<14>, dim3((unsigned)((warps + 7) / 8)), dim3(256), 0, st,
+                       rv, ga, h->status);
+}
+
+int apexb200_sample_gather(apexb200_replay_t h, const double *u, uint64_t seed, int32_t count, int32_t *idx_out,
+                           int32_t *fsel_out, uint64_t *leaf_out, uint64_t *total_out, double *u_out, uint8_t *S_t,
+                           uint8_t *S_tpn, int32_t *A, float *R, float *Gamma, float *q_t, float *q_tpn,
+                           void *stream) {
+    APEX_REQUIRE(h && count >= 0, APEXB200_EINVAL, "sample_gather: bad argument");
+    if (count == 0) return APEXB200_OK;
+    APEX_REQUIRE(idx_out && S_t && S_tpn, APEXB200_EINVAL, "sample_gather: null idx_out/S_t/S_tpn");
+    APEX_REQUIRE((((uintptr_t)S_t | (uintptr_t)S_tpn) & 15) == 0, APEXB200_EINVAL,
+                 "sample_gather: output batches must be 16-byte aligned");
+    const RingView &rv = h->ring;
+    const size_t smem = (size_t)2 * rv.C * rv.F;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (2 * rv.C > 16 || smem > 200 * 1024) {
+        // staging for one record does not fit one CTA: run the two kernels back to back
+        int rc = u ? apexb200_sample(h, u, count, idx_out, leaf_out, total_out, fsel_out, stream)
+                   : apexb200_sample_stratified(h, seed, count, idx_out, leaf_out, total_out, fsel_out, u_out, stream);
+        if (rc) return rc;
+        return apexb200_gather(h, idx_out, fsel_out, count, nullptr, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, stream);
+    }
+    int rc = ensure_smem((const void *)sample_gather_kernel, smem, h->cfg.device);
+    if (rc) return rc;
+    SampleArgs sa{u, (unsigned long long)seed, idx_out, fsel_out, (unsigned long long *)leaf_out,
+                  (unsigned long long *)total_out, u_out};
+    GatherArgs ga{idx_out, fsel_out, nullptr, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, count};
+    return launch_step("sample_gather_kernel", sample_gather_kernel, dim3((unsigned)count), dim3(32), smem, st, h->tree,
+                       rv, sa, ga, h->status);
 }
 
 }  // extern "C"

@@ -9,6 +9,7 @@
 namespace apexb200 {
 
 static thread_local char g_err[512] = "";
+int g_pdl = 1;
 
 void set_error(const char *fmt, ...) {
     va_list ap;
@@ -113,6 +114,11 @@ const char *apexb200_strerror(int code) {
 }
 
 const char *apexb200_last_error(void) { return g_err; }
+
+int apexb200_set_pdl(int32_t enabled) {
+    g_pdl = enabled ? 1 : 0;
+    return APEXB200_OK;
+}
 
 int apexb200_replay_create(apexb200_replay_t *out, const apexb200_replay_config *cfg) {
     APEX_REQUIRE(out && cfg, APEXB200_EINVAL, "replay_create: null argument");

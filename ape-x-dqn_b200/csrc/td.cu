@@ -9,7 +9,7 @@ namespace apexb200 {
 int run_tree_update(apexb200_replay *h, const int32_t *idx, const void *values, int mode, int count,
                     const int32_t *count_dev, float eps, cudaStream_t st);
 int run_tree_apply(apexb200_replay *h, const int32_t *idx, const void *values, int mode, int count,
-                   cudaStream_t st);
+                   const int32_t *count_dev, cudaStream_t st);
 
 struct TdArgs {
     const float *q_on_t, *q_on_tpn, *q_tg_tpn;
@@ -18,7 +18,12 @@ struct TdArgs {
     float *delta, *prio, *loss, *loss_mean;
     int B, nA, loss_kind;
     float alpha, eps, kappa;
+    const int32_t *count_dev;       // nullable: live rows = min(B, *count_dev) (sharded batches)
+    float divisor;                  // loss_mean = sum / divisor (0 -> B); global batch size when sharded
 };
+
+__device__ __forceinline__ int live_rows(const TdArgs &a) { return a.count_dev ? min(a.B, *a.count_dev) : a.B; }
+__device__ __forceinline__ float mean_div(const TdArgs &a) { return a.divisor > 0.0f ? a.divisor : (float)a.B; }
 
 // learner.py:43-50 for one record.  Explicit _rn intrinsics keep the compiler from
 // contracting R + Gamma*q into an FMA, so delta/loss equal a plain fp32 evaluation.
@@ -64,28 +69,45 @@ __device__ __forceinline__ float block_sum_fixed(float v, float *warp_part) {
 }
 
 // ---- B <= 1024: one CTA, no scratch; optionally also the priority write-back.
+// Duplicate record indices must resolve as "last row wins" (replay.py:40).  Stratified
+// draws give non-decreasing indices, so duplicates are adjacent and the last of a run
+// wins without any atomics; an unsorted batch falls back to the stamp protocol of K2.
+// The old leaf is fetched up front, in parallel with the Q rows, to keep the chain of
+// dependent memory round trips at two.
 __global__ void __launch_bounds__(1024)
 td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t *__restrict__ stamp,
                 int32_t *status) {
     __shared__ float warp_part[32];
+    pdl_prologue();
     const int b = threadIdx.x;
+    const int live = live_rows(a);
     float l = 0.0f;
     long long i = -1;
-    if (b < a.B) {
-        td_one(a, b, &l);
+    bool in_order = true, last_of_run = true;
+    unsigned long long old = 0ull;
+    if (b < live) {
         if (idx != nullptr) {
             i = idx[b];
+            const long long nxt = (b + 1 < live) ? (long long)idx[b + 1] : (1ll << 40);
+            in_order = i <= nxt;
+            last_of_run = i != nxt;
             if (i < 0 || i >= tv.size[0]) { atomicOr(status, APEXB200_ST_BAD_INDEX); i = -1; }
-            else atomicMax(stamp + i, (uint32_t)b + 1u);
+            else old = tv.lvl[0][i];
         }
+        td_one(a, b, &l);
     }
-    float s = block_sum_fixed(l, warp_part);                // contains the __syncthreads that orders the stamps
-    if (threadIdx.x == 0) *a.loss_mean = s / (float)a.B;
-    if (i < 0) return;
-    if (__ldcg(stamp + i) != (uint32_t)b + 1u) return;      // a later duplicate wins (replay.py:40)
-    stamp[i] = 0u;
+    const int sorted = __syncthreads_and(in_order);
+    bool winner = (i >= 0) && last_of_run;
+    if (!sorted) {
+        if (i >= 0) atomicMax(stamp + i, (uint32_t)b + 1u);
+        __syncthreads();
+        winner = false;
+        if (i >= 0 && __ldcg(stamp + i) == (uint32_t)b + 1u) { winner = true; stamp[i] = 0u; }
+    }
+    float s = block_sum_fixed(l, warp_part);
+    if (threadIdx.x == 0) *a.loss_mean = s / mean_div(a);
+    if (!winner) return;
     unsigned long long nl = leaf_from_prio(a.prio[b]);
-    unsigned long long old = tv.lvl[0][i];
     tv.lvl[0][i] = nl;
     unsigned long long d = nl - old;
     if (d != 0ull) propagate_delta(tv, i, d);
@@ -99,9 +121,10 @@ td_multi_kernel(TdArgs a, const int32_t *__restrict__ idx, uint32_t *__restrict_
                 int32_t *status, unsigned int *__restrict__ ticket, float *__restrict__ partials) {
     __shared__ float warp_part[8];
     __shared__ bool is_last;
+    pdl_prologue();
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     float l = 0.0f;
-    if (b < a.B) {
+    if (b < live_rows(a)) {
         td_one(a, b, &l);
         if (idx != nullptr) {
             long long i = idx[b];
@@ -121,21 +144,24 @@ td_multi_kernel(TdArgs a, const int32_t *__restrict__ idx, uint32_t *__restrict_
         __threadfence();
         float tot = 0.0f;
         for (unsigned k = 0; k < gridDim.x; ++k) tot += __ldcg(partials + k);
-        *a.loss_mean = tot / (float)a.B;
+        *a.loss_mean = tot / mean_div(a);
     }
 }
 
 __global__ void __launch_bounds__(256)
 td_bwd_kernel(const float *__restrict__ delta, const int32_t *__restrict__ A, const float *__restrict__ grad_out,
-              int B, int nA, int loss_kind, float kappa, float *__restrict__ grad_q) {
+              int B, int nA, int loss_kind, float kappa, const int32_t *__restrict__ count_dev, float divisor,
+              float *__restrict__ grad_q) {
+    pdl_prologue();
     long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= (long long)B * nA) return;
     int b = (int)(e / nA), k = (int)(e - (long long)b * nA);
+    const int live = count_dev ? min(B, *count_dev) : B;
     float g = 0.0f;
-    if (k == A[b]) {
+    if (b < live && k == A[b]) {
         float d = delta[b];
         if (loss_kind == APEXB200_LOSS_HUBER) d = fminf(fmaxf(d, -kappa), kappa);
-        g = -d * (*grad_out) / (float)B;                    // d(mean loss)/dQ(S_t)[b, A_b]
+        g = -d * (*grad_out) / (divisor > 0.0f ? divisor : (float)B);   // d(mean loss)/dQ(S_t)[b, A_b]
     }
     grad_q[e] = g;
 }
@@ -194,9 +220,9 @@ static int td_launch(apexb200_replay *h, const int32_t *idx, const TdArgs &a, vo
                      cudaStream_t st) {
     TreeView tv_none{};
     if (a.B <= 1024) {
-        td_small_kernel<<<1, ((a.B + 31) / 32) * 32, 0, st>>>(a, h ? h->tree : tv_none, idx, h ? h->stamp : nullptr,
-                                                             h ? h->status : nullptr);
-        return launch_check("td_small_kernel");
+        return launch_step("td_small_kernel", td_small_kernel, dim3(1), dim3(((a.B + 31) / 32) * 32), 0, st, a,
+                           h ? h->tree : tv_none, idx, h ? h->stamp : (uint32_t *)nullptr,
+                           h ? h->status : (int32_t *)nullptr);
     }
     APEX_REQUIRE(workspace && ws_bytes >= td_ws_bytes(a.B), APEXB200_EINVAL,
                  "td_fwd: B=%d needs %lld bytes of workspace (got %lld)", a.B, (long long)td_ws_bytes(a.B),
@@ -204,12 +230,12 @@ static int td_launch(apexb200_replay *h, const int32_t *idx, const TdArgs &a, vo
     APEX_REQUIRE(((uintptr_t)workspace & 255) == 0, APEXB200_EINVAL, "td_fwd: workspace must be 256-byte aligned");
     APEX_CUDA(cudaMemsetAsync(workspace, 0, 256, st));
     const int blocks = (a.B + 255) / 256;
-    td_multi_kernel<<<blocks, 256, 0, st>>>(a, idx, h ? h->stamp : nullptr, h ? h->ring.N : 0,
-                                            h ? h->status : nullptr, (unsigned int *)workspace,
-                                            (float *)((char *)workspace + 256));
-    int rc = launch_check("td_multi_kernel");
+    int rc = launch_step("td_multi_kernel", td_multi_kernel, dim3(blocks), dim3(256), 0, st, a, idx,
+                         h ? h->stamp : (uint32_t *)nullptr, h ? (long long)h->ring.N : 0ll,
+                         h ? h->status : (int32_t *)nullptr, (unsigned int *)workspace,
+                         (float *)((char *)workspace + 256));
     if (rc || !h) return rc;
-    return run_tree_apply(h, idx, a.prio, 2, a.B, st);            // stamps were taken inside td_multi_kernel
+    return run_tree_apply(h, idx, a.prio, 2, a.B, a.count_dev, st);   // stamps were taken inside td_multi_kernel
 }
 
 }  // namespace apexb200
@@ -231,7 +257,7 @@ int apexb200_td_fwd(const float *q_on_t, const float *q_on_tpn, const float *q_t
     int rc = td_check(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, B, num_actions, delta, prio, loss, loss_mean);
     if (rc) return rc;
     TdArgs a{q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, delta, prio, loss, loss_mean, B, num_actions, loss_kind,
-             alpha, eps, kappa};
+             alpha, eps, kappa, nullptr, 0.0f};
     return td_launch(nullptr, nullptr, a, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
@@ -239,23 +265,24 @@ int apexb200_td_fwd_update(apexb200_replay_t h, const int32_t *idx, const float 
                            const float *q_tg_tpn, const int32_t *A, const float *R, const float *Gamma, int32_t B,
                            int32_t num_actions, float eps, int32_t loss_kind, float kappa, float *delta,
                            float *prio, float *loss, float *loss_mean, void *workspace, int64_t workspace_bytes,
-                           void *stream) {
+                           const int32_t *count_dev, float mean_divisor, void *stream) {
     APEX_REQUIRE(h && idx, APEXB200_EINVAL, "td_fwd_update: null handle/idx");
     int rc = td_check(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, B, num_actions, delta, prio, loss, loss_mean);
     if (rc) return rc;
     TdArgs a{q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, delta, prio, loss, loss_mean, B, num_actions, loss_kind,
-             h->ring.alpha, eps, kappa};
+             h->ring.alpha, eps, kappa, count_dev, mean_divisor};
     return td_launch(h, idx, a, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 int apexb200_td_bwd(const float *delta, const int32_t *A, const float *grad_loss_mean, int32_t B,
-                    int32_t num_actions, int32_t loss_kind, float kappa, float *grad_q, void *stream) {
+                    int32_t num_actions, int32_t loss_kind, float kappa, const int32_t *count_dev,
+                    float mean_divisor, float *grad_q, void *stream) {
     APEX_REQUIRE(delta && A && grad_loss_mean && grad_q && B > 0 && num_actions >= 1, APEXB200_EINVAL,
                  "td_bwd: bad argument");
     long long n = (long long)B * num_actions;
-    td_bwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(delta, A, grad_loss_mean, B,
-                                                                                 num_actions, loss_kind, kappa, grad_q);
-    return launch_check("td_bwd_kernel");
+    return launch_step("td_bwd_kernel", td_bwd_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0,
+                       (cudaStream_t)stream, delta, A, grad_loss_mean, B, num_actions, loss_kind, kappa, count_dev,
+                       mean_divisor, grad_q);
 }
 
 int apexb200_nstep(const float *rewards, const uint8_t *dones, int32_t E, int32_t T, int32_t n, float gamma,

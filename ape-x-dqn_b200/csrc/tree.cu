@@ -29,6 +29,7 @@ tree_build_level_kernel(const unsigned long long *__restrict__ child, unsigned l
 __global__ void __launch_bounds__(256)
 tree_stamp_kernel(const int32_t *__restrict__ idx, int count, const int32_t *__restrict__ count_dev,
                   uint32_t *__restrict__ stamp, long long N, int32_t *status) {
+    pdl_prologue();
     int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (count_dev) count = min(count, *count_dev);
     if (j >= count) return;
@@ -52,6 +53,7 @@ __global__ void __launch_bounds__(256)
 tree_apply_kernel(TreeView tv, const int32_t *__restrict__ idx, const void *__restrict__ values, int mode,
                   int count, const int32_t *__restrict__ count_dev, uint32_t *__restrict__ stamp,
                   float alpha, float eps) {
+    pdl_prologue();
     int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (count_dev) count = min(count, *count_dev);
     if (j >= count) return;
@@ -70,6 +72,7 @@ tree_apply_kernel(TreeView tv, const int32_t *__restrict__ idx, const void *__re
 __global__ void __launch_bounds__(1024)
 tree_update_small_kernel(TreeView tv, const int32_t *__restrict__ idx, const void *__restrict__ values, int mode,
                          int count, uint32_t *__restrict__ stamp, float alpha, float eps, int32_t *status) {
+    pdl_prologue();
     int j = threadIdx.x;
     long long i = -1;
     if (j < count) {
@@ -89,6 +92,7 @@ tree_update_small_kernel(TreeView tv, const int32_t *__restrict__ idx, const voi
 }
 
 __global__ void tree_total_kernel(TreeView tv, unsigned long long *out) {
+    pdl_prologue();
     int lane = threadIdx.x;
     const int top = tv.n_levels - 1;
     unsigned long long v = lane < tv.size[top] ? tv.lvl[top][lane] : 0ull;
@@ -98,61 +102,7 @@ __global__ void tree_total_kernel(TreeView tv, unsigned long long *out) {
 }
 
 // ---------------------------------------------------------------------------
-// K3.  One warp per draw.  At each level the warp loads the 32 children of the
-// current node (one 256-byte line pair), forms their inclusive prefix sums with
-// shuffles, and the number of prefixes <= target is the child to enter — exactly
-// searchsorted(cumsum, target, side='right') restricted to that node.  The chosen
-// child and the remaining target are broadcast by shuffle; no shared memory.
-__device__ __forceinline__ long long warp_descend(const TreeView &tv, unsigned long long t, bool from_u, double u,
-                                                  unsigned long long *leaf, unsigned long long *total,
-                                                  int32_t *status, bool check_target) {
-    const int lane = threadIdx.x & 31;
-    const int top = tv.n_levels - 1;
-    long long node = 0;
-    unsigned long long lf = 0ull;
-    for (int l = top; l >= 0; --l) {
-        unsigned long long v = tv.lvl[l][node * kFanout + lane];        // padded levels: always in bounds
-        unsigned long long incl = v;
-        #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            unsigned long long n = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += n;
-        }
-        if (l == top) {
-            unsigned long long tot = __shfl_sync(0xffffffffu, incl, 31);
-            *total = tot;
-            if (tot == 0ull) { if (lane == 0) atomicOr(status, APEXB200_ST_EMPTY_TREE); return -1; }
-            if (from_u) {
-                t = (unsigned long long)(u * (double)tot);              // one fp64 multiply, truncation
-                if (t >= tot) t = tot - 1ull;
-            } else if (t >= tot) {
-                if (check_target && lane == 0) atomicOr(status, APEXB200_ST_BAD_TARGET);
-                t = tot - 1ull;
-            }
-        }
-        int c = __popc(__ballot_sync(0xffffffffu, incl <= t));
-        c = min(c, 31);
-        unsigned long long excl = __shfl_sync(0xffffffffu, incl - v, c);
-        if (l == 0) lf = __shfl_sync(0xffffffffu, v, c);
-        t -= excl;
-        node = node * kFanout + c;
-    }
-    *leaf = lf;
-    return node;
-}
-
-// Counter-based uniform for the in-kernel stratified draws: splitmix64 finaliser over
-// (seed, call counter, draw position) -> 53 random bits -> [0,1).
-__device__ __forceinline__ double strat_uniform(unsigned long long seed, unsigned long long counter, int j, int count) {
-    unsigned long long z = seed ^ (counter * 0xD1342543DE82EF95ull);
-    z += (unsigned long long)(j + 1) * 0x9E3779B97F4A7C15ull;
-    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-    z ^= z >> 31;
-    const double v = (double)(z >> 11) * 0x1.0p-53;
-    return ((double)j + v) / (double)count;                 // u_j = (j + v_j) / B
-}
-
+// K3 (the descent itself, warp_descend, lives in common.cuh and is shared with the fused kernel).
 // Draw source: u != null -> caller's uniforms; targets != null -> explicit integer targets;
 // neither -> stratified draws generated here from (seed, device call counter).
 __global__ void __launch_bounds__(128)
@@ -161,6 +111,7 @@ tree_sample_kernel(TreeView tv, const double *__restrict__ u, const unsigned lon
                    unsigned long long *__restrict__ leaf_out, unsigned long long *__restrict__ total_out,
                    const int32_t *__restrict__ fidx, int twoC, int32_t *__restrict__ fsel_out, int32_t *ctrl,
                    unsigned long long seed, double *__restrict__ u_out) {
+    pdl_prologue();
     int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     int lane = threadIdx.x & 31;
     if (count_dev) count = min(count, *count_dev);
@@ -176,7 +127,7 @@ tree_sample_kernel(TreeView tv, const double *__restrict__ u, const unsigned lon
     } else if (u != nullptr) {
         uw = u[w];
     }
-    long long node = warp_descend(tv, from_u ? 0ull : targets[w], from_u, uw, &leaf, &total, ctrl, true);
+    long long node = warp_descend(tv, from_u ? 0ull : targets[w], from_u, uw, &leaf, &total, ctrl);
     if (lane == 0) {
         idx_out[w] = (int32_t)node;
         if (leaf_out) leaf_out[w] = node >= 0 ? leaf : 0ull;
@@ -202,6 +153,7 @@ __global__ void __launch_bounds__(1024)
 shard_targets_kernel(const unsigned long long *__restrict__ totals, int G, int rank,
                      const double *__restrict__ u, int count, unsigned long long *__restrict__ local_targets,
                      int32_t *__restrict__ local_pos, int32_t *__restrict__ local_count) {
+    pdl_prologue();
     __shared__ int warp_sums[32];
     __shared__ int running;
     unsigned long long T = 0ull, lo = 0ull, hi = 0ull;
@@ -245,10 +197,9 @@ shard_targets_kernel(const unsigned long long *__restrict__ totals, int G, int r
 
 // Phase 2 alone, for callers that stamped inside their own kernel (td.cu).
 int run_tree_apply(apexb200_replay *h, const int32_t *idx, const void *values, int mode, int count,
-                   cudaStream_t st) {
-    tree_apply_kernel<<<(count + 255) / 256, 256, 0, st>>>(h->tree, idx, values, mode, count, nullptr, h->stamp,
-                                                           h->ring.alpha, 0.0f);
-    return launch_check("tree_apply_kernel");
+                   const int32_t *count_dev, cudaStream_t st) {
+    return launch_step("tree_apply_kernel", tree_apply_kernel, dim3((count + 255) / 256), dim3(256), 0, st, h->tree, idx,
+                       values, mode, count, count_dev, h->stamp, h->ring.alpha, 0.0f);
 }
 
 // Shared by tree.cu and td.cu: run K2 over (idx, values).
@@ -256,17 +207,15 @@ int run_tree_update(apexb200_replay *h, const int32_t *idx, const void *values, 
                     const int32_t *count_dev, float eps, cudaStream_t st) {
     if (count <= 0) return APEXB200_OK;
     if (count <= 1024 && count_dev == nullptr) {
-        tree_update_small_kernel<<<1, ((count + 31) / 32) * 32, 0, st>>>(h->tree, idx, values, mode, count, h->stamp,
-                                                                         h->ring.alpha, eps, h->status);
-        return launch_check("tree_update_small_kernel");
+        return launch_step("tree_update_small_kernel", tree_update_small_kernel, dim3(1), dim3(((count + 31) / 32) * 32),
+                           0, st, h->tree, idx, values, mode, count, h->stamp, h->ring.alpha, eps, h->status);
     }
     const int blocks = (count + 255) / 256;
-    tree_stamp_kernel<<<blocks, 256, 0, st>>>(idx, count, count_dev, h->stamp, h->ring.N, h->status);
-    int rc = launch_check("tree_stamp_kernel");
+    int rc = launch_step("tree_stamp_kernel", tree_stamp_kernel, dim3(blocks), dim3(256), 0, st, idx, count, count_dev,
+                         h->stamp, (long long)h->ring.N, h->status);
     if (rc) return rc;
-    tree_apply_kernel<<<blocks, 256, 0, st>>>(h->tree, idx, values, mode, count, count_dev, h->stamp,
-                                              h->ring.alpha, eps);
-    return launch_check("tree_apply_kernel");
+    return launch_step("tree_apply_kernel", tree_apply_kernel, dim3(blocks), dim3(256), 0, st, h->tree, idx, values, mode,
+                       count, count_dev, h->stamp, h->ring.alpha, eps);
 }
 
 }  // namespace apexb200
@@ -305,8 +254,8 @@ int apexb200_tree_set_leaves(apexb200_replay_t h, const int32_t *idx, const uint
 
 int apexb200_tree_total(apexb200_replay_t h, uint64_t *total, void *stream) {
     APEX_REQUIRE(h && total, APEXB200_EINVAL, "tree_total: null argument");
-    tree_total_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(h->tree, (unsigned long long *)total);
-    return launch_check("tree_total_kernel");
+    return launch_step("tree_total_kernel", tree_total_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, h->tree,
+                       (unsigned long long *)total);
 }
 
 int apexb200_tree_geometry(apexb200_replay_t h, int32_t *n_levels_host, int64_t *sizes_host) {
@@ -345,10 +294,10 @@ static int launch_sample(apexb200_replay_t h, const double *u, const uint64_t *t
     APEX_REQUIRE(!fsel_out || twoC <= 32, APEXB200_ERANGE, "sample: fsel_out needs 2*frames_per_state <= 32");
     const int warps_per_block = 4;
     const int blocks = (count + warps_per_block - 1) / warps_per_block;
-    tree_sample_kernel<<<blocks, warps_per_block * 32, 0, (cudaStream_t)stream>>>(
-        h->tree, u, (const unsigned long long *)targets, count, count_dev, idx_out, (unsigned long long *)leaf_out,
-        (unsigned long long *)total_out, h->ring.fidx, twoC, fsel_out, h->status, (unsigned long long)seed, u_out);
-    return launch_check("tree_sample_kernel");
+    return launch_step("tree_sample_kernel", tree_sample_kernel, dim3(blocks), dim3(warps_per_block * 32), 0,
+                       (cudaStream_t)stream, h->tree, u, (const unsigned long long *)targets, count, count_dev, idx_out,
+                       (unsigned long long *)leaf_out, (unsigned long long *)total_out, (const int32_t *)h->ring.fidx,
+                       twoC, fsel_out, h->status, (unsigned long long)seed, u_out);
 }
 
 int apexb200_sample(apexb200_replay_t h, const double *u, int32_t count, int32_t *idx_out, uint64_t *leaf_out,
@@ -378,10 +327,9 @@ int apexb200_shard_targets(const uint64_t *totals, int32_t G, int32_t rank, cons
     APEX_REQUIRE(totals && u && local_targets && local_pos && local_count, APEXB200_EINVAL,
                  "shard_targets: null argument");
     APEX_REQUIRE(G >= 1 && rank >= 0 && rank < G && count >= 0, APEXB200_EINVAL, "shard_targets: bad G/rank/count");
-    shard_targets_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>((const unsigned long long *)totals, G, rank, u, count,
-                                                               (unsigned long long *)local_targets, local_pos,
-                                                               local_count);
-    return launch_check("shard_targets_kernel");
+    return launch_step("shard_targets_kernel", shard_targets_kernel, dim3(1), dim3(1024), 0, (cudaStream_t)stream,
+                       (const unsigned long long *)totals, G, rank, u, count, (unsigned long long *)local_targets,
+                       local_pos, local_count);
 }
 
 }  // extern "C"

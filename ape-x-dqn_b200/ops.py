@@ -30,12 +30,13 @@ def td_forward(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, alpha, eps=0.0, loss_kin
     return delta, prio, loss, mean
 
 
-def td_backward(delta, A, grad_loss_mean, num_actions, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0):
+def td_backward(delta, A, grad_loss_mean, num_actions, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0, count_dev=None,
+                mean_divisor=0.0):
     import torch
     B = delta.numel()
     grad_q = torch.empty((B, num_actions), dtype=torch.float32, device=delta.device)
     _C.call("apexb200_td_bwd", _C.ptr(delta), _C.ptr(A), _C.ptr(grad_loss_mean), int(B), int(num_actions),
-            int(loss_kind), float(kappa), _C.ptr(grad_q), _C.stream_ptr())
+            int(loss_kind), float(kappa), _C.ptr(count_dev), float(mean_divisor), _C.ptr(grad_q), _C.stream_ptr())
     return grad_q
 
 

@@ -302,12 +302,23 @@ class ReplayMemory(object):
                 _C.ptr(fsel_out), self._stream())
         return idx_out
 
-    def gather(self, idx, fsel=None, with_q=False, out=None):
-        """K4 only: record indices -> Batch of device tensors."""
+    def sample_targets(self, targets, count_dev, idx_out=None, fsel_out=None, leaf_out=None):
+        """K3 from explicit integer targets (sharded sampling): targets int64-viewed u64 [max], count_dev int32 [1]."""
+        import torch
+        self._ensure()
+        n = int(targets.numel())
+        if idx_out is None:
+            idx_out = torch.empty(n, dtype=torch.int32, device=self.device)
+        _C.call("apexb200_sample_targets", self._h, _C.ptr(targets), _C.ptr(count_dev), n, _C.ptr(idx_out),
+                _C.ptr(leaf_out), _C.ptr(fsel_out), self._stream())
+        return idx_out
+
+    def gather(self, idx, fsel=None, with_q=False, out=None, count_dev=None):
+        """K4 only: record indices -> Batch of device tensors (rows >= *count_dev are left untouched)."""
         self._ensure()
         B = int(idx.numel())
         o = out if out is not None else self._outputs(B, with_q)
-        _C.call("apexb200_gather", self._h, _C.ptr(idx), _C.ptr(fsel), B, None, _C.ptr(o["S_t"]), _C.ptr(o["S_tpn"]),
+        _C.call("apexb200_gather", self._h, _C.ptr(idx), _C.ptr(fsel), B, _C.ptr(count_dev), _C.ptr(o["S_t"]), _C.ptr(o["S_tpn"]),
                 _C.ptr(o["A"]), _C.ptr(o["R"]), _C.ptr(o["Gamma"]), _C.ptr(o.get("q_t")), _C.ptr(o.get("q_tpn")),
                 self._stream())
         self._last_q = (o["q_t"], o["q_tpn"]) if with_q and o.get("q_t") is not None else None
@@ -324,8 +335,9 @@ class ReplayMemory(object):
                 _C.ptr(total_out), _C.ptr(fsel_out), _C.ptr(u_out), self._stream())
         return idx_out
 
-    def sample_tensors(self, batch_size, u=None, with_q=False, u_out=None):
-        """K3 + K4: draw `batch_size` records and gather them into [B, C, F] uint8 batch tensors.
+    def sample_tensors(self, batch_size, u=None, with_q=False, u_out=None, fused=True):
+        """ReplayMemory.sample on the device: draw `batch_size` records and gather them into
+        [B, C, F] uint8 batch tensors (K3 + K4, one fused launch unless fused=False).
 
         u: CUDA float64 uniforms in [0,1); None = stratified draws generated inside the kernel
         (written to u_out if given).  The returned tensors are reused by the next call with the
@@ -334,6 +346,12 @@ class ReplayMemory(object):
         self._ensure()
         B = int(batch_size)
         o = self._outputs(B, with_q)
+        if fused:
+            _C.call("apexb200_sample_gather", self._h, _C.ptr(u), self.seed, B, _C.ptr(o["idx"]), _C.ptr(o["fsel"]),
+                    None, None, _C.ptr(u_out), _C.ptr(o["S_t"]), _C.ptr(o["S_tpn"]), _C.ptr(o["A"]), _C.ptr(o["R"]),
+                    _C.ptr(o["Gamma"]), _C.ptr(o.get("q_t")), _C.ptr(o.get("q_tpn")), self._stream())
+            self._last_q = (o["q_t"], o["q_tpn"]) if with_q and o.get("q_t") is not None else None
+            return Batch(o["idx"], o["S_t"], o["S_tpn"], o["A"], o["R"], o["Gamma"], o["fsel"])
         if u is None:
             self.sample_stratified(B, idx_out=o["idx"], fsel_out=o["fsel"], u_out=u_out)
         else:
@@ -355,8 +373,10 @@ class ReplayMemory(object):
             self._ws = torch.empty(int(n.value), dtype=torch.uint8, device=self.device)
         return self._ws
 
-    def td_update(self, idx, q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0, out=None):
-        """K5 + K2 fused (learner.py:70 + :76): returns (delta, prio, loss, loss_mean) device tensors."""
+    def td_update(self, idx, q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0, out=None,
+                  count_dev=None, mean_divisor=0.0):
+        """K5 + K2 fused (learner.py:70 + :76): returns (delta, prio, loss, loss_mean) device tensors.
+        count_dev / mean_divisor: live-row count on the device and global batch size for sharded batches."""
         import torch
         B, nA = q_on_t.shape
         if out is None:
@@ -366,7 +386,7 @@ class ReplayMemory(object):
         _C.call("apexb200_td_fwd_update", self._h, _C.ptr(idx), _C.ptr(q_on_t), _C.ptr(q_on_tpn), _C.ptr(q_tg_tpn),
                 _C.ptr(A), _C.ptr(R), _C.ptr(Gamma), int(B), int(nA), self.eps, int(loss_kind), float(kappa),
                 _C.ptr(out[0]), _C.ptr(out[1]), _C.ptr(out[2]), _C.ptr(out[3]), _C.ptr(ws), int(ws.numel()),
-                self._stream())
+                _C.ptr(count_dev), float(mean_divisor), self._stream())
         return out
 
     def total(self):

@@ -1,0 +1,410 @@
+#!/usr/bin/env python
+"""Benchmark of the prioritized sample + gather + TD/priority-update loop.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One "step" = one pass of the hot path over one batch of B=512 records on a
+2M-record shard of Atari-shaped (4 x 84 x 84 uint8) synthetic records:
+K3 proportional search -> K4 frame gather -> K5 double-DQN TD/loss/|delta|^alpha
+-> K2 in-place priority write-back.  Prints ONE JSON line.
+Under torchrun every rank owns a 2M shard and the global batch is 512 x N (weak scaling).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+F_BYTES = 7056          # 84 x 84 uint8
+ALPHA = 0.6
+GAMMA_N = 0.99 ** 3
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--capacity", type=int, default=1 << 21)
+    ap.add_argument("--batch", type=int, default=512)
+    ap.add_argument("--frames-per-state", type=int, default=4)
+    ap.add_argument("--actions", type=int, default=4)
+    ap.add_argument("--lanes", type=int, default=32)
+    ap.add_argument("--gather-variant", type=int, default=int(os.environ.get("APEX_GATHER_VARIANT", "0")))
+    ap.add_argument("--no-graph", action="store_true", help="launch every step from Python instead of a CUDA graph")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the CPU-baseline leg")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the GPU is under load."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        rows = [r for r in self.rows if len(r) >= 6 and r[0].isdigit()]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        sm = sorted(int(r[0]) for r in rows)
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": int(rows[0][1]), "reasons": reasons, "samples": len(rows)}
+
+
+def synth_chunk(torch, gen, m, C, nA, dev):
+    """Synthetic Atari-shaped records: incompressible frames, clipped rewards, 1% terminals."""
+    frames = torch.randint(0, 256, (m, F_BYTES), dtype=torch.uint8, device=dev, generator=gen)
+    A = torch.randint(0, nA, (m,), dtype=torch.int32, device=dev, generator=gen)
+    R = torch.randn(m, device=dev, generator=gen).clamp_(-1, 1)
+    G = torch.where(torch.rand(m, device=dev, generator=gen) < 0.01, 0.0, GAMMA_N).float()
+    prio = torch.randn(m, device=dev, generator=gen).abs_() + 1e-3
+    return frames, A, R, G, prio
+
+
+def fill_shard(torch, apex, mem, args, dev, seed):
+    gen = torch.Generator(device=dev).manual_seed(seed)
+    lane_cap = args.capacity // args.lanes
+    chunk = min(8192, lane_cap - (args.frames_per_state - 1 + 3))
+    for lane in range(args.lanes):
+        done = 0
+        while done < lane_cap:
+            m = min(chunk, lane_cap - done)
+            age = (done + np.arange(m)) % 1000                     # episodes of 1000 steps
+            rel = torch.as_tensor(apex.stream_offsets(args.frames_per_state, np.full(m, 3), age)).to(dev)
+            frames, A, R, G, prio = synth_chunk(torch, gen, m, args.frames_per_state, args.actions, dev)
+            mem.insert(lane, frames, rel, A, R, G, prio=prio)
+            done += m
+    torch.cuda.synchronize()
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import apex_b200
+    from apex_b200 import _C
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _C.call("apexb200_set_gather_variant", args.gather_variant)
+    B, C, nA, N = args.batch, args.frames_per_state, args.actions, args.capacity
+    Bg = B * world
+    mem = apex_b200.ReplayMemory(N, {"priority_exponent": ALPHA, "layout": "stream", "lanes": args.lanes, "n_step": 3,
+                                     "state_shape": (C, 84, 84), "seed": 4321})
+    fill_shard(torch, apex_b200, mem, args, dev, 1234 + rank)
+    clocks = ClockSampler(local)
+    clocks.start()
+
+    gen = torch.Generator(device=dev).manual_seed(99 + rank)
+    P = 4                                                         # pool of Q-value inputs, cycled
+    qpool = [[torch.randn(Bg, nA, device=dev, generator=gen) for _ in range(3)] for _ in range(P)]
+    td_out = tuple(torch.empty(Bg, device=dev) for _ in range(3)) + (torch.empty(1, device=dev),)
+    sampler = apex_b200.ShardedSampler(mem, rank=rank, world_size=world) if world > 1 else None
+    ugen = torch.Generator(device=dev).manual_seed(4321)          # same draws on every rank
+    u_table = ((torch.arange(Bg, device=dev, dtype=torch.float64) +
+                torch.rand(64, Bg, device=dev, dtype=torch.float64, generator=ugen)) / Bg) if world > 1 else None
+    step_no = [0]
+
+    def step(k):
+        q = qpool[k % P]
+        if world == 1:
+            b = mem.sample_tensors(B)                             # K3 (in-kernel stratified draws) + K4
+            mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma, out=td_out)      # K5 + K2
+        else:
+            b, _pos, cnt = sampler.sample(u_table[step_no[0] % 64])
+            mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma, out=td_out, count_dev=cnt, mean_divisor=float(Bg))
+            step_no[0] += 1
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    use_graph = (not args.no_graph) and world == 1
+    for k in range(max(args.warmup, 3)):
+        step(k)
+    torch.cuda.synchronize()
+    graph = None
+    if use_graph:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=side):
+                for k in range(P):
+                    step(k)
+        torch.cuda.current_stream().wait_stream(side)
+        for _ in range(3):
+            graph.replay()
+        torch.cuda.synchronize()
+
+    K = args.steps
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    if graph is not None:
+        for _ in range(K // P):
+            graph.replay()
+        for k in range(K % P):
+            step(k)
+    else:
+        for k in range(K):
+            step(k)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    launches_per_step = 3 if world == 1 else 5 + (1 if Bg > 1024 else 0)
+    value = K * Bg / (ms * 1e-3)
+
+    # ---- roofline of the dominant kernel (K4 gather): CUDA events around each launch, eager pass
+    # with the GPU kept busy ahead of the CPU so that intervals are kernel time, not launch gaps.
+    if world == 1:
+        n_r = min(K, 400)
+        o = mem._outputs(B, False)
+        pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_r)]
+        big = torch.zeros(1 << 30, dtype=torch.uint8, device=dev)
+        torch.cuda.synchronize()
+        for _ in range(40):
+            big.add_(1)                                           # ~13 ms of queued GPU work: the CPU runs ahead
+        for k in range(n_r):
+            mem.sample_stratified(B, idx_out=o["idx"], fsel_out=o["fsel"])
+            pairs[k][0].record()
+            mem.gather(o["idx"], fsel=o["fsel"], out=o)
+            pairs[k][1].record()
+            q = qpool[k % P]
+            mem.td_update(o["idx"], q[0], q[1], q[2], o["A"], o["R"], o["Gamma"], out=td_out)
+        torch.cuda.synchronize()
+        g_us = sorted(a.elapsed_time(b) * 1e3 for a, b in pairs)
+        g_mean_us = sum(g_us) / len(g_us)
+        del big
+    else:
+        g_mean_us, g_us = None, []
+    peak, peak_src = peaks()
+    bytes_per_rec = 4 * C * F_BYTES + 32
+    roofline = None
+    if g_mean_us:
+        ach = bytes_per_rec * B / (g_mean_us * 1e-6) / 1e9
+        roofline = {"kernel": "gather_vec_kernel" if args.gather_variant == 0 else "gather_tma_kernel", "bound": "hbm",
+                    "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
+                    "traffic": None, "algorithmic_bytes_per_launch": bytes_per_rec * B,
+                    "launch_us_mean": round(g_mean_us, 3), "launch_us_median": round(g_us[len(g_us) // 2], 3),
+                    "launch_us_min": round(g_us[0], 3), "launches_timed": len(g_us), "peak_source": peak_src}
+
+    # ---- end to end through the public tensor API with HOST inputs and a host-read result
+    e2e = None
+    if world == 1:
+        rng = np.random.default_rng(4321)
+        hu = torch.empty(B, dtype=torch.float64).pin_memory()
+        hq = torch.empty(3, B, nA).pin_memory()
+        hres = torch.empty(1 + 2 * B).pin_memory()                # loss_mean, priorities, indices (as f32 bits)
+        dq = torch.empty(3, B, nA, device=dev)
+        du = torch.empty(B, dtype=torch.float64, device=dev)
+        dres = torch.empty(1 + 2 * B, device=dev)
+        n_e = max(20, min(K, 500))
+        q_host = rng.standard_normal((P, 3, B, nA)).astype(np.float32)
+        t0 = None
+        for k in range(-5, n_e):
+            if k == 0:
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+            hu.numpy()[:] = (np.arange(B) + rng.random(B)) / B    # host-side stratified draws
+            hq.numpy()[:] = q_host[k % P]
+            du.copy_(hu, non_blocking=True)
+            dq.copy_(hq, non_blocking=True)
+            b = mem.sample_tensors(B, u=du)
+            mem.td_update(b.idx, dq[0], dq[1], dq[2], b.A, b.R, b.Gamma, out=td_out)
+            dres[0:1].copy_(td_out[3])
+            dres[1:1 + B].copy_(td_out[1])
+            dres[1 + B:].copy_(b.idx.view(torch.float32))
+            hres.copy_(dres, non_blocking=True)
+            torch.cuda.current_stream().synchronize()             # the host reads the step's result
+            _ = float(hres[0])
+        dt = time.perf_counter() - t0
+        e2e = {"value": round(n_e * B / dt, 1), "unit": "transitions/s", "h2d_bytes_per_step": B * 8 + 3 * B * nA * 4,
+               "d2h_bytes_per_step": 4 * (1 + 2 * B), "steps": n_e, "ms_per_step": round(dt / n_e * 1e3, 4),
+               "api": "ReplayMemory.sample_tensors(u from pinned host) + td_update(Q from pinned host); "
+                      "loss/priorities/indices read back on the host every step"}
+    clk = clocks.stop()
+    mem.check_status()
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline_from_device(torch, mem, args, dev)
+
+    if rank == 0:
+        line = {
+            "metric": "prioritized sample+update transitions/s (2M cap, B=512)", "value": round(value, 1),
+            "unit": "transitions/s", "n_gpus": world, "steps": K, "warmup": max(args.warmup, 3),
+            "ms_per_step": round(ms / K, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8 frames / u64 fixed-point tree / f32 TD", "data": "synthetic",
+            "config": {"workload": "replay microbench: %d-record shard per GPU, batch %d per GPU, C=%d 84x84 uint8, "
+                                   "n=3, alpha=%.1f; sample(K3)+gather(K4)+TD/loss(K5)+priority update(K2) per step"
+                                   % (N, B, C, ALPHA),
+                       "capacity_per_gpu": N, "batch_per_gpu": B, "frames_per_state": C, "lanes": args.lanes,
+                       "launch": "cuda graph of %d steps" % P if graph is not None else "python loop",
+                       "gather_variant": args.gather_variant,
+                       "l2": "frame store %.1f GB >> 126 MB L2 (random gathers miss); the %.1f MB tree is L2-resident by design"
+                             % (N * F_BYTES / 1e9, N * 8 * 33 / 32 / 1e6),
+                       "parallelism": "1 shard per GPU, NCCL all-gather of shard totals" if world > 1 else "single shard"},
+            "gpu_launches": K * launches_per_step, "clocks": clk, "roofline": roofline, "e2e": e2e, "cpu_baseline": cpu,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_baseline_from_device(torch, mem, args, dev):
+    """The C/OpenMP oracle on the host cores, on the SAME shard contents (copied back from HBM)."""
+    from apex_b200 import _C
+    from oracle.c_oracle import CpuReplay
+    from oracle import replay_oracle as ro
+    try:
+        import psutil
+        avail = psutil.virtual_memory().available
+    except Exception:
+        avail = 0
+    N, C, B, nA = args.capacity, args.frames_per_state, args.batch, args.actions
+    need = N * F_BYTES * 1.15
+    if avail and avail < need + (8 << 30):
+        return {"value": None, "unit": "transitions/s", "cores": os.cpu_count(), "kind": "port",
+                "sample": "skipped: host RAM %.0f GB < %.0f GB needed for the frame store" % (avail / 1e9, need / 1e9)}
+    frames = mem.buffer(_C.BUF_FRAMES).cpu().numpy().reshape(-1, F_BYTES)
+    leaves = mem.buffer(_C.BUF_LEAVES).cpu().numpy().view(np.uint64).copy()
+    fidx = mem.buffer(_C.BUF_FIDX).cpu().numpy().reshape(N, 2 * C)
+    A, R, G = (mem.buffer(w).cpu().numpy() for w in (_C.BUF_ACTION, _C.BUF_REWARD, _C.BUF_GAMMA))
+    cpu = CpuReplay(leaves, frames, fidx, A, R, G, C, F_BYTES, ALPHA)
+    rng = np.random.default_rng(7)
+    q = [rng.standard_normal((B, nA)).astype(np.float32) for _ in range(3)]
+    # parity at full size: GPU and CPU draw the same records from the same leaves for the same uniforms
+    u = ro.stratified_uniforms(B, rng)
+    gpu_idx = mem.sample_indices(torch.as_tensor(u).to(dev)).cpu().numpy()
+    torch.cuda.synchronize()
+    parity = bool((gpu_idx == ro.tree_sample(leaves, u)).all())
+    for _ in range(3):
+        cpu.step(ro.stratified_uniforms(B, rng), *q)
+    t0, n = time.perf_counter(), 0
+    while True:
+        cpu.step(ro.stratified_uniforms(B, rng), *q)
+        n += 1
+        dt = time.perf_counter() - t0
+        if dt > args.cpu_seconds or n >= 5000:
+            break
+    return {"value": round(n * B / dt, 1), "unit": "transitions/s", "cores": cpu.threads, "kind": "port",
+            "sample": "%d steps of B=%d on the same %d-record shard (%.1f s), oracle/apex_oracle.c with OpenMP on %d threads; "
+                      "per step: full u64 cumsum + right bisect (np.random.choice law) + frame memcpy + TD + leaf write-back"
+                      % (n, B, N, dt, cpu.threads),
+            "ms_per_step": round(dt / n * 1e3, 4), "index_parity_vs_gpu_at_full_size": parity}
+
+
+def run_reference(args):
+    """CPU arm: the reference's algorithm for the path (oracle port, all host threads); rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    from oracle.c_oracle import CpuReplay
+    from oracle import replay_oracle as ro
+    N, C, B, nA = args.capacity, args.frames_per_state, args.batch, args.actions
+    try:
+        import psutil
+        avail = psutil.virtual_memory().available
+    except Exception:
+        avail = 1 << 62
+    n_cpu = N
+    while n_cpu * F_BYTES * 1.1 + (4 << 30) > avail and n_cpu > 1 << 16:
+        n_cpu //= 2
+    rng = np.random.default_rng(1234)
+    block = rng.integers(0, 256, (1 << 12, F_BYTES), dtype=np.uint8)
+    frames = np.empty((n_cpu, F_BYTES), np.uint8)
+    for lo in range(0, n_cpu, 1 << 12):
+        hi = min(n_cpu, lo + (1 << 12))
+        frames[lo:hi] = block[: hi - lo]
+        frames[lo:hi, 0] = (lo >> 12) & 255
+    lane_cap = n_cpu // args.lanes
+    pos = np.arange(n_cpu) % lane_cap
+    rel = np.concatenate([np.arange(-3 - C + 1, -2), np.arange(-C + 1, 1)])[None, :]
+    fidx = ((np.arange(n_cpu) // lane_cap * lane_cap)[:, None] + (pos[:, None] + rel) % lane_cap).astype(np.int32)
+    A = rng.integers(0, nA, n_cpu).astype(np.int32)
+    R = np.clip(rng.standard_normal(n_cpu), -1, 1).astype(np.float32)
+    G = np.where(rng.random(n_cpu) < 0.01, 0, GAMMA_N).astype(np.float32)
+    leaves = ro.priority_to_leaf(ro.pow_priority(np.abs(rng.standard_normal(n_cpu)) + 1e-3, ALPHA))
+    cpu = CpuReplay(leaves, frames, fidx, A, R, G, C, F_BYTES, ALPHA)
+    q = [[rng.standard_normal((B, nA)).astype(np.float32) for _ in range(3)] for _ in range(4)]
+    W, K = max(args.warmup, 3), args.steps
+    for k in range(W):
+        cpu.step(ro.stratified_uniforms(B, rng), *q[k % 4])
+    us = [ro.stratified_uniforms(B, rng) for _ in range(min(K, 256))]
+    t0 = time.perf_counter()
+    for k in range(K):
+        cpu.step(us[k % len(us)], *q[k % 4])
+    dt = time.perf_counter() - t0
+    value = round(K * B / dt, 1)
+    sample = ("each step = one full B=%d step on a %d-record host-resident shard; oracle/apex_oracle.c "
+              "(reference algorithm restated in C: cumsum + bisect per np.random.choice, frame memcpy, learner.py TD math, "
+              "dict-update write-back) with OpenMP on %d threads" % (B, n_cpu, cpu.threads))
+    print(json.dumps({
+        "impl": "reference", "metric": "prioritized sample+update transitions/s (2M cap, B=512)", "value": value,
+        "unit": "transitions/s", "n_gpus": args.gpus, "steps": K, "warmup": W, "ms_per_step": round(dt / K * 1e3, 5),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8 frames / u64 tree / f32 TD",
+        "data": "synthetic",
+        "config": {"workload": "replay microbench: %d-record shard, batch %d, C=%d 84x84 uint8 (CPU, host RAM)" % (n_cpu, B, C),
+                   "capacity_per_gpu": n_cpu, "batch_per_gpu": B, "frames_per_state": C},
+        "cpu_baseline": {"value": value, "unit": "transitions/s", "cores": cpu.threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "transitions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -167,8 +167,22 @@ int apexb200_sample_targets(apexb200_replay_t h, const uint64_t *targets, const 
 int apexb200_gather(apexb200_replay_t h, const int32_t *idx, const int32_t *fsel, int32_t count,
                     const int32_t *count_dev, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R,
                     float *Gamma, float *q_t, float *q_tpn, void *stream);
-/* 0 = per-warp 16-byte vector copy, 1 = TMA bulk copy staged through shared memory. */
+/* 0 = per-warp 16-byte vector copy, 1 (default) = TMA bulk copy staged through shared memory. */
 int apexb200_set_gather_variant(int32_t variant);
+/* K3 + K4 in one launch: ReplayMemory.sample (replay.py:44-57) as a whole.  u [count]
+ * as in apexb200_sample, or NULL for the in-kernel stratified draws of
+ * apexb200_sample_stratified (seed, u_out).  One CTA per draw: the warp descends the
+ * tree, then moves the record's 2C frames with the TMA engine.  Outputs as in
+ * apexb200_sample + apexb200_gather (fsel_out, leaf_out, total_out, u_out, A, R, Gamma,
+ * q_t, q_tpn nullable). */
+int apexb200_sample_gather(apexb200_replay_t h, const double *u, uint64_t seed, int32_t count,
+                           int32_t *idx_out, int32_t *fsel_out, uint64_t *leaf_out, uint64_t *total_out,
+                           double *u_out, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R, float *Gamma,
+                           float *q_t, float *q_tpn, void *stream);
+/* Programmatic dependent launch for the per-step kernels (default 1): each kernel is
+ * scheduled while its predecessor on the stream drains and blocks on
+ * griddepcontrol.wait before touching memory.  0 = plain stream-ordered launches. */
+int apexb200_set_pdl(int32_t enabled);
 
 /* ---- K5 loss / TD / priority: Learner.compute_loss_and_priorities
  * (learner.py:43-52) ---------------------------------------------------------
@@ -184,17 +198,24 @@ int apexb200_td_fwd(const float *q_on_t, const float *q_on_tpn, const float *q_t
                     float *delta, float *prio, float *loss, float *loss_mean,
                     void *workspace, int64_t workspace_bytes, void *stream);
 /* Gradient of loss_mean w.r.t. q_on_t (loss.backward() through learner.py:46-48):
- * grad_q [B, num_actions], zero except column A_b. grad_loss_mean: device scalar. */
+ * grad_q [B, num_actions], zero except column A_b. grad_loss_mean: device scalar.
+ * count_dev / mean_divisor as in td_fwd_update (NULL / 0 for a plain batch). */
 int apexb200_td_bwd(const float *delta, const int32_t *A, const float *grad_loss_mean, int32_t B,
-                    int32_t num_actions, int32_t loss_kind, float kappa, float *grad_q, void *stream);
+                    int32_t num_actions, int32_t loss_kind, float kappa, const int32_t *count_dev,
+                    float mean_divisor, float *grad_q, void *stream);
 /* K5 + K2 fused: td_fwd, then the new priorities are written into the leaves of
- * idx [B] and their ancestors refreshed (learner.py:70 + :76 in one call). */
+ * idx [B] and their ancestors refreshed (learner.py:70 + :76 in one call).
+ * Sharded batches: count_dev (nullable) is a device int32 with the
+ * number of live rows <= B (the rank's data-dependent quota; rows beyond it are
+ * ignored) and mean_divisor (0 = B) is the GLOBAL batch size, so that summing
+ * loss_mean / gradients over ranks gives the single-batch mean. */
 int apexb200_td_fwd_update(apexb200_replay_t h, const int32_t *idx,
                            const float *q_on_t, const float *q_on_tpn, const float *q_tg_tpn,
                            const int32_t *A, const float *R, const float *Gamma, int32_t B,
                            int32_t num_actions, float eps, int32_t loss_kind, float kappa,
                            float *delta, float *prio, float *loss, float *loss_mean,
-                           void *workspace, int64_t workspace_bytes, void *stream);
+                           void *workspace, int64_t workspace_bytes,
+                           const int32_t *count_dev, float mean_divisor, void *stream);
 
 /* ---- K7 n-step return: ExperienceBuffer.update_buffer (actor.py:29-43),
  * intended semantics, vectorised over E actors x T steps --------

@@ -170,6 +170,64 @@ def test_stratified_draws_generated_in_kernel(apex):
     mem.check_status()
 
 
+@pytest.mark.parametrize("pdl", [1, 0])
+def test_step_loop_in_cuda_graph_equals_eager(apex, pdl):
+    """sample+gather -> TD+update chained on one stream, eager vs replayed from a CUDA graph:
+    same in-kernel draws (device call counter), same indices, same tree afterwards."""
+    apex._C.call("apexb200_set_pdl", pdl)
+    try:
+        N, C_, F, B, nA, steps = 1 << 15, 4, 7056, 256, 4, 6
+
+        def build():
+            rng = np.random.default_rng(77)
+            mem = make_mem(apex, N, C=C_, F=F, layout="stream", lanes=4, n=3)
+            for lane in range(4):
+                m = N // 4 - 8
+                mem.insert(lane, rng.integers(0, 256, (m, F), dtype=np.uint8), apex.stream_offsets(C_, np.full(m, 3), np.arange(m)),
+                           rng.integers(0, nA, m).astype(np.int32), rng.standard_normal(m).astype(np.float32),
+                           np.full(m, 0.97, np.float32), prio=(np.abs(rng.standard_normal(m)) + 1e-3).astype(np.float32))
+            return mem
+        torch.manual_seed(5)
+        q = [[torch.randn(B, nA, device="cuda") for _ in range(3)] for _ in range(steps)]
+        out = tuple(torch.empty(B, device="cuda") for _ in range(3)) + (torch.empty(1, device="cuda"),)
+
+        def run(mem, k, log):
+            b = mem.sample_tensors(B)
+            mem.td_update(b.idx, q[k][0], q[k][1], q[k][2], b.A, b.R, b.Gamma, out=out)
+            log[k].copy_(b.idx)
+        eager, graphed = build(), build()
+        log_e = torch.zeros(steps, B, dtype=torch.int32, device="cuda")
+        log_g = torch.zeros_like(log_e)
+        for k in range(steps):
+            run(eager, k, log_e)
+        run(graphed, 0, log_g)                               # warm-up outside capture (allocations)
+        graphed2 = build()
+        graphed2.sample_tensors(B); graphed2.workspace(B)    # allocate outputs before capture
+        # rewind: a fresh handle so that the draw counter starts at zero again
+        graphed2 = build()
+        graphed2._outputs(B, False); graphed2.workspace(B)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(g, stream=side):
+                for k in range(steps // 2):
+                    run(graphed2, k, log_g)
+        torch.cuda.current_stream().wait_stream(side)
+        g.replay()
+        torch.cuda.synchronize()
+        # capture does not execute: the replay is steps 0..2 of the sequence
+        np.testing.assert_array_equal(log_g.cpu().numpy()[: steps // 2], log_e.cpu().numpy()[: steps // 2])
+        ref = build()
+        for k in range(steps // 2):
+            run(ref, k, torch.zeros_like(log_e))
+        for a, b_ in zip(read_levels(apex, graphed2), read_levels(apex, ref)):
+            np.testing.assert_array_equal(a, b_)
+        graphed2.check_status()
+    finally:
+        apex._C.call("apexb200_set_pdl", 1)
+
+
 def test_sample_targets_and_device_count(apex):
     rng = np.random.default_rng(9)
     N = 3000
@@ -239,9 +297,9 @@ def test_stream_insert_and_gather_byte_exact(apex, variant, C_, F):
         for g, w in zip(read_levels(apex, mem), ro.build_levels(leaves)):
             np.testing.assert_array_equal(g, w)
         ring.leaves[:] = leaves
-        for B in (1, 33, 512):
+        for B, fused in ((1, True), (33, False), (512, True), (512, False), (700, True)):
             u = rng.random(B)
-            b = mem.sample_tensors(B, u=dev(u), with_q=True)
+            b = mem.sample_tensors(B, u=dev(u), with_q=True, fused=fused)
             want = ring.sample(u)
             np.testing.assert_array_equal(b.idx.cpu().numpy(), want)
             g = ring.gather(want)
