@@ -95,6 +95,14 @@ __device__ __forceinline__ float prio_pow(float abs_td, float alpha, float eps) 
     return powf(b, alpha);
 }
 
+// Device control block of a handle: int32 words [0] status, [4..5] u64 update epoch.
+__device__ __forceinline__ unsigned long long read_epoch(const int32_t *ctrl) {
+    return *(const volatile unsigned long long *)(ctrl + 4);
+}
+__device__ __forceinline__ void bump_epoch(int32_t *ctrl) {        // one thread of a tree-changing kernel
+    if (blockIdx.x == 0 && threadIdx.x == 0) *(volatile unsigned long long *)(ctrl + 4) += 1ull;
+}
+
 // Add `d` (mod 2^64) to every ancestor of leaf i.  Integer adds commute, so the
 // tree is exact whatever order concurrent updates land in.
 __device__ __forceinline__ void propagate_delta(const TreeView &tv, long long i, unsigned long long d) {
@@ -106,9 +114,14 @@ __device__ __forceinline__ void propagate_delta(const TreeView &tv, long long i,
 }
 
 // Counter-based uniform for the in-kernel stratified draws: splitmix64 finaliser over
-// (seed, call counter, draw position) -> 53 random bits -> [0,1).
-__device__ __forceinline__ double strat_uniform(unsigned long long seed, unsigned long long counter, int j, int count) {
-    unsigned long long z = seed ^ (counter * 0xD1342543DE82EF95ull);
+// (seed, update epoch, host call index, draw position) -> 53 random bits -> [0,1).
+// The update epoch lives on the device and is advanced by every kernel that changes the
+// tree (bump_epoch), so a CUDA-graph replay of a sample -> ... -> update step draws fresh
+// numbers each time without any host-side state; the call index separates several
+// sample calls between two updates.
+__device__ __forceinline__ double strat_uniform(unsigned long long seed, unsigned long long epoch,
+                                                unsigned long long call, int j, int count) {
+    unsigned long long z = seed ^ (epoch * 0xD1342543DE82EF95ull) ^ (call * 0xA24BAED4963EE407ull);
     z += (unsigned long long)(j + 1) * 0x9E3779B97F4A7C15ull;
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
     z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
@@ -122,15 +135,21 @@ __device__ __forceinline__ double strat_uniform(unsigned long long seed, unsigne
 // shuffles, and the number of prefixes <= target is the child to enter — exactly
 // searchsorted(cumsum, target, side='right') restricted to that node.  The chosen
 // child and the remaining target are broadcast by shuffle; no shared memory.
-__device__ __forceinline__ long long warp_descend(const TreeView &tv, unsigned long long t, bool from_u, double u,
-                                                  unsigned long long *leaf, unsigned long long *total,
-                                                  int32_t *status) {
+// The top-level load does not depend on the draw, so callers fetch it first
+// (top_level_value) and compute the draw while it is in flight.
+__device__ __forceinline__ unsigned long long top_level_value(const TreeView &tv) {
+    return tv.lvl[tv.n_levels - 1][threadIdx.x & 31];
+}
+
+__device__ __forceinline__ long long warp_descend(const TreeView &tv, unsigned long long vtop, unsigned long long t,
+                                                  bool from_u, double u, unsigned long long *leaf,
+                                                  unsigned long long *total, int32_t *status) {
     const int lane = threadIdx.x & 31;
     const int top = tv.n_levels - 1;
     long long node = 0;
     unsigned long long lf = 0ull;
     for (int l = top; l >= 0; --l) {
-        unsigned long long v = tv.lvl[l][node * kFanout + lane];        // padded levels: always in bounds
+        unsigned long long v = (l == top) ? vtop : tv.lvl[l][node * kFanout + lane];   // padded levels: in bounds
         unsigned long long incl = v;
         #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -168,7 +187,8 @@ struct apexb200_replay {
     apexb200::RingView ring;
     void *tree_block = nullptr;        // one allocation for all levels
     uint32_t *stamp = nullptr;         // [N] duplicate-resolution stamps (K2); all zero between calls
-    int32_t *status = nullptr;         // device control block: [0] status word, [2] u32 ticket, [4..5] u64 draw counter
+    int32_t *status = nullptr;         // device control block: [0] status word, [4..5] u64 update epoch
+    unsigned long long draw_calls = 0; // host: stratified-draw calls issued (the `call` of strat_uniform)
     std::vector<long long> lane_count; // host ring heads
     int64_t device_bytes = 0;
 };

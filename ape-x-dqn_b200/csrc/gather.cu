@@ -27,7 +27,7 @@ struct GatherArgs {
 
 struct SampleArgs {
     const double *u;                 // caller's draws, or null -> stratified draws generated here
-    unsigned long long seed;
+    unsigned long long seed, call;
     int32_t *idx_out, *fsel_out;
     unsigned long long *leaf_out, *total_out;
     double *u_out;
@@ -80,31 +80,63 @@ __device__ __forceinline__ void gather_meta(const RingView &rv, const GatherArgs
 
 // One frame through shared memory with the TMA (bulk async-copy) engine: global -> shared
 // completes on an mbarrier, shared -> global drains it; the bytes never enter registers.
+// A frame can move as several chunks, each with its own mbarrier (chunk c stored while
+// chunks c+1.. are landing); measured on B200 (profiles/r01_kernel_experiments.md) whole
+// 7 KB frames are faster than 3 x 2.3 KB chunks, because the launch is bound by L2 slice
+// throughput rather than by phase serialisation, so frames up to 16 KB move as one chunk.
 // Frame reads are single-use (evict_first) so that they do not push the sum tree or the
 // freshly written batch out of L2.
-__device__ __forceinline__ void tma_load_frame(const uint8_t *src, uint8_t *stage, unsigned long long *bar, unsigned bytes) {
-    const unsigned bar_s = (unsigned)__cvta_generic_to_shared(bar);
-    const unsigned buf_s = (unsigned)__cvta_generic_to_shared(stage);
-    unsigned long long pol;
-    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s));
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(bytes) : "memory");
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
-                 ::"r"(buf_s), "l"(src), "r"(bytes), "r"(bar_s), "l"(pol) : "memory");
+constexpr int kMaxChunks = 4;
+
+__device__ __forceinline__ int frame_chunks(int frame_bytes) {
+    if (frame_bytes <= 16384) return 1;
+    const int v = frame_bytes >> 4;
+    return (v % 4 == 0) ? 4 : (v % 3 == 0) ? 3 : (v % 2 == 0) ? 2 : 1;
 }
 
-__device__ __forceinline__ void tma_store_frame(uint8_t *dst, uint8_t *stage, unsigned long long *bar, unsigned bytes) {
-    const unsigned bar_s = (unsigned)__cvta_generic_to_shared(bar);
+__device__ __forceinline__ void tma_load_frame(const uint8_t *src, uint8_t *stage, unsigned long long *bars, unsigned bytes,
+                                               int nch) {
     const unsigned buf_s = (unsigned)__cvta_generic_to_shared(stage);
-    unsigned done = 0;
-    while (!done) {
-        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n"
-                     " selp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(bar_s) : "memory");
+    const unsigned chunk = bytes / nch;
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    for (int c = 0; c < nch; ++c) {
+        const unsigned bar_s = (unsigned)__cvta_generic_to_shared(bars + c);
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s));
     }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(buf_s), "r"(bytes) : "memory");
-    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    for (int c = 0; c < nch; ++c) {
+        const unsigned bar_s = (unsigned)__cvta_generic_to_shared(bars + c);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(chunk) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                     ::"r"(buf_s + c * chunk), "l"(src + c * chunk), "r"(chunk), "r"(bar_s), "l"(pol) : "memory");
+    }
+}
+
+// Drain: every lane that moves a frame polls its own mbarriers without blocking and
+// issues the shared -> global copy of a chunk the moment that chunk has landed, so the
+// stores of early frames overlap the loads of late ones (a blocking wait would hold the
+// whole warp until its slowest frame arrived).  Must be called by all 32 lanes.
+__device__ __forceinline__ void tma_drain_frames(bool moving, uint8_t *dst, uint8_t *stage, unsigned long long *bars,
+                                                 unsigned bytes, int nch) {
+    const unsigned buf_s = (unsigned)__cvta_generic_to_shared(stage);
+    const unsigned chunk = bytes / nch;
+    int next = moving ? 0 : nch;                     // next chunk this lane has to store
+    while (__any_sync(0xffffffffu, next < nch)) {
+        if (next < nch) {
+            const unsigned bar_s = (unsigned)__cvta_generic_to_shared(bars + next);
+            unsigned done;
+            asm volatile("{\n .reg .pred p;\n mbarrier.test_wait.parity.shared::cta.b64 p, [%1], 0;\n"
+                         " selp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(bar_s) : "memory");
+            if (done) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                             ::"l"(dst + next * chunk), "r"(buf_s + next * chunk), "r"(chunk) : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                ++next;
+            }
+        }
+    }
     asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 
@@ -143,85 +175,86 @@ gather_vec_kernel(RingView rv, GatherArgs ga, int32_t *status) {
     }
 }
 
-// ---- variant 1: TMA.  One lane owns one frame; 2 frames per 32-thread CTA keeps
-// 15 CTAs (30 frames, ~210 KB of staging) resident per SM, so a B=512, C=4 gather
-// (4096 frames) is a single wave on 148 SMs.
-constexpr int kTmaItemsPerCta = 2;
+// Shared-memory budget for frame staging: one fat CTA per SM instead of many thin ones.
+// With ~7 KB frames a thin (1-2 frame) CTA spends longer being launched than moving
+// data; 32 frames per CTA (220.5 KB of the 227 KB an SM offers) puts a whole B=512, C=4
+// batch (4096 frames) in flight at once from 128 CTAs, one launch wave, one CTA per SM.
+constexpr size_t kStageBudget = 226 * 1024;
+constexpr size_t kBarBytes = 32 * kMaxChunks * 8;           // mbarriers sit in front of the staging area
 
+// ---- variant 1: TMA.  One lane owns one frame; up to 32 frames per 32-thread CTA.
 __global__ void __launch_bounds__(32)
-gather_tma_kernel(RingView rv, GatherArgs ga, int32_t *status) {
+gather_tma_kernel(RingView rv, GatherArgs ga, int per_cta, int32_t *status) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ __align__(8) unsigned long long bars[kTmaItemsPerCta];
+    unsigned long long *bars = (unsigned long long *)smem;
+    uint8_t *stage = smem + kBarBytes;
     pdl_prologue();
     const int lane = threadIdx.x;
+    const int nch = frame_chunks(rv.F);
     int count = ga.count;
     if (ga.count_dev) count = min(count, *ga.count_dev);
     const long long n_items = (long long)count * 2 * rv.C;
     const long long host_items = (long long)ga.count * 2 * rv.C;
-    const long long first = (long long)blockIdx.x * kTmaItemsPerCta;
+    const long long first = (long long)blockIdx.x * per_cta;
     if (first >= host_items) {                              // trailing CTAs: metadata
-        long long mb = blockIdx.x - (host_items + kTmaItemsPerCta - 1) / kTmaItemsPerCta;
+        long long mb = blockIdx.x - (host_items + per_cta - 1) / per_cta;
         gather_meta(rv, ga, (int)(mb * 32 + lane), count, status);
         return;
     }
-    if (lane < kTmaItemsPerCta) {
-        const long long it = first + lane;
-        const uint8_t *src; uint8_t *dst;
-        if (it < n_items && resolve_item(rv, ga, it, count, &src, &dst, status)) {
-            tma_load_frame(src, smem + (size_t)lane * rv.F, &bars[lane], (unsigned)rv.F);
-            tma_store_frame(dst, smem + (size_t)lane * rv.F, &bars[lane], (unsigned)rv.F);
-        }
-    }
+    const long long it = first + lane;
+    const uint8_t *src = nullptr; uint8_t *dst = nullptr;
+    const bool moving = lane < per_cta && it < n_items && resolve_item(rv, ga, it, count, &src, &dst, status);
+    if (moving) tma_load_frame(src, stage + (size_t)lane * rv.F, bars + lane * kMaxChunks, (unsigned)rv.F, nch);
+    tma_drain_frames(moving, dst, stage + (size_t)lane * rv.F, bars + lane * kMaxChunks, (unsigned)rv.F, nch);
 }
 
-// ---- fused K3 + K4: one 32-thread CTA per draw.  The warp descends the tree, lanes
-// 0..2C-1 read the record's frame slots and each moves one frame with the TMA engine
-// while lanes 16.. copy the metadata row.  2C*F bytes of staging per CTA (56 KB at C=4)
-// -> 4 CTAs per SM, 592 resident draws: a B=512 batch is a single wave.
-__global__ void __launch_bounds__(32)
+// ---- fused K3 + K4: one warp per draw, `wpc` warps per CTA.  Each warp descends the
+// tree for its draw, lanes 0..2C-1 read the record's frame slots and each moves one
+// frame with the TMA engine while lane 16 copies the metadata row.  wpc * 2C * F bytes
+// of staging per CTA: at C=4 four draws (32 frames) per CTA, so a B=512 batch is 128
+// CTAs — a single wave with one CTA per SM and every frame of the batch in flight.
+__global__ void __launch_bounds__(256)
 sample_gather_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int32_t *ctrl) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ __align__(8) unsigned long long bars[16];
+    unsigned long long *bars = (unsigned long long *)smem;
     pdl_prologue();
-    const int lane = threadIdx.x;
-    const int w = blockIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int wl = threadIdx.x >> 5;
+    const int wpc = blockDim.x >> 5;
+    const int nch = frame_chunks(rv.F);
+    const int w = blockIdx.x * wpc + wl;
     const int count = ga.count;
     const int twoC = 2 * rv.C;
+    if (w >= count) return;
+    uint8_t *stage = smem + (size_t)wpc * 16 * kMaxChunks * 8 + (size_t)(wl * twoC + lane) * rv.F;
+    unsigned long long *my_bars = bars + (wl * 16 + lane) * kMaxChunks;
     const bool strat = (sa.u == nullptr);
+    const unsigned long long vtop = top_level_value(tv);     // in flight while the draw is formed
     double uw;
     if (strat) {
-        const unsigned long long counter = *(volatile unsigned long long *)(ctrl + 4);
-        uw = strat_uniform(sa.seed, counter, w, count);
+        uw = strat_uniform(sa.seed, read_epoch(ctrl), sa.call, w, count);
         if (sa.u_out && lane == 0) sa.u_out[w] = uw;
     } else {
         uw = sa.u[w];
     }
     unsigned long long leaf, total;
-    const long long node = warp_descend(tv, 0ull, true, uw, &leaf, &total, ctrl);
+    const long long node = warp_descend(tv, vtop, 0ull, true, uw, &leaf, &total, ctrl);
     long long f = -1;
     if (node >= 0 && lane < twoC) f = rv.fidx[node * twoC + lane];
+    bool moving = false;
+    if (node >= 0 && lane < twoC) {
+        if (f < 0 || f >= rv.N * rv.fpr) atomicOr(ctrl, APEXB200_ST_BAD_INDEX);
+        else { moving = true; tma_load_frame(rv.frames + f * rv.F, stage, my_bars, (unsigned)rv.F, nch); }
+    }
+    // bookkeeping overlaps the frame loads
     if (lane < twoC && sa.fsel_out) sa.fsel_out[(long long)w * twoC + lane] = (int32_t)f;
     if (lane == 0) {
         sa.idx_out[w] = (int32_t)node;
         if (sa.leaf_out) sa.leaf_out[w] = node >= 0 ? leaf : 0ull;
         if (sa.total_out && w == 0) *sa.total_out = total;
     }
-    bool moving = false;
-    if (node >= 0 && lane < twoC) {
-        if (f < 0 || f >= rv.N * rv.fpr) atomicOr(ctrl, APEXB200_ST_BAD_INDEX);
-        else { moving = true; tma_load_frame(rv.frames + f * rv.F, smem + (size_t)lane * rv.F, &bars[lane], (unsigned)rv.F); }
-    }
-    if (node >= 0 && lane == 16) copy_meta_row(rv, ga, w, node);        // overlaps the frame loads
-    if (moving) tma_store_frame(item_dst(rv, ga, w, lane), smem + (size_t)lane * rv.F, &bars[lane], (unsigned)rv.F);
-    if (strat && lane == 0) {
-        // the last CTA to finish (every CTA has read the counter by then) advances it
-        __threadfence();
-        unsigned int t = atomicAdd((unsigned int *)(ctrl + 2), 1u);
-        if (t == (unsigned int)count - 1u) {
-            *(volatile unsigned long long *)(ctrl + 4) += 1ull;
-            *(volatile unsigned int *)(ctrl + 2) = 0u;
-        }
-    }
+    if (node >= 0 && lane == 16) copy_meta_row(rv, ga, w, node);
+    tma_drain_frames(moving, moving ? item_dst(rv, ga, w, lane) : nullptr, stage, my_bars, (unsigned)rv.F, nch);
 }
 
 static int ensure_smem(const void *fn, size_t smem, int device) {
@@ -259,13 +292,17 @@ int apexb200_gather(apexb200_replay_t h, const int32_t *idx, const int32_t *fsel
     cudaStream_t st = (cudaStream_t)stream;
     const long long items = (long long)count * 2 * rv.C;
     const long long meta_warps = (count + 31) / 32;
-    const size_t smem = (size_t)kTmaItemsPerCta * rv.F;
-    if (g_gather_variant == 1 && smem <= 200 * 1024) {
+    if (g_gather_variant == 1 && kBarBytes + (size_t)rv.F <= kStageBudget) {
+        long long per_cta = (long long)((kStageBudget - kBarBytes) / rv.F);
+        if (per_cta > 32) per_cta = 32;
+        const long long spread = (items + kNumSMs - 1) / kNumSMs;      // small batches: use every SM
+        if (spread < per_cta) per_cta = spread;
+        const size_t smem = kBarBytes + (size_t)per_cta * rv.F;
         int rc = ensure_smem((const void *)gather_tma_kernel, smem, h->cfg.device);
         if (rc) return rc;
-        const long long blocks = (items + kTmaItemsPerCta - 1) / kTmaItemsPerCta + meta_warps;
+        const long long blocks = (items + per_cta - 1) / per_cta + meta_warps;
         return launch_step("gather_tma_kernel", gather_tma_kernel, dim3((unsigned)blocks), dim3(32), smem, st, rv, ga,
-                           h->status);
+                           (int)per_cta, h->status);
     }
     const long long warps = items + meta_warps;
     return launch_step("gather_vec_kernel", gather_vec_kernel<14>, dim3((unsigned)((warps + 7) / 8)), dim3(256), 0, st,
@@ -282,22 +319,27 @@ int apexb200_sample_gather(apexb200_replay_t h, const double *u, uint64_t seed, 
     APEX_REQUIRE((((uintptr_t)S_t | (uintptr_t)S_tpn) & 15) == 0, APEXB200_EINVAL,
                  "sample_gather: output batches must be 16-byte aligned");
     const RingView &rv = h->ring;
-    const size_t smem = (size_t)2 * rv.C * rv.F;
+    const size_t per_draw = (size_t)2 * rv.C * rv.F;
     cudaStream_t st = (cudaStream_t)stream;
-    if (2 * rv.C > 16 || smem > 200 * 1024) {
+    if (2 * rv.C > 16 || per_draw + 16 * kMaxChunks * 8 > kStageBudget) {
         // staging for one record does not fit one CTA: run the two kernels back to back
         int rc = u ? apexb200_sample(h, u, count, idx_out, leaf_out, total_out, fsel_out, stream)
                    : apexb200_sample_stratified(h, seed, count, idx_out, leaf_out, total_out, fsel_out, u_out, stream);
         if (rc) return rc;
         return apexb200_gather(h, idx_out, fsel_out, count, nullptr, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, stream);
     }
+    int wpc = (int)(kStageBudget / (per_draw + 16 * kMaxChunks * 8));      // draws (warps) per CTA that fit
+    if (wpc > 8) wpc = 8;
+    const int spread = (count + kNumSMs - 1) / kNumSMs;                    // small batches: use every SM
+    if (spread < wpc) wpc = spread;
+    const size_t smem = (size_t)wpc * (per_draw + 16 * kMaxChunks * 8);
     int rc = ensure_smem((const void *)sample_gather_kernel, smem, h->cfg.device);
     if (rc) return rc;
-    SampleArgs sa{u, (unsigned long long)seed, idx_out, fsel_out, (unsigned long long *)leaf_out,
+    SampleArgs sa{u, (unsigned long long)seed, u ? 0ull : h->draw_calls++, idx_out, fsel_out, (unsigned long long *)leaf_out,
                   (unsigned long long *)total_out, u_out};
     GatherArgs ga{idx_out, fsel_out, nullptr, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, count};
-    return launch_step("sample_gather_kernel", sample_gather_kernel, dim3((unsigned)count), dim3(32), smem, st, h->tree,
-                       rv, sa, ga, h->status);
+    return launch_step("sample_gather_kernel", sample_gather_kernel, dim3((unsigned)((count + wpc - 1) / wpc)),
+                       dim3(wpc * 32), smem, st, h->tree, rv, sa, ga, h->status);
 }
 
 }  // extern "C"

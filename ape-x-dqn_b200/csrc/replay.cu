@@ -49,6 +49,7 @@ insert_meta_kernel(RingView rv, TreeView tv, int lane, long long head, int count
                    const float *__restrict__ R, const float *__restrict__ G,
                    const float *__restrict__ prio, const float *__restrict__ q_t,
                    const float *__restrict__ q_tpn, int32_t *status) {
+    bump_epoch(status);
     int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= count + rv.lookback) return;
     long long p = (head + j) % rv.lane_cap;

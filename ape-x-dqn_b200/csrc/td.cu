@@ -79,6 +79,7 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
                 int32_t *status) {
     __shared__ float warp_part[32];
     pdl_prologue();
+    if (idx != nullptr) bump_epoch(status);
     const int b = threadIdx.x;
     const int live = live_rows(a);
     float l = 0.0f;

@@ -52,8 +52,9 @@ __device__ __forceinline__ unsigned long long new_leaf_value(const void *values,
 __global__ void __launch_bounds__(256)
 tree_apply_kernel(TreeView tv, const int32_t *__restrict__ idx, const void *__restrict__ values, int mode,
                   int count, const int32_t *__restrict__ count_dev, uint32_t *__restrict__ stamp,
-                  float alpha, float eps) {
+                  float alpha, float eps, int32_t *ctrl) {
     pdl_prologue();
+    bump_epoch(ctrl);
     int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (count_dev) count = min(count, *count_dev);
     if (j >= count) return;
@@ -73,6 +74,7 @@ __global__ void __launch_bounds__(1024)
 tree_update_small_kernel(TreeView tv, const int32_t *__restrict__ idx, const void *__restrict__ values, int mode,
                          int count, uint32_t *__restrict__ stamp, float alpha, float eps, int32_t *status) {
     pdl_prologue();
+    bump_epoch(status);
     int j = threadIdx.x;
     long long i = -1;
     if (j < count) {
@@ -110,7 +112,7 @@ tree_sample_kernel(TreeView tv, const double *__restrict__ u, const unsigned lon
                    int count, const int32_t *__restrict__ count_dev, int32_t *__restrict__ idx_out,
                    unsigned long long *__restrict__ leaf_out, unsigned long long *__restrict__ total_out,
                    const int32_t *__restrict__ fidx, int twoC, int32_t *__restrict__ fsel_out, int32_t *ctrl,
-                   unsigned long long seed, double *__restrict__ u_out) {
+                   unsigned long long seed, unsigned long long call, double *__restrict__ u_out) {
     pdl_prologue();
     int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     int lane = threadIdx.x & 31;
@@ -119,15 +121,15 @@ tree_sample_kernel(TreeView tv, const double *__restrict__ u, const unsigned lon
     unsigned long long leaf, total;
     const bool strat = (u == nullptr && targets == nullptr);
     const bool from_u = strat || (u != nullptr);
+    const unsigned long long vtop = top_level_value(tv);     // in flight while the draw is formed
     double uw = 0.0;
     if (strat) {
-        const unsigned long long counter = *(volatile unsigned long long *)(ctrl + 4);
-        uw = strat_uniform(seed, counter, w, count);
+        uw = strat_uniform(seed, read_epoch(ctrl), call, w, count);
         if (u_out && lane == 0) u_out[w] = uw;
     } else if (u != nullptr) {
         uw = u[w];
     }
-    long long node = warp_descend(tv, from_u ? 0ull : targets[w], from_u, uw, &leaf, &total, ctrl);
+    long long node = warp_descend(tv, vtop, from_u ? 0ull : targets[w], from_u, uw, &leaf, &total, ctrl);
     if (lane == 0) {
         idx_out[w] = (int32_t)node;
         if (leaf_out) leaf_out[w] = node >= 0 ? leaf : 0ull;
@@ -135,15 +137,6 @@ tree_sample_kernel(TreeView tv, const double *__restrict__ u, const unsigned lon
     }
     if (fsel_out && lane < twoC)
         fsel_out[(long long)w * twoC + lane] = node >= 0 ? fidx[node * twoC + lane] : -1;
-    if (strat && lane == 0) {
-        // the last warp to finish (every warp has read the counter by then) advances it
-        __threadfence();
-        unsigned int t = atomicAdd((unsigned int *)(ctrl + 2), 1u);
-        if (t == (unsigned int)count - 1u) {
-            *(volatile unsigned long long *)(ctrl + 4) += 1ull;
-            *(volatile unsigned int *)(ctrl + 2) = 0u;
-        }
-    }
 }
 
 // ---------------------------------------------------------------------------
@@ -199,7 +192,7 @@ shard_targets_kernel(const unsigned long long *__restrict__ totals, int G, int r
 int run_tree_apply(apexb200_replay *h, const int32_t *idx, const void *values, int mode, int count,
                    const int32_t *count_dev, cudaStream_t st) {
     return launch_step("tree_apply_kernel", tree_apply_kernel, dim3((count + 255) / 256), dim3(256), 0, st, h->tree, idx,
-                       values, mode, count, count_dev, h->stamp, h->ring.alpha, 0.0f);
+                       values, mode, count, count_dev, h->stamp, h->ring.alpha, 0.0f, h->status);
 }
 
 // Shared by tree.cu and td.cu: run K2 over (idx, values).
@@ -215,7 +208,7 @@ int run_tree_update(apexb200_replay *h, const int32_t *idx, const void *values, 
                          h->stamp, (long long)h->ring.N, h->status);
     if (rc) return rc;
     return launch_step("tree_apply_kernel", tree_apply_kernel, dim3(blocks), dim3(256), 0, st, h->tree, idx, values, mode,
-                       count, count_dev, h->stamp, h->ring.alpha, eps);
+                       count, count_dev, h->stamp, h->ring.alpha, eps, h->status);
 }
 
 }  // namespace apexb200
@@ -288,7 +281,8 @@ int apexb200_tree_load_leaves(apexb200_replay_t h, const uint64_t *leaves, int64
 
 static int launch_sample(apexb200_replay_t h, const double *u, const uint64_t *targets, int32_t count,
                          const int32_t *count_dev, int32_t *idx_out, uint64_t *leaf_out, uint64_t *total_out,
-                         int32_t *fsel_out, void *stream, uint64_t seed = 0, double *u_out = nullptr) {
+                         int32_t *fsel_out, void *stream, uint64_t seed = 0, uint64_t call = 0,
+                         double *u_out = nullptr) {
     if (count == 0) return APEXB200_OK;
     const int twoC = 2 * h->ring.C;
     APEX_REQUIRE(!fsel_out || twoC <= 32, APEXB200_ERANGE, "sample: fsel_out needs 2*frames_per_state <= 32");
@@ -297,7 +291,7 @@ static int launch_sample(apexb200_replay_t h, const double *u, const uint64_t *t
     return launch_step("tree_sample_kernel", tree_sample_kernel, dim3(blocks), dim3(warps_per_block * 32), 0,
                        (cudaStream_t)stream, h->tree, u, (const unsigned long long *)targets, count, count_dev, idx_out,
                        (unsigned long long *)leaf_out, (unsigned long long *)total_out, (const int32_t *)h->ring.fidx,
-                       twoC, fsel_out, h->status, (unsigned long long)seed, u_out);
+                       twoC, fsel_out, h->status, (unsigned long long)seed, (unsigned long long)call, u_out);
 }
 
 int apexb200_sample(apexb200_replay_t h, const double *u, int32_t count, int32_t *idx_out, uint64_t *leaf_out,
@@ -311,7 +305,7 @@ int apexb200_sample_stratified(apexb200_replay_t h, uint64_t seed, int32_t count
                                void *stream) {
     APEX_REQUIRE(h && count >= 0 && (count == 0 || idx_out), APEXB200_EINVAL, "sample_stratified: bad argument");
     return launch_sample(h, nullptr, nullptr, count, nullptr, idx_out, leaf_out, total_out, fsel_out, stream, seed,
-                         u_out);
+                         h->draw_calls++, u_out);
 }
 
 int apexb200_sample_targets(apexb200_replay_t h, const uint64_t *targets, const int32_t *count_dev,

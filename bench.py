@@ -39,7 +39,9 @@ def parse():
     ap.add_argument("--frames-per-state", type=int, default=4)
     ap.add_argument("--actions", type=int, default=4)
     ap.add_argument("--lanes", type=int, default=32)
-    ap.add_argument("--gather-variant", type=int, default=int(os.environ.get("APEX_GATHER_VARIANT", "0")))
+    ap.add_argument("--gather-variant", type=int, default=int(os.environ.get("APEX_GATHER_VARIANT", "1")))
+    ap.add_argument("--unfused", action="store_true", help="separate K3 and K4 launches instead of the fused kernel")
+    ap.add_argument("--no-pdl", action="store_true", help="plain stream-ordered launches (no programmatic dependent launch)")
     ap.add_argument("--no-graph", action="store_true", help="launch every step from Python instead of a CUDA graph")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the CPU-baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -132,6 +134,8 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     _C.call("apexb200_set_gather_variant", args.gather_variant)
+    _C.call("apexb200_set_pdl", 0 if args.no_pdl else 1)
+    fused = not args.unfused
     B, C, nA, N = args.batch, args.frames_per_state, args.actions, args.capacity
     Bg = B * world
     mem = apex_b200.ReplayMemory(N, {"priority_exponent": ALPHA, "layout": "stream", "lanes": args.lanes, "n_step": 3,
@@ -153,7 +157,7 @@ def run_ours(args):
     def step(k):
         q = qpool[k % P]
         if world == 1:
-            b = mem.sample_tensors(B)                             # K3 (in-kernel stratified draws) + K4
+            b = mem.sample_tensors(B, fused=fused)                # K3 (in-kernel stratified draws) + K4
             mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma, out=td_out)      # K5 + K2
         else:
             b, _pos, cnt = sampler.sample(u_table[step_no[0] % 64])
@@ -202,42 +206,48 @@ def run_ours(args):
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    launches_per_step = 3 if world == 1 else 5 + (1 if Bg > 1024 else 0)
+    launches_per_step = (2 if fused else 3) if world == 1 else 5 + (1 if Bg > 1024 else 0)
     value = K * Bg / (ms * 1e-3)
 
-    # ---- roofline of the dominant kernel (K4 gather): CUDA events around each launch, eager pass
-    # with the GPU kept busy ahead of the CPU so that intervals are kernel time, not launch gaps.
+    # ---- roofline of the dominant kernel (fused K3+K4 sample_gather, or K4 alone with --unfused):
+    # CUDA events around each launch in an eager pass over the same loop, with the GPU kept busy
+    # ahead of the CPU so that the intervals are kernel time, not launch gaps.
+    peak, peak_src = peaks()
+    bytes_per_rec = 4 * C * F_BYTES + 32
+    roofline = None
     if world == 1:
         n_r = min(K, 400)
         o = mem._outputs(B, False)
-        pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_r)]
+        ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(n_r)]
         big = torch.zeros(1 << 30, dtype=torch.uint8, device=dev)
         torch.cuda.synchronize()
         for _ in range(40):
             big.add_(1)                                           # ~13 ms of queued GPU work: the CPU runs ahead
         for k in range(n_r):
-            mem.sample_stratified(B, idx_out=o["idx"], fsel_out=o["fsel"])
-            pairs[k][0].record()
-            mem.gather(o["idx"], fsel=o["fsel"], out=o)
-            pairs[k][1].record()
             q = qpool[k % P]
+            if fused:
+                ev[k][0].record()
+                mem.sample_tensors(B)
+            else:
+                mem.sample_stratified(B, idx_out=o["idx"], fsel_out=o["fsel"])
+                ev[k][0].record()
+                mem.gather(o["idx"], fsel=o["fsel"], out=o)
+            ev[k][1].record()
             mem.td_update(o["idx"], q[0], q[1], q[2], o["A"], o["R"], o["Gamma"], out=td_out)
+            ev[k][2].record()
         torch.cuda.synchronize()
-        g_us = sorted(a.elapsed_time(b) * 1e3 for a, b in pairs)
+        g_us = sorted(e[0].elapsed_time(e[1]) * 1e3 for e in ev)
+        t_us = sorted(e[1].elapsed_time(e[2]) * 1e3 for e in ev)
         g_mean_us = sum(g_us) / len(g_us)
         del big
-    else:
-        g_mean_us, g_us = None, []
-    peak, peak_src = peaks()
-    bytes_per_rec = 4 * C * F_BYTES + 32
-    roofline = None
-    if g_mean_us:
         ach = bytes_per_rec * B / (g_mean_us * 1e-6) / 1e9
-        roofline = {"kernel": "gather_vec_kernel" if args.gather_variant == 0 else "gather_tma_kernel", "bound": "hbm",
-                    "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
-                    "traffic": None, "algorithmic_bytes_per_launch": bytes_per_rec * B,
+        kname = "sample_gather_kernel" if fused else ("gather_tma_kernel" if args.gather_variant == 1 else "gather_vec_kernel")
+        roofline = {"kernel": kname, "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
+                    "frac": round(ach / peak, 4), "traffic": None, "algorithmic_bytes_per_launch": bytes_per_rec * B,
                     "launch_us_mean": round(g_mean_us, 3), "launch_us_median": round(g_us[len(g_us) // 2], 3),
-                    "launch_us_min": round(g_us[0], 3), "launches_timed": len(g_us), "peak_source": peak_src}
+                    "launch_us_min": round(g_us[0], 3), "launches_timed": len(g_us), "peak_source": peak_src,
+                    "other_kernels": {"td_small_kernel(K5+K2)_us_mean": round(sum(t_us) / len(t_us), 3)},
+                    "timing": "cuda events around each launch, eager pass of %d steps after the timed region" % n_r}
 
     # ---- end to end through the public tensor API with HOST inputs and a host-read result
     e2e = None
@@ -291,7 +301,9 @@ def run_ours(args):
                                    % (N, B, C, ALPHA),
                        "capacity_per_gpu": N, "batch_per_gpu": B, "frames_per_state": C, "lanes": args.lanes,
                        "launch": "cuda graph of %d steps" % P if graph is not None else "python loop",
-                       "gather_variant": args.gather_variant,
+                       "kernels_per_step": "sample_gather_kernel + td_small_kernel" if fused else
+                                           "tree_sample_kernel + gather kernel (variant %d) + td_small_kernel" % args.gather_variant,
+                       "pdl": not args.no_pdl,
                        "l2": "frame store %.1f GB >> 126 MB L2 (random gathers miss); the %.1f MB tree is L2-resident by design"
                              % (N * F_BYTES / 1e9, N * 8 * 33 / 32 / 1e6),
                        "parallelism": "1 shard per GPU, NCCL all-gather of shard totals" if world > 1 else "single shard"},

@@ -145,10 +145,13 @@ int apexb200_sample(apexb200_replay_t h, const double *u, int32_t count, int32_t
                     uint64_t *leaf_out, uint64_t *total_out, int32_t *fsel_out, void *stream);
 /* K3 with the PER stratification done in the kernel (the reference draws i.i.d. from
  * numpy's global RNG, replay.py:52; stratified draws are the Ape-X/PER paper's variant
- * of the same law): u_j = (j + v_j)/count, v_j = splitmix64(seed, call counter, j) *
- * 2^-53.  The handle keeps the call counter on the device and advances it by one per
- * call, so the launch can be replayed from a CUDA graph.  u_out (nullable) [count]
- * receives the draws so that a checker can replay them. */
+ * of the same law): u_j = (j + v_j)/count, v_j = splitmix64(seed, epoch, call, j) * 2^-53.
+ * `epoch` is a device-resident counter that every tree-changing kernel of this handle
+ * (insert, tree_update, tree_set_leaves, td_fwd_update) advances by one, so a CUDA-graph
+ * replay of a sample -> ... -> update step draws fresh numbers without host state;
+ * `call` counts this handle's stratified calls on the host and separates several samples
+ * taken between two updates (it is baked into a captured launch).  u_out (nullable)
+ * [count] receives the draws so that a checker can replay them. */
 int apexb200_sample_stratified(apexb200_replay_t h, uint64_t seed, int32_t count, int32_t *idx_out,
                                uint64_t *leaf_out, uint64_t *total_out, int32_t *fsel_out, double *u_out,
                                void *stream);

@@ -92,13 +92,13 @@ def stratified_uniforms(batch: int, rng: np.random.Generator) -> np.ndarray:
     return (np.arange(batch, dtype=np.float64) + v) / float(batch)
 
 
-def kernel_stratified_uniforms(seed: int, counter: int, batch: int) -> np.ndarray:
+def kernel_stratified_uniforms(seed: int, epoch: int, call: int, batch: int) -> np.ndarray:
     """The draws apexb200_sample_stratified generates on the device, restated:
-    u_j = (j + v_j)/B with v_j = splitmix64-finaliser(seed, counter, j) * 2^-53."""
+    u_j = (j + v_j)/B with v_j = splitmix64-finaliser(seed, update epoch, call index, j) * 2^-53."""
     M = (1 << 64) - 1
     out = np.empty(batch, np.float64)
     for j in range(batch):
-        z = (seed ^ ((counter * 0xD1342543DE82EF95) & M)) & M
+        z = (seed ^ ((epoch * 0xD1342543DE82EF95) & M) ^ ((call * 0xA24BAED4963EE407) & M)) & M
         z = (z + (j + 1) * 0x9E3779B97F4A7C15) & M
         z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & M
         z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & M

@@ -160,13 +160,21 @@ def test_stratified_draws_generated_in_kernel(apex):
     mem = make_mem(apex, N)
     mem.seed = 0xC0FFEE
     load_leaves(apex, mem, leaves)
-    for call in range(3):                                    # the device call counter advances by one per call
+    epoch = 0                                                # tree-changing kernels run on this handle so far
+    for call in range(4):                                    # host call index separates draws between updates
         u_out = torch.empty(B, dtype=torch.float64, device="cuda")
-        idx = mem.sample_stratified(B, u_out=u_out).cpu().numpy()
+        if call % 2:
+            idx = mem.sample_tensors(B, u_out=u_out).idx.cpu().numpy()         # fused K3+K4
+        else:
+            idx = mem.sample_stratified(B, u_out=u_out).cpu().numpy()
         u = u_out.cpu().numpy()
-        np.testing.assert_array_equal(u, ro.kernel_stratified_uniforms(0xC0FFEE, call, B))
+        np.testing.assert_array_equal(u, ro.kernel_stratified_uniforms(0xC0FFEE, epoch, call, B))
         assert ((u >= np.arange(B) / B) & (u < (np.arange(B) + 1) / B)).all()
         np.testing.assert_array_equal(idx, ro.tree_sample(leaves, u))
+        if call == 1:                                        # a priority update advances the device epoch
+            mem.update_priorities(dev(idx[:7].astype(np.int32)), dev(np.ones(7, np.float32)))
+            leaves[idx[:7]] = 1 << 24
+            epoch += 1
     mem.check_status()
 
 
