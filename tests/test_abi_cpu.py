@@ -143,3 +143,31 @@ def test_learner_constructs_on_cpu_like_the_reference():
     assert sum(p.numel() for p in L.Q.parameters()) == 3321541
     g = L.optimizer.param_groups[0]
     assert (g["lr"], g["weight_decay"], g["eps"]) == (0.00025 / 4, 0.95, 1.5e-7)   # learner.py:26
+
+
+def test_dropin_modules_and_manager_proxy():
+    """main.py:18,40-42: ReplayMemory registered with a BaseManager and built in the server process;
+    main.py:6-8: classes imported as replay.ReplayMemory / learner.Learner / actor.Actor."""
+    import subprocess
+    import sys
+    code = r'''
+import sys
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+from multiprocessing.managers import BaseManager
+from replay import ReplayMemory
+from learner import Learner
+from actor import Actor, ExperienceBuffer
+BaseManager.register("Memory", ReplayMemory)
+if __name__ == "__main__":
+    m = BaseManager(); m.start()
+    mem = m.Memory(100000, {"soft_capacity": 100000, "priority_exponent": 0.6, "importance_sampling_exponent": 0.4})
+    assert mem.size() == 0
+    mem.remove_to_fit(); mem.update_sample_probabilities(); mem.set_priorities({"10": 1.0})
+    exposed = sorted(x for x in dir(mem) if not x.startswith("_"))
+    for name in ("add", "remove_to_fit", "sample", "set_priorities", "size", "update_sample_probabilities"):
+        assert name in exposed, name
+    m.shutdown()
+    print("proxy ok")
+''' % (ROOT, os.path.join(ROOT, "ape-x-dqn_b200", "dropin"))
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and "proxy ok" in out.stdout, out.stderr[-2000:]
