@@ -18,6 +18,7 @@ ST_EMPTY_TREE, ST_BAD_INDEX, ST_BAD_TARGET, ST_BAD_ACTION = 1, 2, 4, 8
 FRAC_BITS = 24
 LEAF_MAX = (1 << 36) - 1
 MAX_CAPACITY = 1 << 24
+TD_NOALLOC_MAX_B = 262144
 BUF_FRAMES, BUF_FIDX, BUF_ACTION, BUF_REWARD, BUF_GAMMA, BUF_QT, BUF_QTPN, BUF_LEAVES = range(8)
 
 
@@ -62,6 +63,7 @@ SIGNATURES = {
     "apexb200_set_pdl": [_I32],
     "apexb200_td_workspace_bytes": [_I32, C.POINTER(_I64)],
     "apexb200_td_fwd": [_P, _P, _P, _P, _P, _P, _I32, _I32, _F, _F, _I32, _F, _P, _P, _P, _P, _P, _I64, _P],
+    "apexb200_td_fwd_noalloc": [_P, _P, _P, _P, _P, _P, _I32, _I32, _F, _F, _I32, _F, _P, _P, _P, _P, _P],
     "apexb200_td_bwd": [_P, _P, _P, _I32, _I32, _I32, _F, _P, _F, _P, _P],
     "apexb200_td_fwd_update": [_P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _F, _I32, _F, _P, _P, _P, _P, _P, _I64,
                                _P, _F, _P],

@@ -2,6 +2,8 @@
 // (+ backward, + in-place priority write-back), K7 n-step returns, and the actor's
 // initial priority.  All fp32, one thread per record; these kernels move a few
 // hundred bytes per record and are launch/latency bound, not bandwidth bound.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace apexb200 {
@@ -239,6 +241,36 @@ static int td_launch(apexb200_replay *h, const int32_t *idx, const TdArgs &a, vo
     return run_tree_apply(h, idx, a.prio, 2, a.B, a.count_dev, st);   // stamps were taken inside td_multi_kernel
 }
 
+// ---------------------------------------------------------------------------
+// Scratch for apexb200_td_fwd_noalloc.  It is part of the loaded module: every GPU that
+// loads the library carries these bytes until the process exits, and every call on that
+// GPU uses the same bytes.  Layout as in td_multi_kernel: [0,256) ticket, then one float
+// partial per 256-row CTA.
+constexpr size_t kNoAllocScratchBytes = 256 + (size_t)(APEXB200_TD_NOALLOC_MAX_B / 256) * sizeof(float);
+static __device__ __align__(256) unsigned char g_td_noalloc_scratch[kNoAllocScratchBytes];
+
+constexpr int kMaxDevices = 64;
+static std::mutex g_noalloc_mutex;
+static void *g_noalloc_ptr[kMaxDevices] = {};
+
+// In host code `g_td_noalloc_scratch` is only a handle for the symbol, not an address a
+// kernel can use; the device address has to be asked for, per device, with that device
+// current.  Done once per device and cached.
+static int noalloc_scratch_of_current_device(void **out) {
+    int dev = -1;
+    APEX_CUDA(cudaGetDevice(&dev));
+    APEX_REQUIRE(dev >= 0 && dev < kMaxDevices, APEXB200_ERANGE, "td_fwd_noalloc: device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (g_noalloc_ptr[dev] == nullptr) {
+        void *p = nullptr;
+        APEX_CUDA(cudaGetSymbolAddress(&p, g_td_noalloc_scratch));
+        APEX_REQUIRE(p != nullptr, APEXB200_ECUDA, "td_fwd_noalloc: no device address for the static scratch");
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return APEXB200_OK;
+}
+
 }  // namespace apexb200
 
 using namespace apexb200;
@@ -260,6 +292,29 @@ int apexb200_td_fwd(const float *q_on_t, const float *q_on_tpn, const float *q_t
     TdArgs a{q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, delta, prio, loss, loss_mean, B, num_actions, loss_kind,
              alpha, eps, kappa, nullptr, 0.0f};
     return td_launch(nullptr, nullptr, a, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int apexb200_td_fwd_noalloc(const float *q_on_t, const float *q_on_tpn, const float *q_tg_tpn, const int32_t *A,
+                            const float *R, const float *Gamma, int32_t B, int32_t num_actions, float alpha,
+                            float eps, int32_t loss_kind, float kappa, float *delta, float *prio, float *loss,
+                            float *loss_mean, void *stream) {
+    int rc = td_check(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, B, num_actions, delta, prio, loss, loss_mean);
+    if (rc) return rc;
+    APEX_REQUIRE(B <= APEXB200_TD_NOALLOC_MAX_B, APEXB200_ERANGE,
+                 "td_fwd_noalloc: B=%d exceeds the built-in scratch (at most %d rows per call); "
+                 "use apexb200_td_fwd with a caller-provided workspace", B, APEXB200_TD_NOALLOC_MAX_B);
+    void *scratch = nullptr;
+    rc = noalloc_scratch_of_current_device(&scratch);        // first call on a device: symbol look-up
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    // The bytes still hold whatever the previous call left; only the ticket has to start at
+    // zero (each CTA overwrites its own partial before the last CTA reads them).
+    APEX_CUDA(cudaMemsetAsync(scratch, 0, 256, st));
+    TdArgs a{q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, delta, prio, loss, loss_mean, B, num_actions, loss_kind,
+             alpha, eps, kappa, nullptr, 0.0f};
+    return launch_step("td_multi_kernel", td_multi_kernel, dim3((B + 255) / 256), dim3(256), 0, st, a,
+                       (const int32_t *)nullptr, (uint32_t *)nullptr, 0ll, (int32_t *)nullptr,
+                       (unsigned int *)scratch, (float *)((char *)scratch + 256));
 }
 
 int apexb200_td_fwd_update(apexb200_replay_t h, const int32_t *idx, const float *q_on_t, const float *q_on_tpn,

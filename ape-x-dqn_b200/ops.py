@@ -30,6 +30,20 @@ def td_forward(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, alpha, eps=0.0, loss_kin
     return delta, prio, loss, mean
 
 
+def td_forward_noalloc(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, alpha, eps=0.0, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0,
+                       out=None):
+    """td_forward for callers that cannot provide (or allocate) a workspace: the reduction scratch
+    is a small static buffer inside the library, shared by every call on the GPU.  At most
+    _C.TD_NOALLOC_MAX_B rows; calls that may overlap on the GPU must be ordered by the caller.
+    `out` = (delta, prio, loss, loss_mean) tensors to write into (allocated here if omitted)."""
+    B, nA = q_on_t.shape
+    delta, prio, loss, mean = out if out is not None else (_f32(B, q_on_t), _f32(B, q_on_t), _f32(B, q_on_t), _f32(1, q_on_t))
+    _C.call("apexb200_td_fwd_noalloc", _C.ptr(q_on_t), _C.ptr(q_on_tpn), _C.ptr(q_tg_tpn), _C.ptr(A), _C.ptr(R),
+            _C.ptr(Gamma), int(B), int(nA), float(alpha), float(eps), int(loss_kind), float(kappa), _C.ptr(delta),
+            _C.ptr(prio), _C.ptr(loss), _C.ptr(mean), _C.stream_ptr())
+    return delta, prio, loss, mean
+
+
 def td_backward(delta, A, grad_loss_mean, num_actions, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0, count_dev=None,
                 mean_divisor=0.0):
     import torch

@@ -49,6 +49,8 @@ extern "C" {
 #define APEXB200_MAX_CAPACITY (1ll << 24)   /* records per handle (shard) */
 #define APEXB200_MAX_ACTIONS 64
 
+#define APEXB200_TD_NOALLOC_MAX_B 262144    /* rows per call of apexb200_td_fwd_noalloc */
+
 #define APEXB200_LOSS_HALF_SQ 0         /* 1/2 delta^2, learner.py:48 */
 #define APEXB200_LOSS_HUBER   1         /* Huber(kappa) */
 
@@ -200,6 +202,31 @@ int apexb200_td_fwd(const float *q_on_t, const float *q_on_tpn, const float *q_t
                     int32_t num_actions, float alpha, float eps, int32_t loss_kind, float kappa,
                     float *delta, float *prio, float *loss, float *loss_mean,
                     void *workspace, int64_t workspace_bytes, void *stream);
+/* apexb200_td_fwd without a workspace argument.  (No counterpart in the reference: it
+ * exists for the way this library gets embedded.)  The loss reduction needs a few KB of
+ * device scratch.  Some callers have nowhere to get it from: a C or ctypes binding that
+ * is handed input and output pointers by its host framework but is not itself linked to
+ * the CUDA runtime cannot call cudaMalloc; a learner that has already given the whole
+ * device to its framework's allocator (or to a replay shard sized to fill HBM) may find
+ * cudaMalloc failing; and a steady-state actor/learner loop that must not stall other
+ * streams cannot afford cudaMalloc/cudaFree, which synchronise the device.  For them the
+ * scratch is compiled into the library: APEXB200_TD_NOALLOC_MAX_B/256 floats + 256 bytes
+ * (4352 bytes) of static device memory, held by every GPU that loads the library until
+ * the process exits.  The call never calls cudaMalloc, cudaFree or any allocating
+ * routine; inputs and outputs are still the caller's.
+ *   - B > APEXB200_TD_NOALLOC_MAX_B returns APEXB200_ERANGE (use apexb200_td_fwd).
+ *   - The device that owns the pointers and the stream must be current.  The first call on
+ *     each device looks up the scratch address (cudaGetSymbolAddress) and caches it; make
+ *     that first call before starting any stream capture.
+ *   - All calls on a GPU share the one scratch, whatever stream they use: two calls that
+ *     can overlap on the GPU race on it, so keep them on one stream or order them with
+ *     events.  The scratch keeps the previous call's contents; the call itself clears the
+ *     one word that has to start at zero.
+ * Results equal apexb200_td_fwd (bit for bit when B > 1024, where both run the same kernel). */
+int apexb200_td_fwd_noalloc(const float *q_on_t, const float *q_on_tpn, const float *q_tg_tpn,
+                            const int32_t *A, const float *R, const float *Gamma, int32_t B,
+                            int32_t num_actions, float alpha, float eps, int32_t loss_kind, float kappa,
+                            float *delta, float *prio, float *loss, float *loss_mean, void *stream);
 /* Gradient of loss_mean w.r.t. q_on_t (loss.backward() through learner.py:46-48):
  * grad_q [B, num_actions], zero except column A_b. grad_loss_mean: device scalar.
  * count_dev / mean_divisor as in td_fwd_update (NULL / 0 for a plain batch). */
