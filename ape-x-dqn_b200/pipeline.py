@@ -1,0 +1,85 @@
+"""Host-facing step: draws and Q-values arrive in HOST memory, loss / priorities / indices
+are read back on the host — the same K3+K4 -> K5+K2 step as the tensor API, wrapped so that
+one step is one CUDA-graph launch (pinned H2D copy, two kernels, one D2H copy).
+
+Replaces, for a caller that keeps its numbers on the host like the reference does, the
+round trip learner.py:68 (sample) -> :70 (loss, priorities) -> :76 (set_priorities).
+Two buffer sets are used alternately, so the host can fill step k+1 while step k runs.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _C
+
+
+class HostStepPipeline:
+    DEPTH = 2
+
+    def __init__(self, mem, batch_size, num_actions, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0, use_graph=True):
+        mem._ensure()
+        self.mem, self.B, self.nA = mem, int(batch_size), int(num_actions)
+        B, nA, dev = self.B, self.nA, mem.device
+        self.in_bytes = B * 8 + 3 * B * nA * 4
+        self.out_words = 4 * B + 4                       # delta | prio | loss | idx(int32 bits) | loss_mean
+        self.slots = []
+        mem._outputs(B, False)
+        mem.workspace(B)
+        for _ in range(self.DEPTH):
+            h_in = torch.empty(self.in_bytes, dtype=torch.uint8).pin_memory()
+            h_out = torch.empty(self.out_words, dtype=torch.float32).pin_memory()
+            d_in = torch.empty(self.in_bytes, dtype=torch.uint8, device=dev)
+            d_out = torch.empty(self.out_words, dtype=torch.float32, device=dev)
+            slot = dict(h_in=h_in, h_out=h_out, d_in=d_in, d_out=d_out, event=torch.cuda.Event(), graph=None,
+                        u_host=h_in[:B * 8].view(torch.float64).numpy(),
+                        q_host=h_in[B * 8:].view(torch.float32).numpy().reshape(3, B, nA),
+                        u=d_in[:B * 8].view(torch.float64), q=d_in[B * 8:].view(torch.float32).view(3, B, nA),
+                        td_out=(d_out[0:B], d_out[B:2 * B], d_out[2 * B:3 * B], d_out[4 * B:4 * B + 1]),
+                        idx_bits=d_out[3 * B:4 * B])
+            self.slots.append(slot)
+        self.loss_kind, self.kappa = loss_kind, kappa
+        self._k = 0
+        if use_graph:
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                self._enqueue(self.slots[0])               # warm-up outside capture
+                side.synchronize()
+                for slot in self.slots:
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, stream=side):
+                        self._enqueue(slot)
+                    slot["graph"] = g
+            torch.cuda.current_stream().wait_stream(side)
+
+    def _enqueue(self, s):
+        s["d_in"].copy_(s["h_in"], non_blocking=True)
+        b = self.mem.sample_tensors(self.B, u=s["u"])
+        self.mem.td_update(b.idx, s["q"][0], s["q"][1], s["q"][2], b.A, b.R, b.Gamma, self.loss_kind, self.kappa,
+                           out=s["td_out"])
+        s["idx_bits"].copy_(b.idx.view(torch.float32))
+        s["h_out"].copy_(s["d_out"], non_blocking=True)
+
+    def submit(self, u, q):
+        """u: float64 [B] host array of draws; q: float32 [3, B, nA] host array (Q(S_t), Q(S_tpn), Q_target(S_tpn)).
+        Returns a ticket for result()."""
+        s = self.slots[self._k % self.DEPTH]
+        s["event"].synchronize()                          # the slot's previous step has been read out
+        s["u_host"][:] = u
+        s["q_host"][:] = q
+        if s["graph"] is not None:
+            s["graph"].replay()
+        else:
+            self._enqueue(s)
+        s["event"].record()
+        self._k += 1
+        return self._k - 1
+
+    def result(self, ticket):
+        """Blocks until step `ticket` has finished; returns (loss_mean, priorities[B], indices[B]) host views."""
+        s = self.slots[ticket % self.DEPTH]
+        s["event"].synchronize()
+        out = s["h_out"].numpy()
+        B = self.B
+        return float(out[4 * B]), out[B:2 * B], out[3 * B:4 * B].view(np.int32)

@@ -209,15 +209,58 @@ def run_ours(args):
     launches_per_step = (2 if fused else 3) if world == 1 else 5 + (1 if Bg > 1024 else 0)
     value = K * Bg / (ms * 1e-3)
 
-    # ---- roofline of the dominant kernel (fused K3+K4 sample_gather, or K4 alone with --unfused):
-    # CUDA events around each launch in an eager pass over the same loop, with the GPU kept busy
-    # ahead of the CPU so that the intervals are kernel time, not launch gaps.
+    # ---- roofline of the dominant kernel (fused K3+K4 sample_gather, or K4 alone with --unfused).
+    # (a) launch duration: CUDA events around a CUDA graph of R back-to-back launches of that kernel
+    #     (fresh draws every launch, 16 x 28.9 MB of distinct source frames per replay >> L2), / launches;
+    # (b) the same kernel timed in place with an event pair per launch in an eager pass of the full
+    #     step (reported for reference: an event pair adds ~4-5 us to a ~12 us kernel).
     peak, peak_src = peaks()
     bytes_per_rec = 4 * C * F_BYTES + 32
     roofline = None
     if world == 1:
-        n_r = min(K, 400)
         o = mem._outputs(B, False)
+
+        def dominant():
+            if fused:
+                mem.sample_tensors(B)
+            else:
+                mem.gather(o["idx"], fsel=o["fsel"], out=o)
+        R_, reps = 16, 25
+        dominant()
+        torch.cuda.synchronize()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        gk = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(gk, stream=side):
+                for _ in range(R_):
+                    if not fused:
+                        mem.sample_stratified(B, idx_out=o["idx"], fsel_out=o["fsel"])
+                    dominant()
+        torch.cuda.current_stream().wait_stream(side)
+        gs = None
+        if not fused:                                             # subtract the interleaved K3 launches
+            gs = torch.cuda.CUDAGraph()
+            with torch.cuda.stream(side):
+                with torch.cuda.graph(gs, stream=side):
+                    for _ in range(R_):
+                        mem.sample_stratified(B, idx_out=o["idx"], fsel_out=o["fsel"])
+            torch.cuda.current_stream().wait_stream(side)
+
+        def time_graph(g):
+            for _ in range(3):
+                g.replay()
+            torch.cuda.synchronize()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            for _ in range(reps):
+                g.replay()
+            a1.record()
+            torch.cuda.synchronize()
+            return a0.elapsed_time(a1) * 1e3 / (R_ * reps)
+        g_mean_us = time_graph(gk) - (time_graph(gs) if gs is not None else 0.0)
+
+        n_r = min(K, 400)
         ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(n_r)]
         big = torch.zeros(1 << 30, dtype=torch.uint8, device=dev)
         torch.cuda.synchronize()
@@ -238,57 +281,57 @@ def run_ours(args):
         torch.cuda.synchronize()
         g_us = sorted(e[0].elapsed_time(e[1]) * 1e3 for e in ev)
         t_us = sorted(e[1].elapsed_time(e[2]) * 1e3 for e in ev)
-        g_mean_us = sum(g_us) / len(g_us)
         del big
         ach = bytes_per_rec * B / (g_mean_us * 1e-6) / 1e9
         kname = "sample_gather_kernel" if fused else ("gather_tma_kernel" if args.gather_variant == 1 else "gather_vec_kernel")
         roofline = {"kernel": kname, "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
                     "frac": round(ach / peak, 4), "traffic": None, "algorithmic_bytes_per_launch": bytes_per_rec * B,
-                    "launch_us_mean": round(g_mean_us, 3), "launch_us_median": round(g_us[len(g_us) // 2], 3),
-                    "launch_us_min": round(g_us[0], 3), "launches_timed": len(g_us), "peak_source": peak_src,
-                    "other_kernels": {"td_small_kernel(K5+K2)_us_mean": round(sum(t_us) / len(t_us), 3)},
-                    "timing": "cuda events around each launch, eager pass of %d steps after the timed region" % n_r}
+                    "launch_us_mean": round(g_mean_us, 3), "launches_timed": R_ * reps, "peak_source": peak_src,
+                    "timing": "cuda events around %d replays of a CUDA graph of %d back-to-back launches "
+                              "(includes one inter-launch gap per launch)" % (reps, R_),
+                    "share_of_step": round(g_mean_us / (ms / K * 1e3), 3),
+                    "in_step_event_pairs": {"launch_us_mean": round(sum(g_us) / len(g_us), 3),
+                                            "launch_us_min": round(g_us[0], 3), "launches_timed": len(g_us),
+                                            "td_small_kernel_us_mean": round(sum(t_us) / len(t_us), 3),
+                                            "note": "event pair per launch inside an eager pass of the full step; "
+                                                    "inflated by event overhead"},
+                    "note": "ncu: DRAM sees 25.5 MB read + 0.3 MB written per launch (batch stays in L2); the launch is "
+                            "bound by L2 slice throughput, see profiles/r01_kernel_experiments.md"}
 
-    # ---- end to end through the public tensor API with HOST inputs and a host-read result
+    # ---- end to end through the host-facing API: draws and Q-values start in pinned HOST memory
+    # every step, loss / priorities / indices are read back on the host every step.
     e2e = None
     if world == 1:
         rng = np.random.default_rng(4321)
-        hu = torch.empty(B, dtype=torch.float64).pin_memory()
-        hq = torch.empty(3, B, nA).pin_memory()
-        hres = torch.empty(1 + 2 * B).pin_memory()                # loss_mean, priorities, indices (as f32 bits)
-        dq = torch.empty(3, B, nA, device=dev)
-        du = torch.empty(B, dtype=torch.float64, device=dev)
-        dres = torch.empty(1 + 2 * B, device=dev)
-        n_e = max(20, min(K, 500))
+        pipe = apex_b200.HostStepPipeline(mem, B, nA, use_graph=not args.no_graph)
+        n_e = max(20, min(K, 2000))
         q_host = rng.standard_normal((P, 3, B, nA)).astype(np.float32)
-        t0 = None
-        for k in range(-5, n_e):
-            if k == 0:
-                torch.cuda.synchronize()
-                t0 = time.perf_counter()
-            hu.numpy()[:] = (np.arange(B) + rng.random(B)) / B    # host-side stratified draws
-            hq.numpy()[:] = q_host[k % P]
-            du.copy_(hu, non_blocking=True)
-            dq.copy_(hq, non_blocking=True)
-            b = mem.sample_tensors(B, u=du)
-            mem.td_update(b.idx, dq[0], dq[1], dq[2], b.A, b.R, b.Gamma, out=td_out)
-            dres[0:1].copy_(td_out[3])
-            dres[1:1 + B].copy_(td_out[1])
-            dres[1 + B:].copy_(b.idx.view(torch.float32))
-            hres.copy_(dres, non_blocking=True)
-            torch.cuda.current_stream().synchronize()             # the host reads the step's result
-            _ = float(hres[0])
+        u_host = (np.arange(B) + rng.random((64, B))) / B         # host-side stratified draws
+        losses = 0.0
+        for k in range(8):
+            pipe.result(pipe.submit(u_host[k % 64], q_host[k % P]))
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        prev = None
+        for k in range(n_e):
+            t = pipe.submit(u_host[k % 64], q_host[k % P])        # fills the pinned inputs, one graph launch
+            if prev is not None:
+                losses += pipe.result(prev)[0]                    # host reads step k-1 while step k runs
+            prev = t
+        losses += pipe.result(prev)[0]
         dt = time.perf_counter() - t0
-        e2e = {"value": round(n_e * B / dt, 1), "unit": "transitions/s", "h2d_bytes_per_step": B * 8 + 3 * B * nA * 4,
-               "d2h_bytes_per_step": 4 * (1 + 2 * B), "steps": n_e, "ms_per_step": round(dt / n_e * 1e3, 4),
-               "api": "ReplayMemory.sample_tensors(u from pinned host) + td_update(Q from pinned host); "
-                      "loss/priorities/indices read back on the host every step"}
+        e2e = {"value": round(n_e * B / dt, 1), "unit": "transitions/s", "h2d_bytes_per_step": pipe.in_bytes,
+               "d2h_bytes_per_step": pipe.out_words * 4, "steps": n_e, "ms_per_step": round(dt / n_e * 1e3, 4),
+               "api": "apex_b200.HostStepPipeline.submit(u_host, q_host)/result(): pinned H2D of draws+Q, fused "
+                      "sample+gather, TD+update, D2H of loss/priorities/indices, one CUDA-graph launch per step, "
+                      "results read on the host one step behind (2 buffer sets)",
+               "mean_loss": round(losses / n_e, 6)}
     clk = clocks.stop()
     mem.check_status()
 
-    cpu = None
+    cpu, cpu_c = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_baseline_from_device(torch, mem, args, dev)
+        cpu, cpu_c = cpu_baseline_from_device(torch, mem, args, dev)
 
     if rank == 0:
         line = {
@@ -308,60 +351,106 @@ def run_ours(args):
                              % (N * F_BYTES / 1e9, N * 8 * 33 / 32 / 1e6),
                        "parallelism": "1 shard per GPU, NCCL all-gather of shard totals" if world > 1 else "single shard"},
             "gpu_launches": K * launches_per_step, "clocks": clk, "roofline": roofline, "e2e": e2e, "cpu_baseline": cpu,
+            "cpu_baseline_c_openmp": cpu_c,
         }
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
-def cpu_baseline_from_device(torch, mem, args, dev):
-    """The C/OpenMP oracle on the host cores, on the SAME shard contents (copied back from HBM)."""
-    from apex_b200 import _C
+class NumpyReplay:
+    """R-vec of BASELINE.md §3: the reference's own algorithm and libraries (numpy / torch-CPU),
+    vectorised over the batch — np.random.choice's cumsum + right-sided search (replay.py:24,52),
+    batch assembly (replay.py:54-56, learner.py:35-38), learner.py:43-52 arithmetic, dict-update
+    write-back (replay.py:40).  torch.index_select does the frame copies on all host threads;
+    numpy's cumsum / searchsorted are single-threaded by construction."""
+
+    def __init__(self, leaves, frames, fidx, A, R, G, C, alpha):
+        import torch
+        self.torch = torch
+        self.leaves, self.fidx, self.A, self.R, self.G, self.C, self.alpha = leaves, fidx, A, R, G, C, alpha
+        self.frames = torch.from_numpy(frames)
+        self.threads = torch.get_num_threads()
+
+    def step(self, u, q1, q2, q3):
+        from oracle import replay_oracle as ro, td_oracle as to
+        c = np.cumsum(self.leaves, dtype=np.uint64)
+        idx = np.searchsorted(c, ro.sample_target(u, int(c[-1])), side="right")
+        f = self.torch.from_numpy(self.fidx[idx].astype(np.int64))
+        S_t = self.torch.index_select(self.frames, 0, f[:, :self.C].reshape(-1))
+        S_tpn = self.torch.index_select(self.frames, 0, f[:, self.C:].reshape(-1))
+        o = to.td_forward(q1, q2, q3, self.A[idx], self.R[idx], self.G[idx], alpha=self.alpha)
+        self.leaves[idx] = ro.priority_to_leaf(o["prio"])
+        return idx, S_t, S_tpn, o
+
+
+def time_cpu(obj, B, nA, seconds, max_steps, rng):
+    from oracle import replay_oracle as ro
+    q = [rng.standard_normal((B, nA)).astype(np.float32) for _ in range(3)]
+    for _ in range(2):
+        obj.step(ro.stratified_uniforms(B, rng), *q)
+    t0, n = time.perf_counter(), 0
+    while True:
+        obj.step(ro.stratified_uniforms(B, rng), *q)
+        n += 1
+        dt = time.perf_counter() - t0
+        if dt > seconds or n >= max_steps:
+            return n, dt
+
+
+def cpu_baselines(leaves, frames, fidx, A, R, G, args, n_records):
+    """-> (cpu_baseline dict [numpy/torch port], extra dict [C/OpenMP port])."""
     from oracle.c_oracle import CpuReplay
+    C, B, nA = args.frames_per_state, args.batch, args.actions
+    rng = np.random.default_rng(7)
+    ref = NumpyReplay(leaves.copy(), frames, fidx, A, R, G, C, ALPHA)
+    n, dt = time_cpu(ref, B, nA, args.cpu_seconds * 0.6, 5000, rng)
+    base = {"value": round(n * B / dt, 1), "unit": "transitions/s", "cores": ref.threads, "kind": "port",
+            "sample": "%d steps of B=%d on a %d-record host-resident shard (%.1f s): numpy/torch-CPU restatement of the "
+                      "reference algorithm (u64 cumsum + right-sided searchsorted per np.random.choice, index_select "
+                      "frame copies on %d torch threads, learner.py TD math in numpy, fancy-index write-back)"
+                      % (n, B, n_records, dt, ref.threads),
+            "ms_per_step": round(dt / n * 1e3, 4)}
+    cpu = CpuReplay(leaves.copy(), frames, fidx, A, R, G, C, F_BYTES, ALPHA)
+    n2, dt2 = time_cpu(cpu, B, nA, args.cpu_seconds * 0.4, 5000, rng)
+    extra = {"value": round(n2 * B / dt2, 1), "unit": "transitions/s", "cores": cpu.threads, "kind": "port (optimised)",
+             "sample": "%d steps (%.1f s) of the same step hand-written in C with OpenMP on %d threads "
+                       "(oracle/apex_oracle.c): a stricter baseline than the reference's numpy path" % (n2, dt2, cpu.threads),
+             "ms_per_step": round(dt2 / n2 * 1e3, 4)}
+    return base, extra
+
+
+def cpu_baseline_from_device(torch, mem, args, dev):
+    """CPU baselines on the host cores, on the SAME shard contents (copied back from HBM)."""
+    from apex_b200 import _C
     from oracle import replay_oracle as ro
     try:
         import psutil
         avail = psutil.virtual_memory().available
     except Exception:
         avail = 0
-    N, C, B, nA = args.capacity, args.frames_per_state, args.batch, args.actions
+    N, C, B = args.capacity, args.frames_per_state, args.batch
     need = N * F_BYTES * 1.15
     if avail and avail < need + (8 << 30):
         return {"value": None, "unit": "transitions/s", "cores": os.cpu_count(), "kind": "port",
-                "sample": "skipped: host RAM %.0f GB < %.0f GB needed for the frame store" % (avail / 1e9, need / 1e9)}
+                "sample": "skipped: host RAM %.0f GB < %.0f GB needed for the frame store" % (avail / 1e9, need / 1e9)}, None
     frames = mem.buffer(_C.BUF_FRAMES).cpu().numpy().reshape(-1, F_BYTES)
     leaves = mem.buffer(_C.BUF_LEAVES).cpu().numpy().view(np.uint64).copy()
     fidx = mem.buffer(_C.BUF_FIDX).cpu().numpy().reshape(N, 2 * C)
     A, R, G = (mem.buffer(w).cpu().numpy() for w in (_C.BUF_ACTION, _C.BUF_REWARD, _C.BUF_GAMMA))
-    cpu = CpuReplay(leaves, frames, fidx, A, R, G, C, F_BYTES, ALPHA)
-    rng = np.random.default_rng(7)
-    q = [rng.standard_normal((B, nA)).astype(np.float32) for _ in range(3)]
     # parity at full size: GPU and CPU draw the same records from the same leaves for the same uniforms
-    u = ro.stratified_uniforms(B, rng)
+    u = ro.stratified_uniforms(B, np.random.default_rng(5))
     gpu_idx = mem.sample_indices(torch.as_tensor(u).to(dev)).cpu().numpy()
-    torch.cuda.synchronize()
     parity = bool((gpu_idx == ro.tree_sample(leaves, u)).all())
-    for _ in range(3):
-        cpu.step(ro.stratified_uniforms(B, rng), *q)
-    t0, n = time.perf_counter(), 0
-    while True:
-        cpu.step(ro.stratified_uniforms(B, rng), *q)
-        n += 1
-        dt = time.perf_counter() - t0
-        if dt > args.cpu_seconds or n >= 5000:
-            break
-    return {"value": round(n * B / dt, 1), "unit": "transitions/s", "cores": cpu.threads, "kind": "port",
-            "sample": "%d steps of B=%d on the same %d-record shard (%.1f s), oracle/apex_oracle.c with OpenMP on %d threads; "
-                      "per step: full u64 cumsum + right bisect (np.random.choice law) + frame memcpy + TD + leaf write-back"
-                      % (n, B, N, dt, cpu.threads),
-            "ms_per_step": round(dt / n * 1e3, 4), "index_parity_vs_gpu_at_full_size": parity}
+    base, extra = cpu_baselines(leaves, frames, fidx, A, R, G, args, N)
+    base["index_parity_vs_gpu_at_full_size"] = parity
+    return base, extra
 
 
 def run_reference(args):
-    """CPU arm: the reference's algorithm for the path (oracle port, all host threads); rank 0 only."""
+    """CPU arm: the reference's algorithm for the path (oracle port on the host cores); rank 0 only."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
-    from oracle.c_oracle import CpuReplay
     from oracle import replay_oracle as ro
     N, C, B, nA = args.capacity, args.frames_per_state, args.batch, args.actions
     try:
@@ -387,20 +476,23 @@ def run_reference(args):
     R = np.clip(rng.standard_normal(n_cpu), -1, 1).astype(np.float32)
     G = np.where(rng.random(n_cpu) < 0.01, 0, GAMMA_N).astype(np.float32)
     leaves = ro.priority_to_leaf(ro.pow_priority(np.abs(rng.standard_normal(n_cpu)) + 1e-3, ALPHA))
-    cpu = CpuReplay(leaves, frames, fidx, A, R, G, C, F_BYTES, ALPHA)
+    ref = NumpyReplay(leaves.copy(), frames, fidx, A, R, G, C, ALPHA)
     q = [[rng.standard_normal((B, nA)).astype(np.float32) for _ in range(3)] for _ in range(4)]
     W, K = max(args.warmup, 3), args.steps
     for k in range(W):
-        cpu.step(ro.stratified_uniforms(B, rng), *q[k % 4])
+        ref.step(ro.stratified_uniforms(B, rng), *q[k % 4])
     us = [ro.stratified_uniforms(B, rng) for _ in range(min(K, 256))]
     t0 = time.perf_counter()
     for k in range(K):
-        cpu.step(us[k % len(us)], *q[k % 4])
+        ref.step(us[k % len(us)], *q[k % 4])
     dt = time.perf_counter() - t0
     value = round(K * B / dt, 1)
-    sample = ("each step = one full B=%d step on a %d-record host-resident shard; oracle/apex_oracle.c "
-              "(reference algorithm restated in C: cumsum + bisect per np.random.choice, frame memcpy, learner.py TD math, "
-              "dict-update write-back) with OpenMP on %d threads" % (B, n_cpu, cpu.threads))
+    sample = ("each step = one full B=%d step on a %d-record host-resident shard; numpy/torch-CPU restatement of the reference "
+              "algorithm (u64 cumsum + right-sided searchsorted per np.random.choice, torch.index_select frame copies on %d "
+              "threads, learner.py TD math, fancy-index write-back); the literal reference is O(N^2) per update and cannot "
+              "run at this size (BASELINE.md §2)" % (B, n_cpu, ref.threads))
+    args.cpu_seconds = min(args.cpu_seconds, 10.0)
+    _, extra = cpu_baselines(leaves, frames, fidx, A, R, G, args, n_cpu)
     print(json.dumps({
         "impl": "reference", "metric": "prioritized sample+update transitions/s (2M cap, B=512)", "value": value,
         "unit": "transitions/s", "n_gpus": args.gpus, "steps": K, "warmup": W, "ms_per_step": round(dt / K * 1e3, 5),
@@ -408,7 +500,8 @@ def run_reference(args):
         "data": "synthetic",
         "config": {"workload": "replay microbench: %d-record shard, batch %d, C=%d 84x84 uint8 (CPU, host RAM)" % (n_cpu, B, C),
                    "capacity_per_gpu": n_cpu, "batch_per_gpu": B, "frames_per_state": C},
-        "cpu_baseline": {"value": value, "unit": "transitions/s", "cores": cpu.threads, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "transitions/s", "cores": ref.threads, "kind": "port", "sample": sample},
+        "cpu_baseline_c_openmp": extra,
         "e2e": {"value": value, "unit": "transitions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
