@@ -45,6 +45,9 @@ def parse():
     ap.add_argument("--no-graph", action="store_true", help="launch every step from Python instead of a CUDA graph")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the CPU-baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="replay", choices=["replay", "learner"],
+                    help="replay = BASELINE configs[1] microbench (default, the metric's workload); "
+                         "learner = configs[2]: the same loop with the duelling network fwd/bwd + RMSprop in it")
     return ap.parse_args()
 
 
@@ -153,6 +156,8 @@ def run_ours(args):
     u_table = ((torch.arange(Bg, device=dev, dtype=torch.float64) +
                 torch.rand(64, Bg, device=dev, dtype=torch.float64, generator=ugen)) / Bg) if world > 1 else None
     step_no = [0]
+    graph_steps = None
+    shard_out = mem._outputs(Bg, False) if world > 1 else None
 
     def step(k):
         q = qpool[k % P]
@@ -160,7 +165,7 @@ def run_ours(args):
             b = mem.sample_tensors(B, fused=fused)                # K3 (in-kernel stratified draws) + K4
             mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma, out=td_out)      # K5 + K2
         else:
-            b, _pos, cnt = sampler.sample(u_table[step_no[0] % 64])
+            b, _pos, cnt = sampler.sample(u_table[(step_no[0] if graph_steps is None else k) % 64], out=shard_out)
             mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma, out=td_out, count_dev=cnt, mean_divisor=float(Bg))
             step_no[0] += 1
 
@@ -169,12 +174,13 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    use_graph = (not args.no_graph) and world == 1
+    use_graph = not args.no_graph                                 # NCCL all-gather is captured too when world > 1
     for k in range(max(args.warmup, 3)):
         step(k)
     torch.cuda.synchronize()
     graph = None
     if use_graph:
+        graph_steps = P
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
@@ -507,9 +513,54 @@ def run_reference(args):
     }))
 
 
+def run_learner(args):
+    """BASELINE configs[2]: Ape-X learner loop, 2M-record replay, batch 512, n=3 double-DQN, 1 GPU.
+    Not the headline metric's workload; prints its own JSON line."""
+    import torch
+    import apex_b200
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda:0")
+    B, C, nA, N = args.batch, args.frames_per_state, args.actions, args.capacity
+    mem = apex_b200.ReplayMemory(N, {"priority_exponent": ALPHA, "layout": "stream", "lanes": args.lanes, "n_step": 3,
+                                     "state_shape": (C, 84, 84), "seed": 4321})
+    fill_shard(torch, apex_b200, mem, args, dev, 1234)
+    lp = {"remove_old_xp_freq": 100, "q_target_sync_freq": 2500, "min_replay_mem_size": 20000, "replay_sample_size": B,
+          "load_saved_state": False}
+    L = apex_b200.Learner({"state_shape": [C, 84, 84], "action_dim": nA}, lp, {}, mem)
+    for _ in range(max(args.warmup, 3)):
+        L.step_fast()
+    torch.cuda.synchronize()
+    K = min(args.steps, 300)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        loss = L.step_fast()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    # the data path alone inside the same loop
+    d0, d1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    q = [torch.randn(B, nA, device=dev) for _ in range(3)]
+    d0.record()
+    for _ in range(K):
+        b = mem.sample_tensors(B)
+        mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma)
+    d1.record()
+    torch.cuda.synchronize()
+    mem.check_status()
+    print(json.dumps({"metric": "Ape-X learner loop transitions/s (2M cap, B=512, duelling net fp32, 1 GPU)",
+                      "value": round(K * B / (ms * 1e-3), 1), "unit": "transitions/s", "n_gpus": 1, "steps": K,
+                      "ms_per_step": round(ms / K, 4), "data_path_ms_per_step_eager": round(d0.elapsed_time(d1) / K, 4),
+                      "final_loss": float(loss), "higher_is_better": True, "data": "synthetic",
+                      "config": {"workload": "learner loop: sample+gather -> 3 forwards + backward + RMSprop (PyTorch/cuDNN fp32) -> "
+                                             "fused TD/priority update", "model": "duelling conv net 3.33M params (unchanged)"}}))
+
+
 if __name__ == "__main__":
     a = parse()
     if a.impl == "reference":
         run_reference(a)
+    elif a.workload == "learner":
+        run_learner(a)
     else:
         run_ours(a)

@@ -1,0 +1,112 @@
+#!/usr/bin/env python
+"""Multi-GPU parity check, one process per GPU (not collected by pytest):
+
+    torchrun --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 tests/multi_gpu_check.py
+
+Every rank owns a shard; the sharded sampler (NCCL all-gather of shard totals + K8 routing +
+local K3/K4/K5/K2) must return, over all ranks together, exactly the records a single tree
+over the concatenated shards returns for the same draws, byte-exact batches, and a loss whose
+sum over ranks equals the single-batch mean.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import apex_b200                                   # noqa: E402
+from apex_b200 import _C                           # noqa: E402
+from oracle import replay_oracle as ro             # noqa: E402
+from oracle import td_oracle as to                 # noqa: E402
+
+
+def shard_data(rank, n, C, F, lanes):
+    rng = np.random.default_rng(500 + rank)
+    W = C - 1 + 3
+    ring = ro.RingOracle(n, C, F, lanes=lanes, fpr=1, lookback=W, alpha=0.6)
+    ops = []
+    for lane in range(lanes):
+        m = n // lanes - W
+        frames = rng.integers(0, 256, (m, F), dtype=np.uint8)
+        rel = apex_b200.stream_offsets(C, np.full(m, 3), np.minimum(np.arange(m), 500))
+        A = rng.integers(0, 4, m).astype(np.int32)
+        R = rng.standard_normal(m).astype(np.float32)
+        G = np.full(m, 0.97, np.float32)
+        prio = (np.abs(rng.standard_normal(m)) * (1 + rank) + 1e-3).astype(np.float32)
+        ring.insert(lane, frames, rel, A, R, G, prio=prio)
+        ops.append((lane, frames, rel, A, R, G, prio))
+    return ring, ops
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    n, C, F, lanes, Bg, nA = 1 << 14, 2, 256, 4, 256 * world, 4
+    rings = [shard_data(r, n, C, F, lanes) for r in range(world)]            # every rank can rebuild every shard
+    ring, ops = rings[rank]
+    mem = apex_b200.ReplayMemory(n, {"priority_exponent": 0.6, "layout": "stream", "lanes": lanes, "n_step": 3,
+                                     "state_shape": (C, 1, F)})
+    for op in ops:
+        mem.insert(*op[:6], prio=op[6])
+    # identical leaves on both sides: take the device's (the fp32 pow is a separate, toleranced item)
+    leaves_local = mem.buffer(_C.BUF_LEAVES).cpu().numpy().view(np.uint64).copy()
+    all_leaves = [torch.zeros(n, dtype=torch.int64, device=dev) for _ in range(world)]
+    dist.all_gather(all_leaves, torch.as_tensor(leaves_local.view(np.int64)).to(dev))
+    all_leaves = [t.cpu().numpy().view(np.uint64) for t in all_leaves]
+    for r in range(world):
+        rings[r][0].leaves[:] = all_leaves[r]
+    sampler = apex_b200.ShardedSampler(mem)
+    ok = True
+    rng = np.random.default_rng(9)                                           # same draws on every rank
+    for step in range(4):
+        u = ro.stratified_uniforms(Bg, rng) if step % 2 else rng.random(Bg)
+        batch, pos, cnt = sampler.sample(torch.as_tensor(u).to(dev))
+        cnt_h = int(cnt.item())
+        whole = ro.tree_sample(np.concatenate([rings[r][0].leaves for r in range(world)]), u)
+        mine = np.nonzero(whole // n == rank)[0]
+        ok &= cnt_h == len(mine) and (pos.cpu().numpy()[:cnt_h] == mine).all()
+        local_idx = batch.idx.cpu().numpy()[:cnt_h]
+        ok &= (local_idx == whole[mine] % n).all()
+        g = ring.gather(local_idx)
+        ok &= (batch.S_t.cpu().numpy()[:cnt_h] == g["S_t"]).all() and (batch.S_tpn.cpu().numpy()[:cnt_h] == g["S_tpn"]).all()
+        ok &= (batch.A.cpu().numpy()[:cnt_h] == g["A"]).all()
+        # K5+K2 on the local rows; loss_mean divided by the GLOBAL batch so that the sum over ranks is the mean
+        qrng = np.random.default_rng(1000 + step)
+        qg = [qrng.standard_normal((Bg, nA)).astype(np.float32) for _ in range(3)]          # one Q row per global draw
+        q = [torch.as_tensor(np.concatenate([x[mine], np.zeros((Bg - cnt_h, nA), np.float32)])).to(dev) for x in qg]
+        delta, prio, loss, mean = mem.td_update(batch.idx, q[0], q[1], q[2], batch.A, batch.R, batch.Gamma,
+                                                count_dev=cnt, mean_divisor=float(Bg))
+        total_loss = mean.clone()
+        dist.all_reduce(total_loss)
+        # oracle: the whole global batch at once
+        gl = [rings[int(i // n)][0] for i in whole]
+        A_g = np.array([r_.A[i % n] for r_, i in zip(gl, whole)])
+        R_g = np.array([r_.R[i % n] for r_, i in zip(gl, whole)])
+        G_g = np.array([r_.G[i % n] for r_, i in zip(gl, whole)])
+        o = to.td_forward(qg[0], qg[1], qg[2], A_g, R_g, G_g, alpha=0.6)
+        ok &= abs(total_loss.item() - o["loss_mean"]) <= 1e-5 * abs(o["loss_mean"]) + 1e-7
+        ok &= np.allclose(prio.cpu().numpy()[:cnt_h], o["prio"][mine], rtol=1e-5, atol=1e-7)
+        # write the same priorities into the oracle shard (last writer wins) and compare shard totals
+        ring.set_leaves(local_idx, ro.priority_to_leaf(prio.cpu().numpy()[:cnt_h]))
+        ok &= mem.total() == ring.total()
+        new_leaves = [torch.zeros(n, dtype=torch.int64, device=dev) for _ in range(world)]
+        dist.all_gather(new_leaves, torch.as_tensor(ring.leaves.view(np.int64)).to(dev))
+        for r in range(world):
+            rings[r][0].leaves[:] = new_leaves[r].cpu().numpy().view(np.uint64)
+    mem.check_status()
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print("multi_gpu_check world=%d: %s" % (world, "PASS" if flag.item() == 1 else "FAIL"))
+    dist.destroy_process_group()
+    sys.exit(0 if flag.item() == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -571,3 +571,58 @@ def test_full_size_properties_2m(apex):
     for gl, w in zip(read_levels(apex, mem), ro.build_levels(leaves)):
         np.testing.assert_array_equal(gl, w)
     mem.check_status()
+
+
+# ------------------------------------------------------------ a8/a9: Learner mirror
+def _small_learner(apex, mem, B=32, C_=1):
+    lp = {"remove_old_xp_freq": 100, "q_target_sync_freq": 3, "min_replay_mem_size": 10, "replay_sample_size": B,
+          "load_saved_state": False}
+    torch.manual_seed(0)
+    return apex.Learner({"state_shape": [C_, 84, 84], "action_dim": 4}, lp, {}, mem)
+
+
+def test_learner_compat_and_fast_tier(apex):
+    """learner.py:29-61 through the mirror class: compat records in -> (loss, {key: |delta|}); fast tier
+    sample -> model -> fused TD + in-place priority update -> RMSprop step."""
+    rng = np.random.default_rng(31)
+    NT = apex.N_Step_Transition
+    K = 200
+    mem = apex.ReplayMemory(K, {"priority_exponent": 0.6})
+    S = rng.integers(0, 256, (K + 1, 1, 84, 84)).astype(np.uint8)
+    recs = [NT(S[i], int(rng.integers(4)), float(rng.standard_normal()), 0.97, None, S[i + 1], None, "1%d" % i) for i in range(K)]
+    mem.add({r.key: 1.0 + i % 3 for i, r in enumerate(recs)}, recs)
+    L = _small_learner(apex, mem)
+    np.random.seed(3)
+    batch = mem.sample(32)
+    loss, prios = L.compute_loss_and_priorities(batch)                      # learner.py:70
+    assert loss.requires_grad and set(prios) == {r.key for r in batch}
+    # the same numbers from plain torch on the same networks (learner.py:43-52 restated in fp32)
+    St = torch.from_numpy(np.stack([r.S_t for r in batch])).cuda().float()
+    Sn = torch.from_numpy(np.stack([r.S_tpn for r in batch])).cuda().float()
+    A = torch.tensor([r.A_t for r in batch], device="cuda")
+    R = torch.tensor([r.R_ttpB for r in batch], device="cuda", dtype=torch.float32)
+    G = torch.tensor([r.Gamma_ttpB for r in batch], device="cuda", dtype=torch.float32)
+    with torch.no_grad():
+        tgt = R + G * L.Q_double(Sn)[2].gather(1, torch.argmax(L.Q(Sn)[2], 1).view(-1, 1)).squeeze()
+    qsa = L.Q(St)[2].gather(1, A.view(-1, 1)).squeeze()
+    ref = (0.5 * (tgt - qsa) ** 2).mean()
+    torch.testing.assert_close(loss, ref, rtol=1e-4, atol=1e-6)
+    want = (tgt - qsa).abs().detach().cpu().numpy()
+    for j, r in enumerate(batch):                                           # per-record |delta| (SURVEY Q12), last dup wins
+        if [x.key for x in batch].index(r.key) == j and [x.key for x in batch].count(r.key) == 1:
+            assert prios[r.key] == pytest.approx(want[j], rel=1e-4, abs=1e-6)
+    g_ref = torch.autograd.grad(ref, list(L.Q.parameters()), allow_unused=True)
+    L.optimizer.zero_grad()
+    loss.backward()
+    for p, g in zip(L.Q.parameters(), g_ref):                               # cuDNN backward is not bit-reproducible
+        torch.testing.assert_close(p.grad, g, rtol=2e-2, atol=1e-3)
+    L.update_Q(L.compute_loss_and_priorities(batch)[0])                     # learner.py:73
+    mem.set_priorities(prios)                                               # learner.py:76
+    assert L.num_q_updates == 1
+    # fast tier: the batch never leaves HBM, priorities are written in place
+    before = mem.total()
+    losses = [float(L.step_fast()) for _ in range(5)]
+    assert L.num_q_updates == 6 and all(np.isfinite(losses)) and mem.total() != before
+    sd_q, sd_t = L.Q.state_dict(), L.Q_double.state_dict()
+    assert all(torch.equal(sd_q[k], sd_t[k]) for k in sd_q)                 # target sync at update 6 (freq 3)
+    mem.check_status()
