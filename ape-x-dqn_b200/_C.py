@@ -14,7 +14,8 @@ LIB_PATH = os.path.join(_HERE, "libapexb200.so")
 
 OK, EINVAL, ECUDA, ENOMEM, ERANGE = 0, -1, -2, -3, -4
 LOSS_HALF_SQ, LOSS_HUBER = 0, 1
-ST_EMPTY_TREE, ST_BAD_INDEX, ST_BAD_TARGET, ST_BAD_ACTION = 1, 2, 4, 8
+ST_EMPTY_TREE, ST_BAD_INDEX, ST_BAD_TARGET, ST_BAD_ACTION, ST_PEER_TIMEOUT, ST_QUOTA = 1, 2, 4, 8, 16, 32
+IPC_HANDLE_BYTES = 64
 FRAC_BITS = 24
 LEAF_MAX = (1 << 36) - 1
 MAX_CAPACITY = 1 << 24
@@ -70,6 +71,10 @@ SIGNATURES = {
     "apexb200_nstep": [_P, _P, _I32, _I32, _I32, _F, _P, _P, _P, _P],
     "apexb200_initial_priority": [_P, _P, _P, _P, _P, _I32, _I32, _P, _P],
     "apexb200_shard_targets": [_P, _I32, _I32, _P, _I32, _P, _P, _P, _P],
+    "apexb200_peer_export": [_P, _P],
+    "apexb200_peer_connect": [_P, _I32, _I32, _P],
+    "apexb200_shard_exchange": [_P, _P, _P],
+    "apexb200_sample_gather_sharded": [_P, C.c_uint64, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "apexb200_replay_buffer": [_P, _I32, C.POINTER(_P), C.POINTER(_I64)],
     "apexb200_replay_get_heads": [_P, C.POINTER(_I64)],
     "apexb200_replay_set_heads": [_P, C.POINTER(_I64)],

@@ -22,6 +22,15 @@ struct TreeView {
     int n_levels;
 };
 
+// Peer-mapped exchange buffers of a group of shards (one per GPU).  xbuf[g] is rank g's
+// buffer as seen from this GPU (own allocation for g == rank, a CUDA-IPC mapping over
+// NVLink otherwise).  Layout: u64 [2 slots][kMaxShards], one word = total << 4 | round & 15.
+constexpr int kMaxShards = 16;
+struct PeerView {
+    unsigned long long *xbuf[kMaxShards];
+    int world, rank;
+};
+
 struct RingView {
     uint8_t *frames;          // [N * fpr, F]
     int32_t *fidx;            // [N, 2C]   absolute frame slots of S_t (C) then S_tpn (C)
@@ -95,7 +104,14 @@ __device__ __forceinline__ float prio_pow(float abs_td, float alpha, float eps) 
     return powf(b, alpha);
 }
 
-// Device control block of a handle: int32 words [0] status, [4..5] u64 update epoch.
+// Device control block of a handle: int32 words [0] status, [4..5] u64 update epoch,
+// [6..7] u64 exchange round, [16..47] u64 totals[kMaxShards] of the last exchange.
+__device__ __forceinline__ unsigned long long read_round(const int32_t *ctrl) {
+    return *(const volatile unsigned long long *)(ctrl + 6);
+}
+__device__ __forceinline__ const unsigned long long *exchanged_totals(const int32_t *ctrl) {
+    return (const unsigned long long *)(ctrl + 16);
+}
 __device__ __forceinline__ unsigned long long read_epoch(const int32_t *ctrl) {
     return *(const volatile unsigned long long *)(ctrl + 4);
 }
@@ -187,7 +203,10 @@ struct apexb200_replay {
     apexb200::RingView ring;
     void *tree_block = nullptr;        // one allocation for all levels
     uint32_t *stamp = nullptr;         // [N] duplicate-resolution stamps (K2); all zero between calls
-    int32_t *status = nullptr;         // device control block: [0] status word, [4..5] u64 update epoch
+    int32_t *status = nullptr;         // device control block (256 B), see read_epoch / read_round
+    unsigned long long *xbuf = nullptr; // this shard's exchange buffer (peers write into it)
+    apexb200::PeerView peers;          // xbuf of every rank; world = 1, xbuf[0] = own until peer_connect
+    void *opened[apexb200::kMaxShards] = {};   // IPC mappings to close
     unsigned long long draw_calls = 0; // host: stratified-draw calls issued (the `call` of strat_uniform)
     std::vector<long long> lane_count; // host ring heads
     int64_t device_bytes = 0;

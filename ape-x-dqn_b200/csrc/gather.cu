@@ -257,9 +257,112 @@ sample_gather_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int
     tma_drain_frames(moving, moving ? item_dst(rv, ga, w, lane) : nullptr, stage, my_bars, (unsigned)rv.F, nch);
 }
 
+// ---- fused K8 + K3 + K4 for one rank of a sharded replay (after shard_exchange_kernel).
+// Rows are dealt to CTAs round-robin (row = cta + k * gridDim.x) so that the live rows —
+// the first `count` of max_rows — spread over every CTA.
+struct ShardArgs {
+    unsigned long long seed, call;
+    int global_count, max_rows;
+    int32_t *pos_out, *count_out;
+};
+
+// target of global draw j: min(trunc(u_j * double(T)), T - 1); non-decreasing in j.
+__device__ __forceinline__ unsigned long long draw_target(unsigned long long seed, unsigned long long round,
+                                                          unsigned long long call, int j, int Bg,
+                                                          unsigned long long T, double *u_out) {
+    const double u = strat_uniform(seed, round, call, j, Bg);
+    if (u_out) *u_out = u;
+    unsigned long long t = (unsigned long long)(u * (double)T);
+    return t >= T ? T - 1ull : t;
+}
+
+// Smallest j in [0, Bg] whose target is >= bound (Bg if none): 32-ary search, every lane
+// evaluates one candidate per round.
+__device__ __forceinline__ int first_draw_at_or_above(unsigned long long bound, unsigned long long seed,
+                                                      unsigned long long round, unsigned long long call, int Bg,
+                                                      unsigned long long T) {
+    const int lane = threadIdx.x & 31;
+    int lo = 0, hi = Bg;                       // answer in [lo, hi]
+    while (lo < hi) {
+        const int span = hi - lo;
+        const int step = (span + 31) >> 5;     // candidates lo + (i+1)*step - 1, i = 0..31
+        const int j = lo + (lane + 1) * step - 1;
+        const bool ge = (j >= hi) || draw_target(seed, round, call, j, Bg, T, nullptr) >= bound;
+        const unsigned m = __ballot_sync(0xffffffffu, ge);
+        const int f = m ? __ffs(m) - 1 : 32;   // no vote: every candidate is below the bound and below hi
+        const int new_hi = min(hi, lo + (f + 1) * step - 1);
+        lo = lo + f * step;
+        hi = new_hi;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(256)
+sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, ShardArgs sh, int world, int rank,
+                             int32_t *ctrl) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    unsigned long long *bars = (unsigned long long *)smem;
+    pdl_prologue();
+    const int lane = threadIdx.x & 31;
+    const int wl = threadIdx.x >> 5;
+    const int wpc = blockDim.x >> 5;
+    const int nch = frame_chunks(rv.F);
+    const int row = blockIdx.x + wl * gridDim.x;
+    const int twoC = 2 * rv.C;
+    if (row >= sh.max_rows) return;
+    const unsigned long long vtop = top_level_value(tv);
+    // totals of the last exchange -> global total T and this rank's prefix interval [lo, hi)
+    unsigned long long tg = lane < world ? exchanged_totals(ctrl)[lane] : 0ull, incl = tg;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned long long n = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += n;
+    }
+    const unsigned long long T = __shfl_sync(0xffffffffu, incl, 31);
+    const unsigned long long hi = __shfl_sync(0xffffffffu, incl, rank);
+    const unsigned long long lo = hi - __shfl_sync(0xffffffffu, tg, rank);
+    const unsigned long long round = read_round(ctrl);
+    if (T == 0ull) {
+        if (lane == 0) { atomicOr(ctrl, APEXB200_ST_EMPTY_TREE); if (row == 0) *sh.count_out = 0; }
+        return;
+    }
+    const int Bg = sh.global_count;
+    const int j_lo = first_draw_at_or_above(lo, sa.seed, round, sh.call, Bg, T);
+    if (row == 0) {
+        const int j_hi = first_draw_at_or_above(hi, sa.seed, round, sh.call, Bg, T);
+        int cnt = j_hi - j_lo;
+        if (cnt > sh.max_rows) { cnt = sh.max_rows; if (lane == 0) atomicOr(ctrl, APEXB200_ST_QUOTA); }
+        if (lane == 0) *sh.count_out = cnt;
+    }
+    const int j = j_lo + row;
+    if (j >= Bg) return;
+    double uw;
+    const unsigned long long t = draw_target(sa.seed, round, sh.call, j, Bg, T, &uw);
+    if (t >= hi) return;                                     // beyond this rank's run of draws
+    unsigned long long leaf, total;
+    const long long node = warp_descend(tv, vtop, t - lo, false, 0.0, &leaf, &total, ctrl);
+    uint8_t *stage = smem + (size_t)wpc * 16 * kMaxChunks * 8 + (size_t)(wl * twoC + lane) * rv.F;
+    unsigned long long *my_bars = bars + (wl * 16 + lane) * kMaxChunks;
+    long long f = -1;
+    if (node >= 0 && lane < twoC) f = rv.fidx[node * twoC + lane];
+    bool moving = false;
+    if (node >= 0 && lane < twoC) {
+        if (f < 0 || f >= rv.N * rv.fpr) atomicOr(ctrl, APEXB200_ST_BAD_INDEX);
+        else { moving = true; tma_load_frame(rv.frames + f * rv.F, stage, my_bars, (unsigned)rv.F, nch); }
+    }
+    if (lane < twoC && sa.fsel_out) sa.fsel_out[(long long)row * twoC + lane] = (int32_t)f;
+    if (lane == 0) {
+        sa.idx_out[row] = (int32_t)node;
+        if (sh.pos_out) sh.pos_out[row] = j;
+        if (sa.u_out) sa.u_out[row] = uw;
+    }
+    if (node >= 0 && lane == 16) copy_meta_row(rv, ga, row, node);
+    tma_drain_frames(moving, moving ? item_dst(rv, ga, row, lane) : nullptr, stage, my_bars, (unsigned)rv.F, nch);
+}
+
 static int ensure_smem(const void *fn, size_t smem, int device) {
-    static size_t configured[2][64] = {};
-    const int which = (fn == (const void *)gather_tma_kernel) ? 0 : 1;
+    static size_t configured[3][64] = {};
+    const int which = (fn == (const void *)gather_tma_kernel) ? 0 : (fn == (const void *)sample_gather_kernel) ? 1 : 2;
     if (smem > 48 * 1024 && device >= 0 && device < 64 && smem > configured[which][device]) {
         APEX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[which][device] = smem;
@@ -340,6 +443,33 @@ int apexb200_sample_gather(apexb200_replay_t h, const double *u, uint64_t seed, 
     GatherArgs ga{idx_out, fsel_out, nullptr, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, count};
     return launch_step("sample_gather_kernel", sample_gather_kernel, dim3((unsigned)((count + wpc - 1) / wpc)),
                        dim3(wpc * 32), smem, st, h->tree, rv, sa, ga, h->status);
+}
+
+int apexb200_sample_gather_sharded(apexb200_replay_t h, uint64_t seed, int32_t global_count, int32_t max_rows,
+                                   int32_t *idx_out, int32_t *fsel_out, int32_t *pos_out, double *u_out,
+                                   int32_t *count_out, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R,
+                                   float *Gamma, float *q_t, float *q_tpn, void *stream) {
+    APEX_REQUIRE(h && global_count > 0 && max_rows > 0, APEXB200_EINVAL, "sample_gather_sharded: bad argument");
+    APEX_REQUIRE(idx_out && count_out && S_t && S_tpn, APEXB200_EINVAL, "sample_gather_sharded: null output");
+    APEX_REQUIRE((((uintptr_t)S_t | (uintptr_t)S_tpn) & 15) == 0, APEXB200_EINVAL,
+                 "sample_gather_sharded: output batches must be 16-byte aligned");
+    const RingView &rv = h->ring;
+    const size_t per_draw = (size_t)2 * rv.C * rv.F + 16 * kMaxChunks * 8;
+    APEX_REQUIRE(2 * rv.C <= 16 && per_draw <= kStageBudget, APEXB200_ERANGE,
+                 "sample_gather_sharded: a record (2*%d frames of %d bytes) does not fit one CTA's staging", rv.C, rv.F);
+    int wpc = (int)(kStageBudget / per_draw);
+    if (wpc > 8) wpc = 8;
+    const int spread = (max_rows + kNumSMs - 1) / kNumSMs;
+    if (spread < wpc) wpc = spread;
+    const int ctas = (max_rows + wpc - 1) / wpc;
+    const size_t smem = (size_t)wpc * per_draw;
+    int rc = ensure_smem((const void *)sample_gather_sharded_kernel, smem, h->cfg.device);
+    if (rc) return rc;
+    SampleArgs sa{nullptr, (unsigned long long)seed, 0ull, idx_out, fsel_out, nullptr, nullptr, u_out};
+    GatherArgs ga{idx_out, fsel_out, nullptr, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, max_rows};
+    ShardArgs sh{(unsigned long long)seed, h->draw_calls++, global_count, max_rows, pos_out, count_out};
+    return launch_step("sample_gather_sharded_kernel", sample_gather_sharded_kernel, dim3((unsigned)ctas), dim3(wpc * 32),
+                       smem, (cudaStream_t)stream, h->tree, rv, sa, ga, sh, h->peers.world, h->peers.rank, h->status);
 }
 
 }  // extern "C"

@@ -185,6 +185,7 @@ int apexb200_replay_create(apexb200_replay_t *out, const apexb200_replay_config 
     bool ok = alloc(&h->tree_block, (size_t)padded_total * 8, true) &&
               alloc((void **)&h->stamp, (size_t)N * 4, true) &&
               alloc((void **)&h->status, 256, true) &&
+              alloc((void **)&h->xbuf, 2 * kMaxShards * 2 * 8, true) &&
               alloc((void **)&rv.frames, (size_t)N * rv.fpr * rv.F, false) &&
               alloc((void **)&rv.fidx, (size_t)N * 2 * C * 4, true) &&
               alloc((void **)&rv.A, (size_t)N * 4, true) &&
@@ -194,6 +195,10 @@ int apexb200_replay_create(apexb200_replay_t *out, const apexb200_replay_config 
         ok = alloc((void **)&rv.q_t, (size_t)N * nA * 4, true) && alloc((void **)&rv.q_tpn, (size_t)N * nA * 4, true);
     if (!ok) { apexb200_replay_destroy(h); return rc; }
     for (int l = 0; l < nl; ++l) tv.lvl[l] = (unsigned long long *)h->tree_block + offs[l];
+    memset(&h->peers, 0, sizeof(h->peers));
+    h->peers.world = 1;
+    h->peers.rank = 0;
+    h->peers.xbuf[0] = h->xbuf;
     *out = h;
     return APEXB200_OK;
 }
@@ -201,7 +206,8 @@ int apexb200_replay_create(apexb200_replay_t *out, const apexb200_replay_config 
 int apexb200_replay_destroy(apexb200_replay_t h) {
     if (!h) return APEXB200_OK;
     cudaSetDevice(h->cfg.device);
-    void *ptrs[] = {h->tree_block, h->stamp, h->status, h->ring.frames, h->ring.fidx, h->ring.A,
+    for (void *m : h->opened) if (m) cudaIpcCloseMemHandle(m);
+    void *ptrs[] = {h->xbuf, h->tree_block, h->stamp, h->status, h->ring.frames, h->ring.fidx, h->ring.A,
                     h->ring.R, h->ring.G, h->ring.q_t, h->ring.q_tpn};
     for (void *p : ptrs) if (p) cudaFree(p);
     delete h;
@@ -264,6 +270,39 @@ int apexb200_replay_insert(apexb200_replay_t h, int32_t lane, int32_t count, con
     rc = launch_check("insert_meta_kernel");
     if (rc) return rc;
     h->lane_count[lane] += count;
+    return APEXB200_OK;
+}
+
+int apexb200_peer_export(apexb200_replay_t h, void *ipc_handle_host) {
+    APEX_REQUIRE(h && ipc_handle_host, APEXB200_EINVAL, "peer_export: null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == APEXB200_IPC_HANDLE_BYTES, "IPC handle size");
+    APEX_CUDA(cudaSetDevice(h->cfg.device));
+    cudaIpcMemHandle_t hd;
+    APEX_CUDA(cudaIpcGetMemHandle(&hd, h->xbuf));
+    memcpy(ipc_handle_host, &hd, sizeof(hd));
+    return APEXB200_OK;
+}
+
+int apexb200_peer_connect(apexb200_replay_t h, int32_t rank, int32_t world, const void *ipc_handles_host) {
+    APEX_REQUIRE(h && ipc_handles_host, APEXB200_EINVAL, "peer_connect: null argument");
+    APEX_REQUIRE(world >= 1 && world <= kMaxShards && rank >= 0 && rank < world, APEXB200_ERANGE,
+                 "peer_connect: rank %d / world %d outside [1, %d]", rank, world, kMaxShards);
+    APEX_CUDA(cudaSetDevice(h->cfg.device));
+    for (void *&m : h->opened) if (m) { cudaIpcCloseMemHandle(m); m = nullptr; }
+    PeerView pv;
+    memset(&pv, 0, sizeof(pv));
+    pv.world = world;
+    pv.rank = rank;
+    for (int g = 0; g < world; ++g) {
+        if (g == rank) { pv.xbuf[g] = h->xbuf; continue; }
+        cudaIpcMemHandle_t hd;
+        memcpy(&hd, (const char *)ipc_handles_host + (size_t)g * sizeof(hd), sizeof(hd));
+        void *p = nullptr;
+        APEX_CUDA(cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess));
+        h->opened[g] = p;
+        pv.xbuf[g] = (unsigned long long *)p;
+    }
+    h->peers = pv;
     return APEXB200_OK;
 }
 

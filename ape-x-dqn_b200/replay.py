@@ -406,7 +406,9 @@ class ReplayMemory(object):
         _C.call("apexb200_replay_status", self._h, C.byref(st), self._stream())
         if st.value:
             names = [n for bit, n in ((1, "sample on empty tree"), (2, "record/frame index out of range"),
-                                      (4, "target beyond tree total"), (8, "action out of range")) if st.value & bit]
+                                      (4, "target beyond tree total"), (8, "action out of range"),
+                                      (16, "peer exchange timed out"), (32, "shard quota exceeded (max_rows)"))
+                     if st.value & bit]
             raise _C.ApexError(_C.EINVAL, "device status: " + ", ".join(names))
 
     def buffer(self, which):

@@ -42,6 +42,50 @@ class ShardedSampler:
         """-> (local_targets [Bg], local_pos [Bg], local_count [1]) for this rank; identical u on every rank."""
         return self._route(self.gather_totals(), self.rank, u_global)
 
+    # ---- peer-memory path: no NCCL call, no host round trip on the per-step path -----------
+    def connect_peers(self):
+        """Exchange CUDA-IPC handles of the shards' exchange buffers (once, at start-up) and map
+        every peer's buffer.  Collective over the group."""
+        import ctypes as C
+        from . import _C
+        self.mem._ensure()
+        mine = (C.c_ubyte * _C.IPC_HANDLE_BYTES)()
+        _C.call("apexb200_peer_export", self.mem._h, mine)
+        handles = [None] * self.world
+        if self.world > 1:
+            dist.all_gather_object(handles, bytes(mine), group=self.group)
+        else:
+            handles = [bytes(mine)]
+        blob = (C.c_ubyte * (_C.IPC_HANDLE_BYTES * self.world)).from_buffer_copy(b"".join(handles))
+        _C.call("apexb200_peer_connect", self.mem._h, int(self.rank), int(self.world), blob)
+        if self.world > 1:
+            dist.barrier(group=self.group)
+        self.connected = True
+
+    def exchange(self, totals_out=None):
+        """One-launch all-gather of the shard totals over peer memory (collective: every rank
+        calls it once per step, before sample_fused)."""
+        from . import _C
+        _C.call("apexb200_shard_exchange", self.mem._h, _C.ptr(totals_out), _C.stream_ptr())
+
+    def sample_fused(self, global_count, max_rows, with_q=False, u_out=None):
+        """Fused routing + search + gather of this rank's share of `global_count` stratified draws
+        generated in the kernel (identical on every rank).  Returns (Batch over max_rows rows,
+        pos [max_rows] global draw index per row, count [1] rows owned)."""
+        import torch
+        from . import _C
+        from .replay import Batch
+        mem = self.mem
+        o = mem._outputs(int(max_rows), with_q)
+        if "pos" not in o:
+            o["pos"] = torch.empty(int(max_rows), dtype=torch.int32, device=mem.device)
+            o["count"] = torch.zeros(1, dtype=torch.int32, device=mem.device)
+        _C.call("apexb200_sample_gather_sharded", mem._h, mem.seed, int(global_count), int(max_rows), _C.ptr(o["idx"]),
+                _C.ptr(o["fsel"]), _C.ptr(o["pos"]), _C.ptr(u_out), _C.ptr(o["count"]), _C.ptr(o["S_t"]),
+                _C.ptr(o["S_tpn"]), _C.ptr(o["A"]), _C.ptr(o["R"]), _C.ptr(o["Gamma"]), _C.ptr(o.get("q_t")),
+                _C.ptr(o.get("q_tpn")), _C.stream_ptr())
+        return Batch(o["idx"], o["S_t"], o["S_tpn"], o["A"], o["R"], o["Gamma"], o["fsel"]), o["pos"], o["count"]
+
     def sample(self, u_global, out=None, with_q=False):
         """Global draws -> this rank's part of the batch (rows beyond local_count are stale)."""
         lt, lp, lc = self.route(u_global)

@@ -45,6 +45,9 @@ def parse():
     ap.add_argument("--no-graph", action="store_true", help="launch every step from Python instead of a CUDA graph")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the CPU-baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--nccl-exchange", action="store_true",
+                    help="multi-GPU: all-gather the shard totals with NCCL + separate routing/search/gather kernels "
+                         "instead of the peer-memory exchange + fused sharded kernel")
     ap.add_argument("--workload", default="replay", choices=["replay", "learner"],
                     help="replay = BASELINE configs[1] microbench (default, the metric's workload); "
                          "learner = configs[2]: the same loop with the duelling network fwd/bwd + RMSprop in it")
@@ -149,9 +152,15 @@ def run_ours(args):
 
     gen = torch.Generator(device=dev).manual_seed(99 + rank)
     P = 4                                                         # pool of Q-value inputs, cycled
-    qpool = [[torch.randn(Bg, nA, device=dev, generator=gen) for _ in range(3)] for _ in range(P)]
-    td_out = tuple(torch.empty(Bg, device=dev) for _ in range(3)) + (torch.empty(1, device=dev),)
+    rows = B if world == 1 else (max(148 * ((B * 9 // 8 + 147) // 148), 148) if not args.nccl_exchange else Bg)
+    qpool = [[torch.randn(rows, nA, device=dev, generator=gen) for _ in range(3)] for _ in range(P)]
+    td_out = tuple(torch.empty(rows, device=dev) for _ in range(3)) + (torch.empty(1, device=dev),)
     sampler = apex_b200.ShardedSampler(mem, rank=rank, world_size=world) if world > 1 else None
+    peer_path = world > 1 and not args.nccl_exchange
+    # per-rank quota of the global batch: one CTA per SM, 4 rows each (592 rows for B=512 => 15 % head-room)
+    max_rows = max(148 * ((B * 9 // 8 + 147) // 148), 148) if peer_path else Bg
+    if peer_path:
+        sampler.connect_peers()
     ugen = torch.Generator(device=dev).manual_seed(4321)          # same draws on every rank
     u_table = ((torch.arange(Bg, device=dev, dtype=torch.float64) +
                 torch.rand(64, Bg, device=dev, dtype=torch.float64, generator=ugen)) / Bg) if world > 1 else None
@@ -164,6 +173,10 @@ def run_ours(args):
         if world == 1:
             b = mem.sample_tensors(B, fused=fused)                # K3 (in-kernel stratified draws) + K4
             mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma, out=td_out)      # K5 + K2
+        elif peer_path:
+            sampler.exchange()                                    # totals over NVLink peer memory, one launch
+            b, _pos, cnt = sampler.sample_fused(Bg, max_rows)     # K8+K3+K4 fused, in-kernel global stratified draws
+            mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma, out=td_out, count_dev=cnt, mean_divisor=float(Bg))
         else:
             b, _pos, cnt = sampler.sample(u_table[(step_no[0] if graph_steps is None else k) % 64], out=shard_out)
             mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma, out=td_out, count_dev=cnt, mean_divisor=float(Bg))
@@ -174,7 +187,7 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    use_graph = not args.no_graph                                 # NCCL all-gather is captured too when world > 1
+    use_graph = (not args.no_graph) and (world == 1 or peer_path)   # the NCCL path stays a python loop
     for k in range(max(args.warmup, 3)):
         step(k)
     torch.cuda.synchronize()
@@ -212,7 +225,7 @@ def run_ours(args):
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    launches_per_step = (2 if fused else 3) if world == 1 else 5 + (1 if Bg > 1024 else 0)
+    launches_per_step = (2 if fused else 3) if world == 1 else (3 if peer_path else 5 + (1 if Bg > 1024 else 0))
     value = K * Bg / (ms * 1e-3)
 
     # ---- roofline of the dominant kernel (fused K3+K4 sample_gather, or K4 alone with --unfused).
@@ -223,6 +236,29 @@ def run_ours(args):
     peak, peak_src = peaks()
     bytes_per_rec = 4 * C * F_BYTES + 32
     roofline = None
+    multi = None
+    if peer_path:
+        def graph_of(fn, reps_in=16):
+            sd = torch.cuda.Stream()
+            sd.wait_stream(torch.cuda.current_stream())
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.stream(sd):
+                with torch.cuda.graph(g, stream=sd):
+                    for _ in range(reps_in):
+                        fn()
+            torch.cuda.current_stream().wait_stream(sd)
+            for _ in range(3):
+                g.replay()
+            barrier()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            for _ in range(20):
+                g.replay()
+            a1.record()
+            barrier()
+            return a0.elapsed_time(a1) * 1e3 / (reps_in * 20)
+        multi = {"shard_exchange_us": round(graph_of(sampler.exchange), 3),
+                 "sample_gather_sharded_us": round(graph_of(lambda: sampler.sample_fused(Bg, max_rows)), 3)}
     if world == 1:
         o = mem._outputs(B, False)
 
@@ -355,8 +391,11 @@ def run_ours(args):
                        "pdl": not args.no_pdl,
                        "l2": "frame store %.1f GB >> 126 MB L2 (random gathers miss); the %.1f MB tree is L2-resident by design"
                              % (N * F_BYTES / 1e9, N * 8 * 33 / 32 / 1e6),
-                       "parallelism": "1 shard per GPU, NCCL all-gather of shard totals" if world > 1 else "single shard"},
-            "gpu_launches": K * launches_per_step, "clocks": clk, "roofline": roofline, "e2e": e2e, "cpu_baseline": cpu,
+                       "parallelism": ("1 shard per GPU; shard totals exchanged over NVLink peer memory by "
+                                       "shard_exchange_kernel, fused routing+search+gather per rank (quota %d rows)" % max_rows
+                                       if peer_path else "1 shard per GPU, NCCL all-gather of shard totals")
+                       if world > 1 else "single shard"},
+            "gpu_launches": K * launches_per_step, "clocks": clk, "roofline": roofline, "multi_gpu_kernels": multi, "e2e": e2e, "cpu_baseline": cpu,
             "cpu_baseline_c_openmp": cpu_c,
         }
         print(json.dumps(line))

@@ -59,6 +59,11 @@ extern "C" {
 #define APEXB200_ST_BAD_INDEX    2      /* record index outside [0, capacity) */
 #define APEXB200_ST_BAD_TARGET   4      /* target >= total in sample_targets */
 #define APEXB200_ST_BAD_ACTION   8      /* action outside [0, num_actions) */
+#define APEXB200_ST_PEER_TIMEOUT 16     /* shard_exchange: a peer never delivered its total */
+#define APEXB200_ST_QUOTA        32     /* sharded sample: this shard owns more draws than max_rows */
+
+#define APEXB200_MAX_SHARDS       16
+#define APEXB200_IPC_HANDLE_BYTES 64
 
 typedef struct apexb200_replay *apexb200_replay_t;
 
@@ -267,6 +272,34 @@ int apexb200_initial_priority(const float *q_t, const float *q_tpn, const int32_
 int apexb200_shard_targets(const uint64_t *totals, int32_t G, int32_t rank, const double *u,
                            int32_t count, uint64_t *local_targets, int32_t *local_pos,
                            int32_t *local_count, void *stream);
+
+/* ---- multi-GPU: exchange of shard totals over peer memory, fused sharded sample
+ * (no reference counterpart).  One process per GPU, one handle per rank.
+ * peer_export writes a CUDA-IPC handle (APEXB200_IPC_HANDLE_BYTES) of this shard's
+ * exchange buffer; the host all-gathers the handles (torch.distributed) and gives every
+ * rank the full list [world][64] through peer_connect, which maps the peers' buffers
+ * (NVLink peer access).  world <= APEXB200_MAX_SHARDS. */
+int apexb200_peer_export(apexb200_replay_t h, void *ipc_handle_host);
+int apexb200_peer_connect(apexb200_replay_t h, int32_t rank, int32_t world, const void *ipc_handles_host);
+/* One launch replacing tree_total + all-gather: every rank writes {total, round} into
+ * every peer's buffer and waits for all entries of the round.  Collective: every rank
+ * must call it the same number of times.  The totals are kept in the handle for
+ * apexb200_sample_gather_sharded and copied to totals_out (device u64 [world], nullable). */
+int apexb200_shard_exchange(apexb200_replay_t h, uint64_t *totals_out, void *stream);
+/* Fused K8 + K3 + K4 for one rank of a sharded replay, after apexb200_shard_exchange.
+ * The global batch is global_count stratified draws u_j = (j + v_j)/global_count with
+ * v_j = splitmix64(seed, exchange round, call index, j): identical on every rank.  This
+ * rank owns the contiguous run of draws whose global target falls into its prefix
+ * interval; each warp finds the run by a 32-ary search on the draw function, takes local
+ * row r = j - j_first, descends the local tree with (target - prefix) and gathers the
+ * record into row r of the outputs ([max_rows, ...]).  count_out [1] = rows owned (rows
+ * beyond it are stale), pos_out [max_rows] = global draw index j of each row.  A shard
+ * that owns more than max_rows draws keeps the first max_rows and sets
+ * APEXB200_ST_QUOTA.  Needs 2*frames_per_state <= 16 and a record that fits shared memory. */
+int apexb200_sample_gather_sharded(apexb200_replay_t h, uint64_t seed, int32_t global_count, int32_t max_rows,
+                                   int32_t *idx_out, int32_t *fsel_out, int32_t *pos_out, double *u_out,
+                                   int32_t *count_out, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R,
+                                   float *Gamma, float *q_t, float *q_tpn, void *stream);
 
 /* ---- raw access for checkpoint / tests (learner.py:18-23 is load-only; the
  * replay itself is never persisted by the reference) ---------------------- */

@@ -99,6 +99,44 @@ def main():
         dist.all_gather(new_leaves, torch.as_tensor(ring.leaves.view(np.int64)).to(dev))
         for r in range(world):
             rings[r][0].leaves[:] = new_leaves[r].cpu().numpy().view(np.uint64)
+    # ---- peer-memory exchange + fused routing/search/gather (no NCCL on the step path)
+    sampler.connect_peers()
+    B = 256
+    max_rows = int(B * 1.5)
+    totals = torch.zeros(world, dtype=torch.int64, device=dev)
+    for rnd in range(1, 6):
+        sampler.exchange(totals)
+        want_tot = [int(rings[r][0].leaves.sum(dtype=np.uint64)) for r in range(world)]
+        ok &= [int(x) for x in totals.cpu().numpy().view(np.uint64)] == want_tot
+        u_out = torch.zeros(max_rows, dtype=torch.float64, device=dev)
+        batch, pos, cnt = sampler.sample_fused(Bg, max_rows, u_out=u_out)
+        cnt_h = int(cnt.item())
+        # reassemble the global draw vector from what every rank reports for its own rows
+        u_glob = torch.zeros(Bg, dtype=torch.float64, device=dev)
+        owner = torch.zeros(Bg, dtype=torch.int64, device=dev)
+        u_glob[pos[:cnt_h].long()] = u_out[:cnt_h]
+        owner[pos[:cnt_h].long()] = 1
+        dist.all_reduce(u_glob)
+        dist.all_reduce(owner)
+        ok &= bool((owner == 1).all().item())                                # every draw owned by exactly one rank
+        u = u_glob.cpu().numpy()
+        ok &= bool((u == ro.kernel_stratified_uniforms(mem.seed, rnd, rnd - 1, Bg)).all())
+        whole = ro.tree_sample(np.concatenate([rings[r][0].leaves for r in range(world)]), u)
+        mine = np.nonzero(whole // n == rank)[0]
+        ok &= cnt_h == len(mine) and (pos.cpu().numpy()[:cnt_h] == mine).all()
+        local_idx = batch.idx.cpu().numpy()[:cnt_h]
+        ok &= (local_idx == whole[mine] % n).all()
+        g = ring.gather(local_idx)
+        ok &= (batch.S_t.cpu().numpy()[:cnt_h] == g["S_t"]).all() and (batch.S_tpn.cpu().numpy()[:cnt_h] == g["S_tpn"]).all()
+        q = [torch.randn(max_rows, nA, device=dev) for _ in range(3)]
+        delta, prio, loss, mean = mem.td_update(batch.idx, q[0], q[1], q[2], batch.A, batch.R, batch.Gamma,
+                                                count_dev=cnt, mean_divisor=float(Bg))
+        ring.set_leaves(local_idx, ro.priority_to_leaf(prio.cpu().numpy()[:cnt_h]))
+        ok &= mem.total() == ring.total()
+        new_leaves = [torch.zeros(n, dtype=torch.int64, device=dev) for _ in range(world)]
+        dist.all_gather(new_leaves, torch.as_tensor(ring.leaves.view(np.int64)).to(dev))
+        for r in range(world):
+            rings[r][0].leaves[:] = new_leaves[r].cpu().numpy().view(np.uint64)
     mem.check_status()
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)

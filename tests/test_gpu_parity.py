@@ -505,6 +505,51 @@ def test_shard_routing_equals_single_tree(apex):
     np.testing.assert_array_equal(got, whole)
 
 
+def test_peer_exchange_and_fused_sharded_sample_world1(apex):
+    """The peer-memory exchange and the fused routing+search+gather kernel with a group of one
+    (the multi-rank behaviour is checked by tests/multi_gpu_check.py under torchrun)."""
+    rng = np.random.default_rng(15)
+    N, C_, F, B = 1 << 13, 2, 256, 300
+    mem = make_mem(apex, N, C=C_, F=F, layout="stream", lanes=2, n=3)
+    ring = ro.RingOracle(N, C_, F, lanes=2, fpr=1, lookback=C_ - 1 + 3, alpha=0.6)
+    for lane in range(2):
+        m = N // 2 - 8
+        args = (lane, rng.integers(0, 256, (m, F), dtype=np.uint8), apex.stream_offsets(C_, np.full(m, 3), np.arange(m)),
+                rng.integers(0, 4, m).astype(np.int32), rng.standard_normal(m).astype(np.float32), np.full(m, 0.97, np.float32))
+        prio = (np.abs(rng.standard_normal(m)) + 1e-3).astype(np.float32)
+        mem.insert(*args, prio=prio)
+        ring.insert(*args, prio=prio)
+    ring.leaves[:] = u64(mem.buffer(apex._C.BUF_LEAVES))
+    sampler = apex.ShardedSampler(mem, rank=0, world_size=1)
+    sampler.connect_peers()
+    totals = torch.zeros(1, dtype=torch.int64, device="cuda")
+    for rnd in range(1, 4):
+        sampler.exchange(totals)
+        assert int(u64(totals)[0]) == ring.total()
+        for max_rows in (B, B + 37):
+            u_out = torch.full((max_rows,), -1.0, dtype=torch.float64, device="cuda")
+            b, pos, cnt = sampler.sample_fused(B, max_rows, u_out=u_out)
+            assert int(cnt.item()) == B
+            np.testing.assert_array_equal(pos.cpu().numpy()[:B], np.arange(B))
+            u = u_out.cpu().numpy()[:B]
+            assert ((u >= np.arange(B) / B) & (u <= (np.arange(B) + 1) / B)).all()
+            want = ring.sample(u)
+            np.testing.assert_array_equal(b.idx.cpu().numpy()[:B], want)
+            g = ring.gather(want)
+            np.testing.assert_array_equal(b.S_t.cpu().numpy()[:B], g["S_t"])
+            np.testing.assert_array_equal(b.S_tpn.cpu().numpy()[:B], g["S_tpn"])
+            np.testing.assert_array_equal(b.R.cpu().numpy()[:B], g["R"])
+        # quota overflow is reported, not silent
+        b, pos, cnt = sampler.sample_fused(B, B - 50)
+        assert int(cnt.item()) == B - 50
+        with pytest.raises(apex._C.ApexError, match="quota"):
+            mem.check_status()
+        mem.update_priorities(dev(np.arange(5, dtype=np.int32)), dev(np.full(5, 2.0 * rnd, np.float32)))
+        ring.set_priorities(np.arange(5), np.full(5, 2.0 * rnd, np.float32))
+        ring.leaves[:5] = u64(mem.buffer(apex._C.BUF_LEAVES))[:5]
+    mem.check_status()
+
+
 # --------------------------------------------------------------- error behaviour
 def test_argument_errors(apex):
     _C = apex._C
