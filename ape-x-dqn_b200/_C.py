@@ -74,6 +74,7 @@ SIGNATURES = {
     "apexb200_peer_export": [_P, _P],
     "apexb200_peer_connect": [_P, _I32, _I32, _P],
     "apexb200_shard_exchange": [_P, _P, _P],
+    "apexb200_peer_push_on_update": [_P, _I32],
     "apexb200_sample_gather_sharded": [_P, C.c_uint64, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "apexb200_replay_buffer": [_P, _I32, C.POINTER(_P), C.POINTER(_I64)],
     "apexb200_replay_get_heads": [_P, C.POINTER(_I64)],

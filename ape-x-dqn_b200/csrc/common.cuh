@@ -119,6 +119,31 @@ __device__ __forceinline__ void bump_epoch(int32_t *ctrl) {        // one thread
     if (blockIdx.x == 0 && threadIdx.x == 0) *(volatile unsigned long long *)(ctrl + 4) += 1ull;
 }
 
+// ---- exchange of shard totals over peer memory (multi-GPU) ---------------------------
+// One 8-byte word per (slot, rank): total << 4 | round & 15.  Total and tag travel in the
+// same naturally aligned word, so no fence is needed between them (a shard total < 2^60).
+// Round r lives in slot r & 1.  A rank only pushes round r+1 after it has seen every
+// peer's round-r word (peer_wait_round), which proves the peers are done with round r-1,
+// whose slot the push overwrites; hence a slot sees tags r, r+2, r+4, ... and the 4-bit
+// tag cannot alias.  Both helpers are called by the lanes g < world of one warp.
+__device__ __forceinline__ unsigned long long peer_wait_round(const PeerView &pv, unsigned long long round, int g,
+                                                              int32_t *ctrl) {
+    volatile unsigned long long *in = pv.xbuf[pv.rank] + (size_t)((int)(round & 1ull) * kMaxShards + g);
+    const unsigned long long tag = round & 15ull;
+    const long long t0 = clock64();
+    unsigned long long w = *in;
+    while ((w & 15ull) != tag) {
+        if (clock64() - t0 > (5ll << 31)) { atomicOr(ctrl, APEXB200_ST_PEER_TIMEOUT); return 0ull; }   // ~5 s: peer gone
+        w = *in;
+    }
+    return w >> 4;
+}
+__device__ __forceinline__ void peer_push_round(const PeerView &pv, unsigned long long round, int g,
+                                                unsigned long long total) {
+    volatile unsigned long long *out = pv.xbuf[g] + (size_t)((int)(round & 1ull) * kMaxShards + pv.rank);
+    *out = (total << 4) | (round & 15ull);
+}
+
 // Add `d` (mod 2^64) to every ancestor of leaf i.  Integer adds commute, so the
 // tree is exact whatever order concurrent updates land in.
 __device__ __forceinline__ void propagate_delta(const TreeView &tv, long long i, unsigned long long d) {
@@ -207,6 +232,7 @@ struct apexb200_replay {
     unsigned long long *xbuf = nullptr; // this shard's exchange buffer (peers write into it)
     apexb200::PeerView peers;          // xbuf of every rank; world = 1, xbuf[0] = own until peer_connect
     void *opened[apexb200::kMaxShards] = {};   // IPC mappings to close
+    int push_on_update = 0;            // td_fwd_update also publishes the new total to the peers
     unsigned long long draw_calls = 0; // host: stratified-draw calls issued (the `call` of strat_uniform)
     std::vector<long long> lane_count; // host ring heads
     int64_t device_bytes = 0;

@@ -298,7 +298,7 @@ __device__ __forceinline__ int first_draw_at_or_above(unsigned long long bound, 
 }
 
 __global__ void __launch_bounds__(256)
-sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, ShardArgs sh, int world, int rank,
+sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, ShardArgs sh, PeerView pv,
                              int32_t *ctrl) {
     extern __shared__ __align__(128) uint8_t smem[];
     unsigned long long *bars = (unsigned long long *)smem;
@@ -309,10 +309,17 @@ sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs
     const int nch = frame_chunks(rv.F);
     const int row = blockIdx.x + wl * gridDim.x;
     const int twoC = 2 * rv.C;
-    if (row >= sh.max_rows) return;
     const unsigned long long vtop = top_level_value(tv);
-    // totals of the last exchange -> global total T and this rank's prefix interval [lo, hi)
-    unsigned long long tg = lane < world ? exchanged_totals(ctrl)[lane] : 0ull, incl = tg;
+    const int world = pv.world, rank = pv.rank;
+    // the shard totals of the current round (pushed by shard_exchange_kernel or by the peers'
+    // td_small_kernel) -> global total T and this rank's prefix interval [lo, hi).  One warp per
+    // CTA polls the exchange buffer; the others take the words from shared memory.
+    __shared__ unsigned long long s_totals[kMaxShards];
+    const unsigned long long round = read_round(ctrl);
+    if (wl == 0 && lane < world) s_totals[lane] = peer_wait_round(pv, round, lane, ctrl);
+    __syncthreads();
+    if (row >= sh.max_rows) return;
+    unsigned long long tg = lane < world ? s_totals[lane] : 0ull, incl = tg;
     #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         unsigned long long n = __shfl_up_sync(0xffffffffu, incl, o);
@@ -321,7 +328,6 @@ sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs
     const unsigned long long T = __shfl_sync(0xffffffffu, incl, 31);
     const unsigned long long hi = __shfl_sync(0xffffffffu, incl, rank);
     const unsigned long long lo = hi - __shfl_sync(0xffffffffu, tg, rank);
-    const unsigned long long round = read_round(ctrl);
     if (T == 0ull) {
         if (lane == 0) { atomicOr(ctrl, APEXB200_ST_EMPTY_TREE); if (row == 0) *sh.count_out = 0; }
         return;
@@ -469,7 +475,7 @@ int apexb200_sample_gather_sharded(apexb200_replay_t h, uint64_t seed, int32_t g
     GatherArgs ga{idx_out, fsel_out, nullptr, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, max_rows};
     ShardArgs sh{(unsigned long long)seed, h->draw_calls++, global_count, max_rows, pos_out, count_out};
     return launch_step("sample_gather_sharded_kernel", sample_gather_sharded_kernel, dim3((unsigned)ctas), dim3(wpc * 32),
-                       smem, (cudaStream_t)stream, h->tree, rv, sa, ga, sh, h->peers.world, h->peers.rank, h->status);
+                       smem, (cudaStream_t)stream, h->tree, rv, sa, ga, sh, h->peers, h->status);
 }
 
 }  // extern "C"

@@ -12,6 +12,7 @@ int run_tree_update(apexb200_replay *h, const int32_t *idx, const void *values, 
                     const int32_t *count_dev, float eps, cudaStream_t st);
 int run_tree_apply(apexb200_replay *h, const int32_t *idx, const void *values, int mode, int count,
                    const int32_t *count_dev, cudaStream_t st);
+int run_peer_push(apexb200_replay *h, cudaStream_t st);
 
 struct TdArgs {
     const float *q_on_t, *q_on_tpn, *q_tg_tpn;
@@ -78,7 +79,7 @@ __device__ __forceinline__ float block_sum_fixed(float v, float *warp_part) {
 // dependent memory round trips at two.
 __global__ void __launch_bounds__(1024)
 td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t *__restrict__ stamp,
-                int32_t *status) {
+                int32_t *status, PeerView pv, int push) {
     __shared__ float warp_part[32];
     pdl_prologue();
     if (idx != nullptr) bump_epoch(status);
@@ -109,11 +110,32 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
     }
     float s = block_sum_fixed(l, warp_part);
     if (threadIdx.x == 0) *a.loss_mean = s / mean_div(a);
-    if (!winner) return;
-    unsigned long long nl = leaf_from_prio(a.prio[b]);
-    tv.lvl[0][i] = nl;
-    unsigned long long d = nl - old;
-    if (d != 0ull) propagate_delta(tv, i, d);
+    if (winner) {
+        unsigned long long nl = leaf_from_prio(a.prio[b]);
+        tv.lvl[0][i] = nl;
+        unsigned long long d = nl - old;
+        if (d != 0ull) propagate_delta(tv, i, d);
+    }
+    if (!push) return;
+    // Fused collective (multi-GPU): publish this shard's new total to every peer from the
+    // kernel that produced it — the next step's sharded sample on each rank waits for these
+    // words instead of an all-gather.  All tree updates of this CTA are at L2 before the sum.
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        const int top = tv.n_levels - 1;
+        unsigned long long v = lane < tv.size[top] ? *(volatile unsigned long long *)(tv.lvl[top] + lane) : 0ull;
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        const unsigned long long cur = read_round(status);
+        if (lane < pv.world) {
+            if (cur > 0ull) peer_wait_round(pv, cur, lane, status);     // already there in the steady state
+            peer_push_round(pv, cur + 1ull, lane, v);
+        }
+        __syncwarp();
+        if (lane == 0) *(volatile unsigned long long *)(status + 6) = cur + 1ull;
+    }
 }
 
 // ---- any B: 256 records per CTA; per-CTA loss partials go to scratch and the last
@@ -223,9 +245,11 @@ static int td_launch(apexb200_replay *h, const int32_t *idx, const TdArgs &a, vo
                      cudaStream_t st) {
     TreeView tv_none{};
     if (a.B <= 1024) {
+        PeerView pv_none{};
         return launch_step("td_small_kernel", td_small_kernel, dim3(1), dim3(((a.B + 31) / 32) * 32), 0, st, a,
                            h ? h->tree : tv_none, idx, h ? h->stamp : (uint32_t *)nullptr,
-                           h ? h->status : (int32_t *)nullptr);
+                           h ? h->status : (int32_t *)nullptr, h ? h->peers : pv_none,
+                           (h && idx && h->push_on_update) ? 1 : 0);
     }
     APEX_REQUIRE(workspace && ws_bytes >= td_ws_bytes(a.B), APEXB200_EINVAL,
                  "td_fwd: B=%d needs %lld bytes of workspace (got %lld)", a.B, (long long)td_ws_bytes(a.B),
@@ -238,7 +262,9 @@ static int td_launch(apexb200_replay *h, const int32_t *idx, const TdArgs &a, vo
                          h ? h->status : (int32_t *)nullptr, (unsigned int *)workspace,
                          (float *)((char *)workspace + 256));
     if (rc || !h) return rc;
-    return run_tree_apply(h, idx, a.prio, 2, a.B, a.count_dev, st);   // stamps were taken inside td_multi_kernel
+    rc = run_tree_apply(h, idx, a.prio, 2, a.B, a.count_dev, st);     // stamps were taken inside td_multi_kernel
+    if (rc || !h->push_on_update) return rc;
+    return run_peer_push(h, st);                                      // large batches: publish from a trailing launch
 }
 
 // ---------------------------------------------------------------------------

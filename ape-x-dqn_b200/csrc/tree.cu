@@ -189,15 +189,12 @@ shard_targets_kernel(const unsigned long long *__restrict__ totals, int G, int r
 }
 
 // ---------------------------------------------------------------------------
-// All-gather of the shard totals over peer memory (one warp, one launch): the warp sums
-// its own top level, lane g writes ONE 8-byte word (total << 4 | round & 15) straight into
-// rank g's exchange buffer over NVLink, then lane g polls the local buffer for rank g's
-// word of this round.  Total and round tag travel in the same naturally-aligned word, so
-// no fence is needed between them (a shard total is < 2^60).  Rounds alternate between
-// two slots; a rank cannot start round r+2 before every peer has finished reading round
-// r (it needs their round r+1 words first), so a slot sees tags r, r+2, r+4, ... and the
-// 4-bit tag never aliases.  Replaces tree_total + ncclAllGather (8 bytes per rank: pure
-// latency) on the per-step path.
+// All-gather of the shard totals over peer memory (one warp, one launch; protocol in
+// common.cuh).  The warp sums its own top level, lane g waits for rank g's word of the
+// current round (so that the slot about to be overwritten is no longer needed), writes
+// the new word straight into rank g's exchange buffer over NVLink, then polls the local
+// buffer for rank g's word of the new round.  Replaces tree_total + ncclAllGather
+// (8 bytes per rank: pure latency) on the per-step path.
 __global__ void __launch_bounds__(32)
 shard_exchange_kernel(TreeView tv, PeerView pv, int32_t *ctrl, unsigned long long *totals_out) {
     pdl_prologue();
@@ -206,25 +203,38 @@ shard_exchange_kernel(TreeView tv, PeerView pv, int32_t *ctrl, unsigned long lon
     unsigned long long v = lane < tv.size[top] ? tv.lvl[top][lane] : 0ull;
     #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    const unsigned long long round = read_round(ctrl) + 1ull;
-    const int parity = (int)(round & 1ull);
-    const unsigned long long tag = round & 15ull;
+    const unsigned long long cur = read_round(ctrl);
     if (lane < pv.world) {
-        volatile unsigned long long *out = pv.xbuf[lane] + (size_t)(parity * kMaxShards + pv.rank);
-        *out = (v << 4) | tag;
-        volatile unsigned long long *in = pv.xbuf[pv.rank] + (size_t)(parity * kMaxShards + lane);
-        const long long t0 = clock64();
-        unsigned long long w = *in;
-        while ((w & 15ull) != tag) {
-            if (clock64() - t0 > (5ll << 31)) { atomicOr(ctrl, APEXB200_ST_PEER_TIMEOUT); w = 0ull; break; }   // ~5 s
-            w = *in;
-        }
-        const unsigned long long t = w >> 4;
+        if (cur > 0ull) peer_wait_round(pv, cur, lane, ctrl);
+        peer_push_round(pv, cur + 1ull, lane, v);
+        const unsigned long long t = peer_wait_round(pv, cur + 1ull, lane, ctrl);
         ((unsigned long long *)(ctrl + 16))[lane] = t;
         if (totals_out) totals_out[lane] = t;
     }
     __syncwarp();
-    if (lane == 0) *(volatile unsigned long long *)(ctrl + 6) = round;
+    if (lane == 0) *(volatile unsigned long long *)(ctrl + 6) = cur + 1ull;
+}
+
+// Push without the trailing wait (what td_small_kernel does at its tail), as its own launch.
+__global__ void __launch_bounds__(32)
+shard_push_kernel(TreeView tv, PeerView pv, int32_t *ctrl) {
+    pdl_prologue();
+    const int lane = threadIdx.x;
+    const int top = tv.n_levels - 1;
+    unsigned long long v = lane < tv.size[top] ? tv.lvl[top][lane] : 0ull;
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const unsigned long long cur = read_round(ctrl);
+    if (lane < pv.world) {
+        if (cur > 0ull) peer_wait_round(pv, cur, lane, ctrl);
+        peer_push_round(pv, cur + 1ull, lane, v);
+    }
+    __syncwarp();
+    if (lane == 0) *(volatile unsigned long long *)(ctrl + 6) = cur + 1ull;
+}
+
+int run_peer_push(apexb200_replay *h, cudaStream_t st) {
+    return launch_step("shard_push_kernel", shard_push_kernel, dim3(1), dim3(32), 0, st, h->tree, h->peers, h->status);
 }
 
 // Phase 2 alone, for callers that stamped inside their own kernel (td.cu).
@@ -359,6 +369,12 @@ int apexb200_shard_exchange(apexb200_replay_t h, uint64_t *totals_out, void *str
     APEX_REQUIRE(h, APEXB200_EINVAL, "shard_exchange: null handle");
     return launch_step("shard_exchange_kernel", shard_exchange_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, h->tree,
                        h->peers, h->status, (unsigned long long *)totals_out);
+}
+
+int apexb200_peer_push_on_update(apexb200_replay_t h, int32_t enabled) {
+    APEX_REQUIRE(h, APEXB200_EINVAL, "peer_push_on_update: null handle");
+    h->push_on_update = enabled ? 1 : 0;
+    return APEXB200_OK;
 }
 
 int apexb200_shard_targets(const uint64_t *totals, int32_t G, int32_t rank, const double *u, int32_t count,

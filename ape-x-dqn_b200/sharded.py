@@ -62,6 +62,12 @@ class ShardedSampler:
             dist.barrier(group=self.group)
         self.connected = True
 
+    def push_on_update(self, enabled=True):
+        """Let every td_update publish the new shard total to the peers from inside its kernel
+        (fused compute + collective); the step loop then needs no exchange() call."""
+        from . import _C
+        _C.call("apexb200_peer_push_on_update", self.mem._h, 1 if enabled else 0)
+
     def exchange(self, totals_out=None):
         """One-launch all-gather of the shard totals over peer memory (collective: every rank
         calls it once per step, before sample_fused)."""

@@ -48,6 +48,9 @@ def parse():
     ap.add_argument("--nccl-exchange", action="store_true",
                     help="multi-GPU: all-gather the shard totals with NCCL + separate routing/search/gather kernels "
                          "instead of the peer-memory exchange + fused sharded kernel")
+    ap.add_argument("--no-push", action="store_true",
+                    help="multi-GPU: exchange the totals with one shard_exchange launch per step instead of "
+                         "publishing them from the TD/update kernel")
     ap.add_argument("--workload", default="replay", choices=["replay", "learner"],
                     help="replay = BASELINE configs[1] microbench (default, the metric's workload); "
                          "learner = configs[2]: the same loop with the duelling network fwd/bwd + RMSprop in it")
@@ -161,6 +164,8 @@ def run_ours(args):
     max_rows = max(148 * ((B * 9 // 8 + 147) // 148), 148) if peer_path else Bg
     if peer_path:
         sampler.connect_peers()
+        sampler.push_on_update(not args.no_push)                  # K5+K2 publishes the new total to the peers itself
+        sampler.exchange()                                        # first round (after the fill)
     ugen = torch.Generator(device=dev).manual_seed(4321)          # same draws on every rank
     u_table = ((torch.arange(Bg, device=dev, dtype=torch.float64) +
                 torch.rand(64, Bg, device=dev, dtype=torch.float64, generator=ugen)) / Bg) if world > 1 else None
@@ -174,8 +179,9 @@ def run_ours(args):
             b = mem.sample_tensors(B, fused=fused)                # K3 (in-kernel stratified draws) + K4
             mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma, out=td_out)      # K5 + K2
         elif peer_path:
-            sampler.exchange()                                    # totals over NVLink peer memory, one launch
-            b, _pos, cnt = sampler.sample_fused(Bg, max_rows)     # K8+K3+K4 fused, in-kernel global stratified draws
+            if args.no_push:
+                sampler.exchange()
+            b, _pos, cnt = sampler.sample_fused(Bg, max_rows)     # waits for the peers' totals, K8+K3+K4 fused
             mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma, out=td_out, count_dev=cnt, mean_divisor=float(Bg))
         else:
             b, _pos, cnt = sampler.sample(u_table[(step_no[0] if graph_steps is None else k) % 64], out=shard_out)
@@ -225,7 +231,7 @@ def run_ours(args):
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    launches_per_step = (2 if fused else 3) if world == 1 else (3 if peer_path else 5 + (1 if Bg > 1024 else 0))
+    launches_per_step = (2 if fused else 3) if world == 1 else (2 if peer_path else 5 + (1 if Bg > 1024 else 0))
     value = K * Bg / (ms * 1e-3)
 
     # ---- roofline of the dominant kernel (fused K3+K4 sample_gather, or K4 alone with --unfused).
@@ -257,8 +263,10 @@ def run_ours(args):
             a1.record()
             barrier()
             return a0.elapsed_time(a1) * 1e3 / (reps_in * 20)
+        sampler.push_on_update(False)
         multi = {"shard_exchange_us": round(graph_of(sampler.exchange), 3),
                  "sample_gather_sharded_us": round(graph_of(lambda: sampler.sample_fused(Bg, max_rows)), 3)}
+        sampler.push_on_update(not args.no_push)
     if world == 1:
         o = mem._outputs(B, False)
 
@@ -391,8 +399,9 @@ def run_ours(args):
                        "pdl": not args.no_pdl,
                        "l2": "frame store %.1f GB >> 126 MB L2 (random gathers miss); the %.1f MB tree is L2-resident by design"
                              % (N * F_BYTES / 1e9, N * 8 * 33 / 32 / 1e6),
-                       "parallelism": ("1 shard per GPU; shard totals exchanged over NVLink peer memory by "
-                                       "shard_exchange_kernel, fused routing+search+gather per rank (quota %d rows)" % max_rows
+                       "parallelism": ("1 shard per GPU; every rank's TD/update kernel pushes its new shard total into all peers' "
+                                       "memory over NVLink, the next fused routing+search+gather kernel waits for them "
+                                       "(no NCCL on the step path; quota %d rows per rank)" % max_rows
                                        if peer_path else "1 shard per GPU, NCCL all-gather of shard totals")
                        if world > 1 else "single shard"},
             "gpu_launches": K * launches_per_step, "clocks": clk, "roofline": roofline, "multi_gpu_kernels": multi, "e2e": e2e, "cpu_baseline": cpu,

@@ -286,7 +286,17 @@ int apexb200_peer_connect(apexb200_replay_t h, int32_t rank, int32_t world, cons
  * must call it the same number of times.  The totals are kept in the handle for
  * apexb200_sample_gather_sharded and copied to totals_out (device u64 [world], nullable). */
 int apexb200_shard_exchange(apexb200_replay_t h, uint64_t *totals_out, void *stream);
-/* Fused K8 + K3 + K4 for one rank of a sharded replay, after apexb200_shard_exchange.
+/* Fused compute + collective: with this enabled every apexb200_td_fwd_update on the handle
+ * also publishes the shard's new total to all peers from the kernel that produced it (as a
+ * new exchange round), so the steady-state step is sample_gather_sharded -> model ->
+ * td_fwd_update with no exchange launch in between.  Every rank must then issue the same
+ * sequence of td_fwd_update / shard_exchange calls (collective discipline); after inserts,
+ * which change totals at different rates per rank, call apexb200_shard_exchange on every
+ * rank before the next sharded sample. */
+int apexb200_peer_push_on_update(apexb200_replay_t h, int32_t enabled);
+/* Fused K8 + K3 + K4 for one rank of a sharded replay.  The kernel itself waits for every
+ * peer's total of the current exchange round — published by apexb200_shard_exchange or,
+ * with push-on-update, by the peers' apexb200_td_fwd_update.
  * The global batch is global_count stratified draws u_j = (j + v_j)/global_count with
  * v_j = splitmix64(seed, exchange round, call index, j): identical on every rank.  This
  * rank owns the contiguous run of draws whose global target falls into its prefix

@@ -137,6 +137,48 @@ def main():
         dist.all_gather(new_leaves, torch.as_tensor(ring.leaves.view(np.int64)).to(dev))
         for r in range(world):
             rings[r][0].leaves[:] = new_leaves[r].cpu().numpy().view(np.uint64)
+    # ---- push-on-update: the TD/update kernel publishes the new total itself, no exchange() per step
+    sampler.push_on_update(True)
+    sampler.exchange()
+    rnd, call = 6, 5
+    for step in range(6):
+        u_out = torch.zeros(max_rows, dtype=torch.float64, device=dev)
+        batch, pos, cnt = sampler.sample_fused(Bg, max_rows, u_out=u_out)
+        cnt_h = int(cnt.item())
+        u_glob = torch.zeros(Bg, dtype=torch.float64, device=dev)
+        u_glob[pos[:cnt_h].long()] = u_out[:cnt_h]
+        dist.all_reduce(u_glob)
+        u = u_glob.cpu().numpy()
+        ok &= bool((u == ro.kernel_stratified_uniforms(mem.seed, rnd, call, Bg)).all())
+        whole = ro.tree_sample(np.concatenate([rings[r][0].leaves for r in range(world)]), u)
+        mine = np.nonzero(whole // n == rank)[0]
+        ok &= cnt_h == len(mine) and (pos.cpu().numpy()[:cnt_h] == mine).all()
+        local_idx = batch.idx.cpu().numpy()[:cnt_h]
+        ok &= (local_idx == whole[mine] % n).all()
+        q = [torch.randn(max_rows, nA, device=dev) for _ in range(3)]
+        delta, prio, loss, mean = mem.td_update(batch.idx, q[0], q[1], q[2], batch.A, batch.R, batch.Gamma,
+                                                count_dev=cnt, mean_divisor=float(Bg))       # pushes round rnd+1
+        ring.set_leaves(local_idx, ro.priority_to_leaf(prio.cpu().numpy()[:cnt_h]))
+        ok &= mem.total() == ring.total()
+        new_leaves = [torch.zeros(n, dtype=torch.int64, device=dev) for _ in range(world)]
+        dist.all_gather(new_leaves, torch.as_tensor(ring.leaves.view(np.int64)).to(dev))
+        for r in range(world):
+            rings[r][0].leaves[:] = new_leaves[r].cpu().numpy().view(np.uint64)
+        rnd, call = rnd + 1, call + 1
+        if step == 2:                                        # an insert changes one shard's total: re-exchange
+            m = 40
+            ins = (rank % lanes, np.random.default_rng(77 + rank).integers(0, 256, (m, F), dtype=np.uint8),
+                   apex_b200.stream_offsets(C, np.full(m, 3), np.full(m, 50)), np.zeros(m, np.int32),
+                   np.zeros(m, np.float32), np.ones(m, np.float32))
+            pr = np.full(m, 1.0 + rank, np.float32)
+            mem.insert(*ins, prio=pr)
+            ring.insert(*ins, prio=pr)
+            ring.leaves[:] = mem.buffer(_C.BUF_LEAVES).cpu().numpy().view(np.uint64)
+            dist.all_gather(new_leaves, torch.as_tensor(ring.leaves.view(np.int64)).to(dev))
+            for r in range(world):
+                rings[r][0].leaves[:] = new_leaves[r].cpu().numpy().view(np.uint64)
+            sampler.exchange()
+            rnd += 1
     mem.check_status()
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
