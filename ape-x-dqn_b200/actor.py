@@ -178,6 +178,11 @@ class Actor(mp.Process):
         return {r.key: td[i] for i, r in enumerate(recs)}
 
     def _setup(self):
+        import torch
+        # This runs in a forked child (main.py:51-54).  The parent has already used torch's OpenMP
+        # pool (building the learner's networks), and a forked copy of that pool deadlocks on its
+        # first parallel region; batch-1 inference wants one thread anyway.
+        torch.set_num_threads(1)
         if self.Q is None:
             from .learner import make_q_network
             self.Q = (self._q_factory or make_q_network)(self.state_shape, self.action_dim)

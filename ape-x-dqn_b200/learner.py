@@ -143,6 +143,8 @@ class Learner(object):
 
     def learn(self, T):
         """learner.py:63-80."""
+        if self.device is None:
+            torch.set_num_threads(1)      # forked child (main.py:46): the parent's OpenMP pool is unusable here
         while self.replay_memory.size() <= self.params["min_replay_mem_size"]:
             time.sleep(1)
         fast = self._fast()
