@@ -441,6 +441,10 @@ int apexb200_sample_gather(apexb200_replay_t h, const double *u, uint64_t seed, 
     if (wpc > 8) wpc = 8;
     const int spread = (count + kNumSMs - 1) / kNumSMs;                    // small batches: use every SM
     if (spread < wpc) wpc = spread;
+    // A batch that needs several waves runs faster with one draw per CTA (4 CTAs per SM: one CTA's
+    // tree descent overlaps another's frame movement; 78 vs 88 us at B=4096), a single-wave batch
+    // with fat CTAs (profiles/r01_kernel_experiments.md).
+    if (count > wpc * kNumSMs) wpc = 1;
     const size_t smem = (size_t)wpc * (per_draw + 16 * kMaxChunks * 8);
     int rc = ensure_smem((const void *)sample_gather_kernel, smem, h->cfg.device);
     if (rc) return rc;
