@@ -68,6 +68,7 @@ SIGNATURES = {
     "apexb200_td_bwd": [_P, _P, _P, _I32, _I32, _I32, _F, _P, _F, _P, _P],
     "apexb200_td_fwd_update": [_P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _F, _I32, _F, _P, _P, _P, _P, _P, _I64,
                                _P, _F, _P],
+    "apexb200_host_step": [_P, _I32, _P, _P, _I32, _I32, _F, _I32, _F, _P, _P, _P, _P, _P, _P, _P, _P],
     "apexb200_nstep": [_P, _P, _I32, _I32, _I32, _F, _P, _P, _P, _P],
     "apexb200_initial_priority": [_P, _P, _P, _P, _P, _I32, _I32, _P, _P],
     "apexb200_shard_targets": [_P, _I32, _I32, _P, _I32, _P, _P, _P, _P],

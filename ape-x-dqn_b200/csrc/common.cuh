@@ -233,6 +233,13 @@ struct apexb200_replay {
     apexb200::PeerView peers;          // xbuf of every rank; world = 1, xbuf[0] = own until peer_connect
     void *opened[apexb200::kMaxShards] = {};   // IPC mappings to close
     int push_on_update = 0;            // td_fwd_update also publishes the new total to the peers
+    // apexb200_host_step: two sets of device staging + copy streams, so that the H2D copy of step
+    // k+1 and the D2H copy of step k overlap the kernels of the other step
+    unsigned char *hs_in[2] = {nullptr, nullptr};
+    float *hs_out[2] = {nullptr, nullptr};
+    size_t hs_in_cap = 0, hs_out_cap = 0;
+    cudaStream_t hs_copy_in = nullptr, hs_copy_out = nullptr;
+    cudaEvent_t hs_ev_in[2] = {nullptr, nullptr}, hs_ev_k[2] = {nullptr, nullptr}, hs_ev_out[2] = {nullptr, nullptr};
     unsigned long long draw_calls = 0; // host: stratified-draw calls issued (the `call` of strat_uniform)
     std::vector<long long> lane_count; // host ring heads
     int64_t device_bytes = 0;

@@ -207,7 +207,14 @@ int apexb200_replay_destroy(apexb200_replay_t h) {
     if (!h) return APEXB200_OK;
     cudaSetDevice(h->cfg.device);
     for (void *m : h->opened) if (m) cudaIpcCloseMemHandle(m);
-    void *ptrs[] = {h->xbuf, h->tree_block, h->stamp, h->status, h->ring.frames, h->ring.fidx, h->ring.A,
+    if (h->hs_copy_in) cudaStreamDestroy(h->hs_copy_in);
+    if (h->hs_copy_out) cudaStreamDestroy(h->hs_copy_out);
+    for (int k = 0; k < 2; ++k) {
+        if (h->hs_ev_in[k]) cudaEventDestroy(h->hs_ev_in[k]);
+        if (h->hs_ev_k[k]) cudaEventDestroy(h->hs_ev_k[k]);
+        if (h->hs_ev_out[k]) cudaEventDestroy(h->hs_ev_out[k]);
+    }
+    void *ptrs[] = {h->hs_in[0], h->hs_in[1], h->hs_out[0], h->hs_out[1], h->xbuf, h->tree_block, h->stamp, h->status, h->ring.frames, h->ring.fidx, h->ring.A,
                     h->ring.R, h->ring.G, h->ring.q_t, h->ring.q_tpn};
     for (void *p : ptrs) if (p) cudaFree(p);
     delete h;
@@ -303,6 +310,76 @@ int apexb200_peer_connect(apexb200_replay_t h, int32_t rank, int32_t world, cons
         pv.xbuf[g] = (unsigned long long *)p;
     }
     h->peers = pv;
+    return APEXB200_OK;
+}
+
+int apexb200_host_step(apexb200_replay_t h, int32_t slot, const double *u_host, const float *q_host, int32_t B,
+                       int32_t num_actions, float eps, int32_t loss_kind, float kappa, uint8_t *S_t, uint8_t *S_tpn,
+                       int32_t *A, float *R, float *Gamma, float *result_host, void *done_event, void *stream) {
+    APEX_REQUIRE(h && u_host && q_host && result_host && S_t && S_tpn && A && R && Gamma, APEXB200_EINVAL,
+                 "host_step: null argument");
+    APEX_REQUIRE(slot == 0 || slot == 1, APEXB200_EINVAL, "host_step: slot must be 0 or 1");
+    APEX_REQUIRE(B > 0 && B <= 1024 && num_actions >= 1 && num_actions <= APEXB200_MAX_ACTIONS, APEXB200_ERANGE,
+                 "host_step: B=%d (max 1024) / num_actions=%d out of range", B, num_actions);
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t in_bytes = (size_t)B * 8 + (size_t)3 * B * num_actions * 4;
+    const size_t out_words = (size_t)4 * B + 4;
+    if (!h->hs_copy_in) {                                        // first call: copy streams and events
+        APEX_CUDA(cudaSetDevice(h->cfg.device));
+        APEX_CUDA(cudaStreamCreateWithFlags(&h->hs_copy_in, cudaStreamNonBlocking));
+        APEX_CUDA(cudaStreamCreateWithFlags(&h->hs_copy_out, cudaStreamNonBlocking));
+        for (int k = 0; k < 2; ++k) {
+            APEX_CUDA(cudaEventCreateWithFlags(&h->hs_ev_in[k], cudaEventDisableTiming));
+            APEX_CUDA(cudaEventCreateWithFlags(&h->hs_ev_k[k], cudaEventDisableTiming));
+            APEX_CUDA(cudaEventCreateWithFlags(&h->hs_ev_out[k], cudaEventDisableTiming));
+        }
+    }
+    if (in_bytes > h->hs_in_cap || out_words * 4 > h->hs_out_cap) {          // first call / larger batch: grow staging
+        APEX_CUDA(cudaDeviceSynchronize());
+        for (int k = 0; k < 2; ++k) {
+            if (h->hs_in[k]) cudaFree(h->hs_in[k]);
+            if (h->hs_out[k]) cudaFree(h->hs_out[k]);
+            h->hs_in[k] = nullptr; h->hs_out[k] = nullptr;
+        }
+        h->hs_in_cap = h->hs_out_cap = 0;
+        for (int k = 0; k < 2; ++k) {
+            APEX_CUDA(cudaMalloc((void **)&h->hs_in[k], in_bytes));
+            APEX_CUDA(cudaMalloc((void **)&h->hs_out[k], out_words * 4));
+        }
+        h->hs_in_cap = in_bytes;
+        h->hs_out_cap = out_words * 4;
+    }
+    unsigned char *d_in = h->hs_in[slot];
+    float *d_res = h->hs_out[slot];
+    // copy-in stream: the staging of this slot is free once the kernels of its previous use are done
+    APEX_CUDA(cudaStreamWaitEvent(h->hs_copy_in, h->hs_ev_k[slot], 0));
+    double *d_u = (double *)d_in;
+    float *d_q = (float *)(d_in + (size_t)B * 8);
+    if ((const void *)q_host == (const void *)(u_host + B)) {    // adjacent in the caller's pinned block: one copy
+        APEX_CUDA(cudaMemcpyAsync(d_in, u_host, in_bytes, cudaMemcpyHostToDevice, h->hs_copy_in));
+    } else {
+        APEX_CUDA(cudaMemcpyAsync(d_u, u_host, (size_t)B * 8, cudaMemcpyHostToDevice, h->hs_copy_in));
+        APEX_CUDA(cudaMemcpyAsync(d_q, q_host, (size_t)3 * B * num_actions * 4, cudaMemcpyHostToDevice, h->hs_copy_in));
+    }
+    APEX_CUDA(cudaEventRecord(h->hs_ev_in[slot], h->hs_copy_in));
+    // compute stream: inputs have landed, and this slot's previous results have left the device
+    APEX_CUDA(cudaStreamWaitEvent(st, h->hs_ev_in[slot], 0));
+    APEX_CUDA(cudaStreamWaitEvent(st, h->hs_ev_out[slot], 0));
+    float *d_delta = d_res, *d_prio = d_res + B, *d_loss = d_res + 2 * B, *d_mean = d_res + 4 * B;
+    int32_t *d_idx = (int32_t *)(d_res + 3 * B);
+    int rc = apexb200_sample_gather(h, d_u, 0, B, d_idx, nullptr, nullptr, nullptr, nullptr, S_t, S_tpn, A, R, Gamma,
+                                    nullptr, nullptr, stream);
+    if (rc) return rc;
+    const size_t qs = (size_t)B * num_actions;
+    rc = apexb200_td_fwd_update(h, d_idx, d_q, d_q + qs, d_q + 2 * qs, A, R, Gamma, B, num_actions, eps, loss_kind, kappa,
+                                d_delta, d_prio, d_loss, d_mean, nullptr, 0, nullptr, 0.0f, stream);
+    if (rc) return rc;
+    APEX_CUDA(cudaEventRecord(h->hs_ev_k[slot], st));
+    // copy-out stream
+    APEX_CUDA(cudaStreamWaitEvent(h->hs_copy_out, h->hs_ev_k[slot], 0));
+    APEX_CUDA(cudaMemcpyAsync(result_host, d_res, out_words * 4, cudaMemcpyDeviceToHost, h->hs_copy_out));
+    APEX_CUDA(cudaEventRecord(h->hs_ev_out[slot], h->hs_copy_out));
+    if (done_event) APEX_CUDA(cudaEventRecord((cudaEvent_t)done_event, h->hs_copy_out));
     return APEXB200_OK;
 }
 

@@ -1,6 +1,7 @@
 """Host-facing step: draws and Q-values arrive in HOST memory, loss / priorities / indices
-are read back on the host — the same K3+K4 -> K5+K2 step as the tensor API, wrapped so that
-one step is one CUDA-graph launch (pinned H2D copy, two kernels, one D2H copy).
+are read back on the host — the same K3+K4 -> K5+K2 step as the tensor API, issued by one
+C-ABI call (apexb200_host_step: pinned H2D copy, two kernels, one D2H copy, event record);
+use_graph=True replays a torch CUDA graph of the tensor-API calls instead.
 
 Replaces, for a caller that keeps its numbers on the host like the reference does, the
 round trip learner.py:68 (sample) -> :70 (loss, priorities) -> :76 (set_priorities).
@@ -17,7 +18,7 @@ from . import _C
 class HostStepPipeline:
     DEPTH = 2
 
-    def __init__(self, mem, batch_size, num_actions, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0, use_graph=True):
+    def __init__(self, mem, batch_size, num_actions, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0, use_graph=False):
         mem._ensure()
         self.mem, self.B, self.nA = mem, int(batch_size), int(num_actions)
         B, nA, dev = self.B, self.nA, mem.device
@@ -40,13 +41,25 @@ class HostStepPipeline:
             self.slots.append(slot)
         self.loss_kind, self.kappa = loss_kind, kappa
         self._k = 0
+        o = mem._outputs(B, False)
+        self._batch = o
+        self._lib = _C.lib()
+        for k, s in enumerate(self.slots):                 # everything apexb200_host_step needs, prebuilt
+            s["event"].record()                            # materialises the cudaEvent_t
+            s["args"] = (mem._h, k, _C.ptr(s["h_in"]), _C.C.c_void_p(s["h_in"].data_ptr() + B * 8), B, nA, float(mem.eps),
+                         int(loss_kind), float(kappa), _C.ptr(o["S_t"]), _C.ptr(o["S_tpn"]), _C.ptr(o["A"]), _C.ptr(o["R"]),
+                         _C.ptr(o["Gamma"]), _C.ptr(s["h_out"]), _C.C.c_void_p(s["event"].cuda_event),
+                         _C.stream_ptr())                  # kernels run on the stream current at construction
+            out = s["h_out"].numpy()
+            s["views"] = (out[4 * B:4 * B + 1], out[B:2 * B], out[3 * B:4 * B].view(np.int32))
+            s["busy"] = False
+        self._host_step = self._lib.apexb200_host_step
+        torch.cuda.current_stream().synchronize()
         if use_graph:
             side = torch.cuda.Stream(device=dev)
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
-                self._enqueue(self.slots[0])               # warm-up outside capture
-                side.synchronize()
-                for slot in self.slots:
+                for slot in self.slots:                    # nothing allocates in _enqueue: capture directly
                     g = torch.cuda.CUDAGraph()
                     with torch.cuda.graph(g, stream=side):
                         self._enqueue(slot)
@@ -65,14 +78,18 @@ class HostStepPipeline:
         """u: float64 [B] host array of draws; q: float32 [3, B, nA] host array (Q(S_t), Q(S_tpn), Q_target(S_tpn)).
         Returns a ticket for result()."""
         s = self.slots[self._k % self.DEPTH]
-        s["event"].synchronize()                          # the slot's previous step has been read out
+        if s["busy"]:
+            s["event"].synchronize()                      # the slot's previous step has left the device
         s["u_host"][:] = u
         s["q_host"][:] = q
         if s["graph"] is not None:
             s["graph"].replay()
-        else:
-            self._enqueue(s)
-        s["event"].record()
+            s["event"].record()
+        else:                                              # one C call: H2D, K3+K4, K5+K2, D2H, event record
+            rc = self._host_step(*s["args"])
+            if rc:
+                _C.check(rc)
+        s["busy"] = True
         self._k += 1
         return self._k - 1
 
@@ -80,6 +97,6 @@ class HostStepPipeline:
         """Blocks until step `ticket` has finished; returns (loss_mean, priorities[B], indices[B]) host views."""
         s = self.slots[ticket % self.DEPTH]
         s["event"].synchronize()
-        out = s["h_out"].numpy()
-        B = self.B
-        return float(out[4 * B]), out[B:2 * B], out[3 * B:4 * B].view(np.int32)
+        s["busy"] = False
+        mean, prio, idx = s["views"]
+        return float(mean[0]), prio, idx

@@ -26,6 +26,7 @@ if ROOT not in sys.path:
 F_BYTES = 7056          # 84 x 84 uint8
 ALPHA = 0.6
 GAMMA_N = 0.99 ** 3
+NCU_DRAM_BYTES_PER_LAUNCH = 26_050_000      # sample_gather_kernel, B=512, C=4 (profiles/r01_ncu_full_sample_gather.csv)
 
 
 def parse():
@@ -335,7 +336,11 @@ def run_ours(args):
         ach = bytes_per_rec * B / (g_mean_us * 1e-6) / 1e9
         kname = "sample_gather_kernel" if fused else ("gather_tma_kernel" if args.gather_variant == 1 else "gather_vec_kernel")
         roofline = {"kernel": kname, "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
-                    "frac": round(ach / peak, 4), "traffic": None, "algorithmic_bytes_per_launch": bytes_per_rec * B,
+                    "frac": round(ach / peak, 4),
+                    "traffic": NCU_DRAM_BYTES_PER_LAUNCH if (fused and B == 512 and C == 4) else None,
+                    "traffic_source": "profiles/r01_ncu_full_sample_gather.csv (ncu --set full, B=512, C=4: "
+                                      "dram__bytes_read.sum 25.8 MB + dram__bytes_write.sum 0.23 MB per launch)",
+                    "algorithmic_bytes_per_launch": bytes_per_rec * B,
                     "launch_us_mean": round(g_mean_us, 3), "launches_timed": R_ * reps, "peak_source": peak_src,
                     "timing": "cuda events around %d replays of a CUDA graph of %d back-to-back launches "
                               "(includes one inter-launch gap per launch)" % (reps, R_),
@@ -353,7 +358,7 @@ def run_ours(args):
     e2e = None
     if world == 1:
         rng = np.random.default_rng(4321)
-        pipe = apex_b200.HostStepPipeline(mem, B, nA, use_graph=not args.no_graph)
+        pipe = apex_b200.HostStepPipeline(mem, B, nA)
         n_e = max(20, min(K, 2000))
         q_host = rng.standard_normal((P, 3, B, nA)).astype(np.float32)
         u_host = (np.arange(B) + rng.random((64, B))) / B         # host-side stratified draws
@@ -372,9 +377,9 @@ def run_ours(args):
         dt = time.perf_counter() - t0
         e2e = {"value": round(n_e * B / dt, 1), "unit": "transitions/s", "h2d_bytes_per_step": pipe.in_bytes,
                "d2h_bytes_per_step": pipe.out_words * 4, "steps": n_e, "ms_per_step": round(dt / n_e * 1e3, 4),
-               "api": "apex_b200.HostStepPipeline.submit(u_host, q_host)/result(): pinned H2D of draws+Q, fused "
-                      "sample+gather, TD+update, D2H of loss/priorities/indices, one CUDA-graph launch per step, "
-                      "results read on the host one step behind (2 buffer sets)",
+               "api": "apex_b200.HostStepPipeline.submit(u_host, q_host)/result() -> C ABI apexb200_host_step: pinned H2D of "
+                      "draws+Q on a copy stream, fused sample+gather, TD+update, D2H of loss/priorities/indices on a copy "
+                      "stream, ordered by events; results read on the host one step behind (2 buffer sets)",
                "mean_loss": round(losses / n_e, 6)}
     clk = clocks.stop()
     mem.check_status()

@@ -252,6 +252,23 @@ int apexb200_td_fwd_update(apexb200_replay_t h, const int32_t *idx,
                            void *workspace, int64_t workspace_bytes,
                            const int32_t *count_dev, float mean_divisor, void *stream);
 
+/* ---- host-facing step: learner.py:68 (sample) -> :70 (loss, priorities) -> :76
+ * (set_priorities) for a caller that keeps its numbers on the host, as the reference does.
+ * u_host [B] fp64 draws and q_host [3, B, num_actions] fp32 (Q(S_t), Q(S_tpn), Q_target(S_tpn))
+ * are in pinned HOST memory (one H2D copy if q_host == u_host + B); S_t/S_tpn/A/R/Gamma are
+ * the learner's device batch tensors; result_host [4B+4] fp32, pinned, receives
+ * delta[B] | priority[B] | loss[B] | record index[B] (int32 bits) | loss_mean.  The kernels
+ * run on `stream`; the two copies run on copy streams owned by the handle and are ordered
+ * with events, so with alternating slot = 0, 1 the H2D copy of one step and the D2H copy of
+ * the previous one overlap the kernels.  done_event (cudaEvent_t, nullable) is recorded
+ * after the D2H copy; the call returns without synchronising.  A slot's host buffers may be
+ * refilled once its done_event has completed.  B <= 1024.  The first call (and any call
+ * with a larger B) creates the copy streams and allocates the device staging. */
+int apexb200_host_step(apexb200_replay_t h, int32_t slot, const double *u_host, const float *q_host, int32_t B,
+                       int32_t num_actions, float eps, int32_t loss_kind, float kappa,
+                       uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R, float *Gamma,
+                       float *result_host, void *done_event, void *stream);
+
 /* ---- K7 n-step return: ExperienceBuffer.update_buffer (actor.py:29-43),
  * intended semantics, vectorised over E actors x T steps --------
  * R[e,t] = sum_{k<m} gamma^k r[e,t+k], Gamma = gamma^m, or 0 when a terminal lies

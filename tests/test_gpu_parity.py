@@ -550,6 +550,43 @@ def test_peer_exchange_and_fused_sharded_sample_world1(apex):
     mem.check_status()
 
 
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_host_step_pipeline(apex, use_graph):
+    """apexb200_host_step / HostStepPipeline: host draws + Q in, host loss / priorities / indices out,
+    equal to the oracle's sample -> TD -> write-back on the same numbers, step after step."""
+    rng = np.random.default_rng(41)
+    N, C_, F, B, nA = 1 << 13, 2, 256, 96, 5
+    mem = make_mem(apex, N, C=C_, F=F, layout="stream", lanes=2, n=3)
+    ring = ro.RingOracle(N, C_, F, lanes=2, fpr=1, lookback=C_ - 1 + 3, alpha=0.6)
+    for lane in range(2):
+        m = N // 2 - 8
+        args = (lane, rng.integers(0, 256, (m, F), dtype=np.uint8), apex.stream_offsets(C_, np.full(m, 3), np.arange(m)),
+                rng.integers(0, nA, m).astype(np.int32), rng.standard_normal(m).astype(np.float32), np.full(m, 0.97, np.float32))
+        prio = (np.abs(rng.standard_normal(m)) + 1e-3).astype(np.float32)
+        mem.insert(*args, prio=prio)
+        ring.insert(*args, prio=prio)
+    ring.leaves[:] = u64(mem.buffer(apex._C.BUF_LEAVES))
+    pipe = apex.HostStepPipeline(mem, B, nA, use_graph=use_graph)
+    tickets, inputs = [], []
+    for k in range(5):
+        u = ro.stratified_uniforms(B, rng)
+        q = rng.standard_normal((3, B, nA)).astype(np.float32)
+        tickets.append(pipe.submit(u, q))
+        inputs.append((u, q))
+        if k >= 1:                                                   # read one step behind, as the bench does
+            t, (u0, q0) = tickets[k - 1], inputs[k - 1]
+            loss_mean, prio, idx = pipe.result(t)
+            want = ring.sample(u0)
+            np.testing.assert_array_equal(idx, want)
+            g = ring.gather(want)
+            o = to.td_forward(q0[0], q0[1], q0[2], g["A"], g["R"], g["G"], alpha=0.6)
+            np.testing.assert_allclose(prio, o["prio"], rtol=RTOL, atol=1e-7)
+            assert loss_mean == pytest.approx(o["loss_mean"], rel=RTOL)
+            ring.set_leaves(want, ro.priority_to_leaf(prio.copy()))
+    pipe.result(tickets[-1])
+    mem.check_status()
+
+
 # --------------------------------------------------------------- error behaviour
 def test_argument_errors(apex):
     _C = apex._C
