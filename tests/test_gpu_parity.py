@@ -587,6 +587,64 @@ def test_host_step_pipeline(apex, use_graph):
     mem.check_status()
 
 
+def test_vector_actor_ingest_matches_sliding_buffer(apex):
+    """K7 + K6 ingest of E lock-stepped environments == the host ExperienceBuffer(semantics="sliding")
+    fed the same steps, record by record (a10/a11/a3 on the device, frames stored once)."""
+    rng = np.random.default_rng(52)
+    E, n, C_, F, nA, lane_cap, gamma = 3, 3, 4, 16, 4, 256, 0.99
+    mem = apex.ReplayMemory(E * lane_cap, {"priority_exponent": 0.6, "layout": "stream", "lanes": E, "n_step": n,
+                                           "state_shape": (C_, 1, F), "num_actions": 0})
+    ing = apex.VectorActorIngest(mem, E, gamma=gamma)
+    steps = 150
+    frames = np.zeros((E, steps, F), np.uint8)
+    frames[:, :, 0] = np.arange(E)[:, None]
+    frames[:, :, 1] = np.arange(steps)[None, :] % 256                   # frame (e, tau) names itself
+    acts = rng.integers(0, nA, (E, steps)).astype(np.int32)
+    rews = rng.standard_normal((E, steps)).astype(np.float32)
+    dones = rng.random((E, steps)) < 0.06
+    qs = rng.standard_normal((E, steps, nA)).astype(np.float32)
+    for lo, hi in ((0, 40), (40, 41), (41, 97), (97, 150)):                # ragged chunks, including a 1-step chunk
+        ing.push(frames[:, lo:hi], acts[:, lo:hi], rews[:, lo:hi], dones[:, lo:hi], qs[:, lo:hi])
+    A_d, R_d, G_d = (mem.buffer(w).cpu().numpy() for w in (apex._C.BUF_ACTION, apex._C.BUF_REWARD, apex._C.BUF_GAMMA))
+    leaves = u64(mem.buffer(apex._C.BUF_LEAVES))
+    fidx = mem.buffer(apex._C.BUF_FIDX).cpu().numpy().reshape(-1, 2 * C_)
+    store = mem.buffer(apex._C.BUF_FRAMES).cpu().numpy().reshape(-1, F)
+    for e in range(E):
+        buf = apex.ExperienceBuffer(n, e, semantics="sliding", gamma=gamma)
+        for t in range(steps):
+            buf.add(apex.Transition(t, int(acts[e, t]), float(rews[e, t]), gamma, qs[e, t]))
+            if dones[e, t]:
+                buf.construct_nstep_transition(apex.Transition(t + 1, 0, 0, gamma, qs[e, min(t + 1, steps - 1)]))
+        recs = {r.S_t: r for r in buf.get(buf.size)}                       # keyed by step index t
+        ep_start = 0
+        starts = np.zeros(steps, np.int64)
+        for t in range(steps):
+            starts[t] = ep_start
+            if dones[e, t]:
+                ep_start = t + 1
+        assert (leaves[e * lane_cap: e * lane_cap + n] == 0).all()         # no record on the first n frames
+        for tau in range(n, steps):
+            t = tau - n
+            slot = e * lane_cap + tau
+            r = recs[t]                                                    # sliding buffer emitted step t (window complete by tau)
+            assert A_d[slot] == r.A_t
+            assert R_d[slot] == pytest.approx(r.R_ttpB, rel=RTOL, abs=1e-6)
+            assert G_d[slot] == pytest.approx(r.Gamma_ttpB, rel=RTOL)
+            want_p = abs(r.R_ttpB + r.Gamma_ttpB * float(qs[e, tau].max()) - float(qs[e, t, r.A_t]))
+            got_p = leaves[slot] / float(1 << 24)
+            assert got_p == pytest.approx(want_p ** 0.6, rel=1e-4, abs=2e-7)
+            # S_t = the C frames ending at t, repeated at the episode start; each frame names (env, time)
+            want_t = [max(t - b, starts[t]) for b in range(C_ - 1, -1, -1)]
+            got = store[fidx[slot, :C_]]
+            assert (got[:, 0] == e).all() and got[:, 1].tolist() == [x % 256 for x in want_t]
+            if r.Gamma_ttpB != 0.0:                                        # S_tpn only matters when we bootstrap
+                want_n = [max(tau - b, starts[tau]) for b in range(C_ - 1, -1, -1)]
+                got = store[fidx[slot, C_:]]
+                assert (got[:, 0] == e).all() and got[:, 1].tolist() == [x % 256 for x in want_n]
+                assert starts[tau] == starts[t]
+    mem.check_status()
+
+
 # --------------------------------------------------------------- error behaviour
 def test_argument_errors(apex):
     _C = apex._C
