@@ -372,7 +372,7 @@ int apexb200_host_step(apexb200_replay_t h, int32_t slot, const double *u_host, 
     if (rc) return rc;
     const size_t qs = (size_t)B * num_actions;
     rc = apexb200_td_fwd_update(h, d_idx, d_q, d_q + qs, d_q + 2 * qs, A, R, Gamma, B, num_actions, eps, loss_kind, kappa,
-                                d_delta, d_prio, d_loss, d_mean, nullptr, 0, nullptr, 0.0f, stream);
+                                nullptr, d_delta, d_prio, d_loss, d_mean, nullptr, 0, nullptr, 0.0f, stream);
     if (rc) return rc;
     APEX_CUDA(cudaEventRecord(h->hs_ev_k[slot], st));
     // copy-out stream

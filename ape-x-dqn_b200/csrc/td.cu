@@ -23,6 +23,7 @@ struct TdArgs {
     float alpha, eps, kappa;
     const int32_t *count_dev;       // nullable: live rows = min(B, *count_dev) (sharded batches)
     float divisor;                  // loss_mean = sum / divisor (0 -> B); global batch size when sharded
+    const float *weights;           // nullable: per-record importance weights multiplying the loss
 };
 
 __device__ __forceinline__ int live_rows(const TdArgs &a) { return a.count_dev ? min(a.B, *a.count_dev) : a.B; }
@@ -48,6 +49,7 @@ __device__ __forceinline__ float td_one(const TdArgs &a, int b, float *loss_out)
     float l;
     if (a.loss_kind == APEXB200_LOSS_HALF_SQ) l = __fmul_rn(__fmul_rn(0.5f, d), d);   // learner.py:48
     else l = ad <= a.kappa ? __fmul_rn(__fmul_rn(0.5f, d), d) : __fmul_rn(a.kappa, __fsub_rn(ad, 0.5f * a.kappa));
+    if (a.weights) l = __fmul_rn(l, a.weights[b]);                              // importance-sampling correction
     a.delta[b] = d;
     a.prio[b] = prio_pow(ad, a.alpha, a.eps);                                   // learner.py:50 + replay.py:24
     a.loss[b] = l;
@@ -176,7 +178,7 @@ td_multi_kernel(TdArgs a, const int32_t *__restrict__ idx, uint32_t *__restrict_
 __global__ void __launch_bounds__(256)
 td_bwd_kernel(const float *__restrict__ delta, const int32_t *__restrict__ A, const float *__restrict__ grad_out,
               int B, int nA, int loss_kind, float kappa, const int32_t *__restrict__ count_dev, float divisor,
-              float *__restrict__ grad_q) {
+              const float *__restrict__ weights, float *__restrict__ grad_q) {
     pdl_prologue();
     long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= (long long)B * nA) return;
@@ -187,6 +189,7 @@ td_bwd_kernel(const float *__restrict__ delta, const int32_t *__restrict__ A, co
         float d = delta[b];
         if (loss_kind == APEXB200_LOSS_HUBER) d = fminf(fmaxf(d, -kappa), kappa);
         g = -d * (*grad_out) / (divisor > 0.0f ? divisor : (float)B);   // d(mean loss)/dQ(S_t)[b, A_b]
+        if (weights) g *= weights[b];
     }
     grad_q[e] = g;
 }
@@ -225,6 +228,31 @@ initial_priority_kernel(const float *__restrict__ q_t, const float *__restrict__
     int a = A[j];
     a = a < 0 ? 0 : (a >= nA ? nA - 1 : a);
     abs_td[j] = fabsf(__fsub_rn(__fadd_rn(R[j], __fmul_rn(G[j], mx)), qa[a]));   // actor.py:138-140
+}
+
+// Importance-sampling weights of PER (parameters.json:30, README.md:25 TODO — never read by
+// the reference): w_j = (N * leaf_j / total)^(-beta), divided by the batch maximum.  Single CTA.
+__global__ void __launch_bounds__(1024)
+is_weights_kernel(const unsigned long long *__restrict__ leaf, const unsigned long long *__restrict__ total, int B,
+                  float n_records, float beta, float *__restrict__ w) {
+    __shared__ float wmax[32];
+    pdl_prologue();
+    const double tot = (double)(*total);
+    float local = 0.0f;
+    for (int j = threadIdx.x; j < B; j += blockDim.x) {
+        const double p = (double)leaf[j] / tot;
+        const float v = p > 0.0 ? powf((float)(n_records * p), -beta) : 0.0f;
+        w[j] = v;
+        local = fmaxf(local, v);
+    }
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) local = fmaxf(local, __shfl_xor_sync(0xffffffffu, local, o));
+    if ((threadIdx.x & 31) == 0) wmax[threadIdx.x >> 5] = local;
+    __syncthreads();
+    float m = 0.0f;
+    for (int k = 0; k < (int)((blockDim.x + 31) >> 5); ++k) m = fmaxf(m, wmax[k]);
+    if (m > 0.0f)
+        for (int j = threadIdx.x; j < B; j += blockDim.x) w[j] = w[j] / m;
 }
 
 static int td_check(const float *q1, const float *q2, const float *q3, const int32_t *A, const float *R,
@@ -311,12 +339,12 @@ int apexb200_td_workspace_bytes(int32_t B, int64_t *bytes_host) {
 
 int apexb200_td_fwd(const float *q_on_t, const float *q_on_tpn, const float *q_tg_tpn, const int32_t *A,
                     const float *R, const float *Gamma, int32_t B, int32_t num_actions, float alpha, float eps,
-                    int32_t loss_kind, float kappa, float *delta, float *prio, float *loss, float *loss_mean,
-                    void *workspace, int64_t workspace_bytes, void *stream) {
+                    int32_t loss_kind, float kappa, const float *weights, float *delta, float *prio, float *loss,
+                    float *loss_mean, void *workspace, int64_t workspace_bytes, void *stream) {
     int rc = td_check(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, B, num_actions, delta, prio, loss, loss_mean);
     if (rc) return rc;
     TdArgs a{q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, delta, prio, loss, loss_mean, B, num_actions, loss_kind,
-             alpha, eps, kappa, nullptr, 0.0f};
+             alpha, eps, kappa, nullptr, 0.0f, weights};
     return td_launch(nullptr, nullptr, a, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
@@ -337,34 +365,42 @@ int apexb200_td_fwd_noalloc(const float *q_on_t, const float *q_on_tpn, const fl
     // zero (each CTA overwrites its own partial before the last CTA reads them).
     APEX_CUDA(cudaMemsetAsync(scratch, 0, 256, st));
     TdArgs a{q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, delta, prio, loss, loss_mean, B, num_actions, loss_kind,
-             alpha, eps, kappa, nullptr, 0.0f};
+             alpha, eps, kappa, nullptr, 0.0f, nullptr};
     return launch_step("td_multi_kernel", td_multi_kernel, dim3((B + 255) / 256), dim3(256), 0, st, a,
                        (const int32_t *)nullptr, (uint32_t *)nullptr, 0ll, (int32_t *)nullptr,
                        (unsigned int *)scratch, (float *)((char *)scratch + 256));
 }
 
+int apexb200_is_weights(const uint64_t *leaf, const uint64_t *total, int32_t B, int64_t n_records, float beta,
+                        float *weights, void *stream) {
+    APEX_REQUIRE(leaf && total && weights && B > 0 && n_records > 0, APEXB200_EINVAL, "is_weights: bad argument");
+    return launch_step("is_weights_kernel", is_weights_kernel, dim3(1), dim3(B < 1024 ? ((B + 31) / 32) * 32 : 1024), 0,
+                       (cudaStream_t)stream, (const unsigned long long *)leaf, (const unsigned long long *)total, B,
+                       (float)n_records, beta, weights);
+}
+
 int apexb200_td_fwd_update(apexb200_replay_t h, const int32_t *idx, const float *q_on_t, const float *q_on_tpn,
                            const float *q_tg_tpn, const int32_t *A, const float *R, const float *Gamma, int32_t B,
-                           int32_t num_actions, float eps, int32_t loss_kind, float kappa, float *delta,
-                           float *prio, float *loss, float *loss_mean, void *workspace, int64_t workspace_bytes,
-                           const int32_t *count_dev, float mean_divisor, void *stream) {
+                           int32_t num_actions, float eps, int32_t loss_kind, float kappa, const float *weights,
+                           float *delta, float *prio, float *loss, float *loss_mean, void *workspace,
+                           int64_t workspace_bytes, const int32_t *count_dev, float mean_divisor, void *stream) {
     APEX_REQUIRE(h && idx, APEXB200_EINVAL, "td_fwd_update: null handle/idx");
     int rc = td_check(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, B, num_actions, delta, prio, loss, loss_mean);
     if (rc) return rc;
     TdArgs a{q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, delta, prio, loss, loss_mean, B, num_actions, loss_kind,
-             h->ring.alpha, eps, kappa, count_dev, mean_divisor};
+             h->ring.alpha, eps, kappa, count_dev, mean_divisor, weights};
     return td_launch(h, idx, a, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 
 int apexb200_td_bwd(const float *delta, const int32_t *A, const float *grad_loss_mean, int32_t B,
                     int32_t num_actions, int32_t loss_kind, float kappa, const int32_t *count_dev,
-                    float mean_divisor, float *grad_q, void *stream) {
+                    float mean_divisor, const float *weights, float *grad_q, void *stream) {
     APEX_REQUIRE(delta && A && grad_loss_mean && grad_q && B > 0 && num_actions >= 1, APEXB200_EINVAL,
                  "td_bwd: bad argument");
     long long n = (long long)B * num_actions;
     return launch_step("td_bwd_kernel", td_bwd_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0,
                        (cudaStream_t)stream, delta, A, grad_loss_mean, B, num_actions, loss_kind, kappa, count_dev,
-                       mean_divisor, grad_q);
+                       mean_divisor, weights, grad_q);
 }
 
 int apexb200_nstep(const float *rewards, const uint8_t *dones, int32_t E, int32_t T, int32_t n, float gamma,

@@ -32,13 +32,16 @@ class _TDLoss(torch.autograd.Function):
     (learner.py:43-48: the target is built under no_grad)."""
 
     @staticmethod
-    def forward(ctx, q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, replay, idx, alpha, eps, loss_kind, kappa):
+    def forward(ctx, q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, replay, idx, alpha, eps, loss_kind, kappa, weights=None):
         q_on_t, q_on_tpn, q_tg_tpn = (x.detach().contiguous().float() for x in (q_on_t, q_on_tpn, q_tg_tpn))
         if replay is not None:
-            delta, prio, loss, mean = replay.td_update(idx, q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, loss_kind, kappa)
+            delta, prio, loss, mean = replay.td_update(idx, q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, loss_kind, kappa,
+                                                       weights=weights)
         else:
-            delta, prio, loss, mean = ops.td_forward(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, alpha, eps, loss_kind, kappa)
+            delta, prio, loss, mean = ops.td_forward(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, alpha, eps, loss_kind, kappa,
+                                                     weights=weights)
         ctx.save_for_backward(delta, A)
+        ctx.weights = weights
         ctx.meta = (q_on_t.shape[1], loss_kind, kappa)
         ctx.mark_non_differentiable(delta, prio, loss)
         return mean.reshape(()), delta, prio, loss
@@ -48,14 +51,15 @@ class _TDLoss(torch.autograd.Function):
         delta, A = ctx.saved_tensors
         nA, loss_kind, kappa = ctx.meta
         g = g_mean.detach().reshape(1).float().contiguous()
-        return (ops.td_backward(delta, A, g, nA, loss_kind, kappa),) + (None,) * 11
+        return (ops.td_backward(delta, A, g, nA, loss_kind, kappa, weights=ctx.weights),) + (None,) * 12
 
 
 def td_loss(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, alpha=0.6, eps=0.0, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0,
-            replay=None, idx=None):
+            replay=None, idx=None, weights=None):
     """Differentiable fused loss.  Returns (loss_mean, delta, prio, loss).  With `replay` and `idx`
-    the new priorities are also written into the replay's sum tree in the same call."""
-    return _TDLoss.apply(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, replay, idx, alpha, eps, loss_kind, kappa)
+    the new priorities are also written into the replay's sum tree in the same call; `weights`
+    (f32 [B], e.g. ops.is_weights) multiply the per-record loss and gradient."""
+    return _TDLoss.apply(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, replay, idx, alpha, eps, loss_kind, kappa, weights)
 
 
 class Learner(object):

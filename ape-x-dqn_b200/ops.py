@@ -19,15 +19,24 @@ def td_workspace(B, device):
 
 
 def td_forward(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, alpha, eps=0.0, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0,
-               workspace=None):
+               workspace=None, weights=None):
     """learner.py:43-52 on device: returns (delta[B], prio[B], loss[B], loss_mean[1])."""
     B, nA = q_on_t.shape
     delta, prio, loss, mean = _f32(B, q_on_t), _f32(B, q_on_t), _f32(B, q_on_t), _f32(1, q_on_t)
     ws = workspace if workspace is not None else td_workspace(B, q_on_t.device)
     _C.call("apexb200_td_fwd", _C.ptr(q_on_t), _C.ptr(q_on_tpn), _C.ptr(q_tg_tpn), _C.ptr(A), _C.ptr(R), _C.ptr(Gamma),
-            int(B), int(nA), float(alpha), float(eps), int(loss_kind), float(kappa), _C.ptr(delta), _C.ptr(prio),
-            _C.ptr(loss), _C.ptr(mean), _C.ptr(ws), int(ws.numel()), _C.stream_ptr())
+            int(B), int(nA), float(alpha), float(eps), int(loss_kind), float(kappa), _C.ptr(weights), _C.ptr(delta),
+            _C.ptr(prio), _C.ptr(loss), _C.ptr(mean), _C.ptr(ws), int(ws.numel()), _C.stream_ptr())
     return delta, prio, loss, mean
+
+
+def is_weights(leaf, total, n_records, beta):
+    """PER importance weights from the leaf / total outputs of a sample call -> f32 [B], max-normalised."""
+    B = leaf.numel()
+    w = _f32(B, leaf)
+    _C.call("apexb200_is_weights", _C.ptr(leaf), _C.ptr(total), int(B), int(n_records), float(beta), _C.ptr(w),
+            _C.stream_ptr())
+    return w
 
 
 def td_forward_noalloc(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, alpha, eps=0.0, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0,
@@ -45,12 +54,13 @@ def td_forward_noalloc(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, alpha, eps=0.0, 
 
 
 def td_backward(delta, A, grad_loss_mean, num_actions, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0, count_dev=None,
-                mean_divisor=0.0):
+                mean_divisor=0.0, weights=None):
     import torch
     B = delta.numel()
     grad_q = torch.empty((B, num_actions), dtype=torch.float32, device=delta.device)
     _C.call("apexb200_td_bwd", _C.ptr(delta), _C.ptr(A), _C.ptr(grad_loss_mean), int(B), int(num_actions),
-            int(loss_kind), float(kappa), _C.ptr(count_dev), float(mean_divisor), _C.ptr(grad_q), _C.stream_ptr())
+            int(loss_kind), float(kappa), _C.ptr(count_dev), float(mean_divisor), _C.ptr(weights), _C.ptr(grad_q),
+            _C.stream_ptr())
     return grad_q
 
 

@@ -374,7 +374,7 @@ class ReplayMemory(object):
         return self._ws
 
     def td_update(self, idx, q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0, out=None,
-                  count_dev=None, mean_divisor=0.0):
+                  count_dev=None, mean_divisor=0.0, weights=None):
         """K5 + K2 fused (learner.py:70 + :76): returns (delta, prio, loss, loss_mean) device tensors.
         count_dev / mean_divisor: live-row count on the device and global batch size for sharded batches."""
         import torch
@@ -385,7 +385,7 @@ class ReplayMemory(object):
         ws = self.workspace(B)
         _C.call("apexb200_td_fwd_update", self._h, _C.ptr(idx), _C.ptr(q_on_t), _C.ptr(q_on_tpn), _C.ptr(q_tg_tpn),
                 _C.ptr(A), _C.ptr(R), _C.ptr(Gamma), int(B), int(nA), self.eps, int(loss_kind), float(kappa),
-                _C.ptr(out[0]), _C.ptr(out[1]), _C.ptr(out[2]), _C.ptr(out[3]), _C.ptr(ws), int(ws.numel()),
+                _C.ptr(weights), _C.ptr(out[0]), _C.ptr(out[1]), _C.ptr(out[2]), _C.ptr(out[3]), _C.ptr(ws), int(ws.numel()),
                 _C.ptr(count_dev), float(mean_divisor), self._stream())
         return out
 

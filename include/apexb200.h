@@ -205,8 +205,15 @@ int apexb200_td_workspace_bytes(int32_t B, int64_t *bytes_host);
 int apexb200_td_fwd(const float *q_on_t, const float *q_on_tpn, const float *q_tg_tpn,
                     const int32_t *A, const float *R, const float *Gamma, int32_t B,
                     int32_t num_actions, float alpha, float eps, int32_t loss_kind, float kappa,
-                    float *delta, float *prio, float *loss, float *loss_mean,
+                    const float *weights, float *delta, float *prio, float *loss, float *loss_mean,
                     void *workspace, int64_t workspace_bytes, void *stream);
+/* Importance-sampling weights of prioritized replay (parameters.json:30
+ * importance_sampling_exponent, README.md:25 TODO: never read by the reference):
+ * weights[j] = (n_records * leaf[j] / total)^(-beta) / max_j, from the leaf and total
+ * outputs of the sample calls.  Passed as `weights` (nullable everywhere) they multiply the
+ * per-record loss and its gradient in td_fwd / td_fwd_update / td_bwd. */
+int apexb200_is_weights(const uint64_t *leaf, const uint64_t *total, int32_t B, int64_t n_records,
+                        float beta, float *weights, void *stream);
 /* apexb200_td_fwd without a workspace argument.  (No counterpart in the reference: it
  * exists for the way this library gets embedded.)  The loss reduction needs a few KB of
  * device scratch.  Some callers have nowhere to get it from: a C or ctypes binding that
@@ -237,7 +244,7 @@ int apexb200_td_fwd_noalloc(const float *q_on_t, const float *q_on_tpn, const fl
  * count_dev / mean_divisor as in td_fwd_update (NULL / 0 for a plain batch). */
 int apexb200_td_bwd(const float *delta, const int32_t *A, const float *grad_loss_mean, int32_t B,
                     int32_t num_actions, int32_t loss_kind, float kappa, const int32_t *count_dev,
-                    float mean_divisor, float *grad_q, void *stream);
+                    float mean_divisor, const float *weights, float *grad_q, void *stream);
 /* K5 + K2 fused: td_fwd, then the new priorities are written into the leaves of
  * idx [B] and their ancestors refreshed (learner.py:70 + :76 in one call).
  * Sharded batches: count_dev (nullable) is a device int32 with the
@@ -248,7 +255,7 @@ int apexb200_td_fwd_update(apexb200_replay_t h, const int32_t *idx,
                            const float *q_on_t, const float *q_on_tpn, const float *q_tg_tpn,
                            const int32_t *A, const float *R, const float *Gamma, int32_t B,
                            int32_t num_actions, float eps, int32_t loss_kind, float kappa,
-                           float *delta, float *prio, float *loss, float *loss_mean,
+                           const float *weights, float *delta, float *prio, float *loss, float *loss_mean,
                            void *workspace, int64_t workspace_bytes,
                            const int32_t *count_dev, float mean_divisor, void *stream);
 

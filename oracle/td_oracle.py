@@ -22,7 +22,7 @@ LOSS_HUBER = 1     # north_star option, kappa = huber_kappa
 
 
 def td_forward(q_on_t, q_on_tpn, q_tg_tpn, A, R, G, alpha=0.6, loss_kind=LOSS_HALF_SQ,
-               kappa=1.0, eps=0.0, dtype=np.float32):
+               kappa=1.0, eps=0.0, dtype=np.float32, weights=None):
     """Returns dict(delta, abs_td, prio (|delta|^alpha), loss, loss_mean)."""
     f = dtype
     q_on_t, q_on_tpn, q_tg_tpn = (np.asarray(x, f) for x in (q_on_t, q_on_tpn, q_tg_tpn))
@@ -38,19 +38,31 @@ def td_forward(q_on_t, q_on_tpn, q_tg_tpn, A, R, G, alpha=0.6, loss_kind=LOSS_HA
     else:
         k = f(kappa)
         loss = np.where(ad <= k, f(0.5) * delta * delta, k * (ad - f(0.5) * k))
+    if weights is not None:
+        loss = loss * np.asarray(weights, f)               # importance-sampling correction (not in the reference)
     base = np.maximum(ad, f(eps)) if eps > 0 else ad
     prio = np.power(base, f(alpha)).astype(f)
     return dict(delta=delta, abs_td=ad, prio=prio, loss=loss.astype(f),
                 loss_mean=f(np.sum(loss.astype(np.float64)) / A.shape[0]), a_star=a_star)
 
 
+def is_weights(leaf_u64, total, n_records, beta):
+    """PER importance weights w = (N * P)^(-beta) / max w, P = leaf / total (parameters.json:30, unused upstream)."""
+    p = np.asarray(leaf_u64, np.float64) / float(total)
+    w = np.where(p > 0, (n_records * p) ** (-float(beta)), 0.0)
+    return (w / w.max()).astype(np.float32)
+
+
 def td_backward(delta, A, num_actions, grad_out=1.0, loss_kind=LOSS_HALF_SQ, kappa=1.0,
-                dtype=np.float32):
+                dtype=np.float32, weights=None):
     """d loss_mean / d Q_online(S_t): -dloss/ddelta / B at [b, A_b], 0 elsewhere."""
     f = dtype
     delta = np.asarray(delta, f)
     B = delta.shape[0]
     g = delta if loss_kind == LOSS_HALF_SQ else np.clip(delta, -f(kappa), f(kappa))
     out = np.zeros((B, num_actions), f)
-    out[np.arange(B), np.asarray(A, np.int64)] = -g * f(grad_out) / f(B)
+    col = -g * f(grad_out) / f(B)
+    if weights is not None:
+        col = col * np.asarray(weights, f)
+    out[np.arange(B), np.asarray(A, np.int64)] = col
     return out

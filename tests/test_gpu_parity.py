@@ -409,6 +409,33 @@ def test_td_forward_backward(apex, B, kind, nA):
     assert again.item() == mean.item()
 
 
+def test_importance_weights_and_weighted_loss(apex):
+    rng = np.random.default_rng(61)
+    N, B, nA, beta = 20000, 512, 4, 0.4
+    leaves = ro.priority_to_leaf(ro.pow_priority(np.abs(rng.standard_normal(N)) + 1e-3, 0.6))
+    mem = make_mem(apex, N)
+    load_leaves(apex, mem, leaves)
+    u = rng.random(B)
+    leaf_out = torch.empty(B, dtype=torch.int64, device="cuda")
+    total_out = torch.empty(1, dtype=torch.int64, device="cuda")
+    idx = mem.sample_indices(dev(u), leaf_out=leaf_out, total_out=total_out).cpu().numpy()
+    w = apex.ops.is_weights(leaf_out, total_out, N, beta)
+    want_w = to.is_weights(leaves[idx], int(leaves.sum(dtype=np.uint64)), N, beta)
+    np.testing.assert_allclose(w.cpu().numpy(), want_w, rtol=1e-5)
+    assert w.max().item() == 1.0
+    q = [rng.standard_normal((B, nA)).astype(np.float32) for _ in range(3)]
+    A = rng.integers(0, nA, B).astype(np.int32)
+    R, G = rng.standard_normal(B).astype(np.float32), np.full(B, 0.97, np.float32)
+    t1 = torch.tensor(q[0], device="cuda", requires_grad=True)
+    loss, delta, prio, per = apex.td_loss(t1, dev(q[1]), dev(q[2]), dev(A), dev(R), dev(G), alpha=0.6, weights=w)
+    loss.backward()
+    o = to.td_forward(q[0], q[1], q[2], A, R, G, alpha=0.6, weights=want_w)
+    np.testing.assert_allclose(per.cpu().numpy(), o["loss"], rtol=RTOL, atol=1e-7)
+    np.testing.assert_allclose(loss.item(), o["loss_mean"], rtol=RTOL)
+    np.testing.assert_allclose(prio.cpu().numpy(), o["prio"], rtol=RTOL, atol=1e-7)       # priorities are unweighted
+    np.testing.assert_allclose(t1.grad.cpu().numpy(), to.td_backward(o["delta"], A, nA, weights=want_w), rtol=RTOL, atol=1e-9)
+
+
 def test_td_loss_autograd_matches_torch(apex):
     torch.manual_seed(0)
     B, nA = 300, 6
