@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libapexb200.so")
+LIB_PATH = os.environ.get("APEXB200_LIB", os.path.join(_HERE, "libapexb200.so"))   # override: A/B of two builds
 
 OK, EINVAL, ECUDA, ENOMEM, ERANGE = 0, -1, -2, -3, -4
 LOSS_HALF_SQ, LOSS_HUBER = 0, 1

@@ -208,12 +208,14 @@ gather_tma_kernel(RingView rv, GatherArgs ga, int per_cta, int32_t *status) {
     tma_drain_frames(moving, dst, stage + (size_t)lane * rv.F, bars + lane * kMaxChunks, (unsigned)rv.F, nch);
 }
 
-// ---- fused K3 + K4: one warp per draw, `wpc` warps per CTA.  Each warp descends the
-// tree for its draw, lanes 0..2C-1 read the record's frame slots and each moves one
-// frame with the TMA engine while lane 16 copies the metadata row.  wpc * 2C * F bytes
-// of staging per CTA: at C=4 four draws (32 frames) per CTA, so a B=512 batch is 128
-// CTAs — a single wave with one CTA per SM and every frame of the batch in flight.
-__global__ void __launch_bounds__(256)
+// ---- fused K3 + K4: one warp per HALF draw (the C frames of S_t, or those of S_tpn),
+// `wpc` warps per CTA.  Each warp descends the tree for its draw (the two halves of a draw
+// repeat the descent: a few hundred bytes of L2 reads), lanes 0..C-1 read the frame slots
+// of their half and each moves one frame with the TMA engine; the S_t half also writes the
+// index and metadata outputs.  Half draws as the unit of work balance the frames over the
+// SMs: a B=512, C=4 batch is 1024 units = 147 CTAs of 7 warps (28 frames, 193 KB of
+// staging each), one CTA per SM, every frame of the batch in flight at once.
+__global__ void __launch_bounds__(512)
 sample_gather_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int32_t *ctrl) {
     extern __shared__ __align__(128) uint8_t smem[];
     unsigned long long *bars = (unsigned long long *)smem;
@@ -222,39 +224,43 @@ sample_gather_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int
     const int wl = threadIdx.x >> 5;
     const int wpc = blockDim.x >> 5;
     const int nch = frame_chunks(rv.F);
-    const int w = blockIdx.x * wpc + wl;
+    const int unit = blockIdx.x * wpc + wl;
+    const int w = unit >> 1, half = unit & 1;
     const int count = ga.count;
-    const int twoC = 2 * rv.C;
+    const int C = rv.C, twoC = 2 * rv.C;
     if (w >= count) return;
-    uint8_t *stage = smem + (size_t)wpc * 16 * kMaxChunks * 8 + (size_t)(wl * twoC + lane) * rv.F;
-    unsigned long long *my_bars = bars + (wl * 16 + lane) * kMaxChunks;
+    uint8_t *stage = smem + (size_t)wpc * 8 * kMaxChunks * 8 + (size_t)(wl * C + lane) * rv.F;
+    unsigned long long *my_bars = bars + (wl * 8 + lane) * kMaxChunks;
     const bool strat = (sa.u == nullptr);
     const unsigned long long vtop = top_level_value(tv);     // in flight while the draw is formed
     double uw;
     if (strat) {
         uw = strat_uniform(sa.seed, read_epoch(ctrl), sa.call, w, count);
-        if (sa.u_out && lane == 0) sa.u_out[w] = uw;
+        if (sa.u_out && lane == 0 && half == 0) sa.u_out[w] = uw;
     } else {
         uw = sa.u[w];
     }
     unsigned long long leaf, total;
     const long long node = warp_descend(tv, vtop, 0ull, true, uw, &leaf, &total, ctrl);
+    const int k = half * C + lane;                           // this lane's frame among the record's 2C
     long long f = -1;
-    if (node >= 0 && lane < twoC) f = rv.fidx[node * twoC + lane];
+    if (node >= 0 && lane < C) f = rv.fidx[node * twoC + k];
     bool moving = false;
-    if (node >= 0 && lane < twoC) {
+    if (node >= 0 && lane < C) {
         if (f < 0 || f >= rv.N * rv.fpr) atomicOr(ctrl, APEXB200_ST_BAD_INDEX);
         else { moving = true; tma_load_frame(rv.frames + f * rv.F, stage, my_bars, (unsigned)rv.F, nch); }
     }
     // bookkeeping overlaps the frame loads
-    if (lane < twoC && sa.fsel_out) sa.fsel_out[(long long)w * twoC + lane] = (int32_t)f;
-    if (lane == 0) {
-        sa.idx_out[w] = (int32_t)node;
-        if (sa.leaf_out) sa.leaf_out[w] = node >= 0 ? leaf : 0ull;
-        if (sa.total_out && w == 0) *sa.total_out = total;
+    if (lane < C && sa.fsel_out) sa.fsel_out[(long long)w * twoC + k] = (int32_t)f;
+    if (half == 0) {
+        if (lane == 0) {
+            sa.idx_out[w] = (int32_t)node;
+            if (sa.leaf_out) sa.leaf_out[w] = node >= 0 ? leaf : 0ull;
+            if (sa.total_out && w == 0) *sa.total_out = total;
+        }
+        if (node >= 0 && lane == 16) copy_meta_row(rv, ga, w, node);
     }
-    if (node >= 0 && lane == 16) copy_meta_row(rv, ga, w, node);
-    tma_drain_frames(moving, moving ? item_dst(rv, ga, w, lane) : nullptr, stage, my_bars, (unsigned)rv.F, nch);
+    tma_drain_frames(moving, moving ? item_dst(rv, ga, w, k) : nullptr, stage, my_bars, (unsigned)rv.F, nch);
 }
 
 // ---- fused K8 + K3 + K4 for one rank of a sharded replay (after shard_exchange_kernel).
@@ -297,7 +303,7 @@ __device__ __forceinline__ int first_draw_at_or_above(unsigned long long bound, 
     return lo;
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(512)
 sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, ShardArgs sh, PeerView pv,
                              int32_t *ctrl) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -307,8 +313,9 @@ sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs
     const int wl = threadIdx.x >> 5;
     const int wpc = blockDim.x >> 5;
     const int nch = frame_chunks(rv.F);
-    const int row = blockIdx.x + wl * gridDim.x;
-    const int twoC = 2 * rv.C;
+    const int unit = blockIdx.x + wl * gridDim.x;            // half rows dealt round-robin over the CTAs
+    const int row = unit >> 1, half = unit & 1;
+    const int C = rv.C, twoC = 2 * rv.C;
     const unsigned long long vtop = top_level_value(tv);
     const int world = pv.world, rank = pv.rank;
     // the shard totals of the current round (pushed by shard_exchange_kernel or by the peers'
@@ -329,12 +336,12 @@ sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs
     const unsigned long long hi = __shfl_sync(0xffffffffu, incl, rank);
     const unsigned long long lo = hi - __shfl_sync(0xffffffffu, tg, rank);
     if (T == 0ull) {
-        if (lane == 0) { atomicOr(ctrl, APEXB200_ST_EMPTY_TREE); if (row == 0) *sh.count_out = 0; }
+        if (lane == 0) { atomicOr(ctrl, APEXB200_ST_EMPTY_TREE); if (unit == 0) *sh.count_out = 0; }
         return;
     }
     const int Bg = sh.global_count;
     const int j_lo = first_draw_at_or_above(lo, sa.seed, round, sh.call, Bg, T);
-    if (row == 0) {
+    if (unit == 0) {
         const int j_hi = first_draw_at_or_above(hi, sa.seed, round, sh.call, Bg, T);
         int cnt = j_hi - j_lo;
         if (cnt > sh.max_rows) { cnt = sh.max_rows; if (lane == 0) atomicOr(ctrl, APEXB200_ST_QUOTA); }
@@ -347,23 +354,26 @@ sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs
     if (t >= hi) return;                                     // beyond this rank's run of draws
     unsigned long long leaf, total;
     const long long node = warp_descend(tv, vtop, t - lo, false, 0.0, &leaf, &total, ctrl);
-    uint8_t *stage = smem + (size_t)wpc * 16 * kMaxChunks * 8 + (size_t)(wl * twoC + lane) * rv.F;
-    unsigned long long *my_bars = bars + (wl * 16 + lane) * kMaxChunks;
+    uint8_t *stage = smem + (size_t)wpc * 8 * kMaxChunks * 8 + (size_t)(wl * C + lane) * rv.F;
+    unsigned long long *my_bars = bars + (wl * 8 + lane) * kMaxChunks;
+    const int k = half * C + lane;
     long long f = -1;
-    if (node >= 0 && lane < twoC) f = rv.fidx[node * twoC + lane];
+    if (node >= 0 && lane < C) f = rv.fidx[node * twoC + k];
     bool moving = false;
-    if (node >= 0 && lane < twoC) {
+    if (node >= 0 && lane < C) {
         if (f < 0 || f >= rv.N * rv.fpr) atomicOr(ctrl, APEXB200_ST_BAD_INDEX);
         else { moving = true; tma_load_frame(rv.frames + f * rv.F, stage, my_bars, (unsigned)rv.F, nch); }
     }
-    if (lane < twoC && sa.fsel_out) sa.fsel_out[(long long)row * twoC + lane] = (int32_t)f;
-    if (lane == 0) {
-        sa.idx_out[row] = (int32_t)node;
-        if (sh.pos_out) sh.pos_out[row] = j;
-        if (sa.u_out) sa.u_out[row] = uw;
+    if (lane < C && sa.fsel_out) sa.fsel_out[(long long)row * twoC + k] = (int32_t)f;
+    if (half == 0) {
+        if (lane == 0) {
+            sa.idx_out[row] = (int32_t)node;
+            if (sh.pos_out) sh.pos_out[row] = j;
+            if (sa.u_out) sa.u_out[row] = uw;
+        }
+        if (node >= 0 && lane == 16) copy_meta_row(rv, ga, row, node);
     }
-    if (node >= 0 && lane == 16) copy_meta_row(rv, ga, row, node);
-    tma_drain_frames(moving, moving ? item_dst(rv, ga, row, lane) : nullptr, stage, my_bars, (unsigned)rv.F, nch);
+    tma_drain_frames(moving, moving ? item_dst(rv, ga, row, k) : nullptr, stage, my_bars, (unsigned)rv.F, nch);
 }
 
 static int ensure_smem(const void *fn, size_t smem, int device) {
@@ -428,30 +438,31 @@ int apexb200_sample_gather(apexb200_replay_t h, const double *u, uint64_t seed, 
     APEX_REQUIRE((((uintptr_t)S_t | (uintptr_t)S_tpn) & 15) == 0, APEXB200_EINVAL,
                  "sample_gather: output batches must be 16-byte aligned");
     const RingView &rv = h->ring;
-    const size_t per_draw = (size_t)2 * rv.C * rv.F;
+    const size_t per_unit = (size_t)rv.C * rv.F + 8 * kMaxChunks * 8;       // one half draw: C frames + their mbarriers
     cudaStream_t st = (cudaStream_t)stream;
-    if (2 * rv.C > 16 || per_draw + 16 * kMaxChunks * 8 > kStageBudget) {
-        // staging for one record does not fit one CTA: run the two kernels back to back
+    if (rv.C > 8 || per_unit > kStageBudget) {
+        // staging for half a record does not fit one CTA: run the two kernels back to back
         int rc = u ? apexb200_sample(h, u, count, idx_out, leaf_out, total_out, fsel_out, stream)
                    : apexb200_sample_stratified(h, seed, count, idx_out, leaf_out, total_out, fsel_out, u_out, stream);
         if (rc) return rc;
         return apexb200_gather(h, idx_out, fsel_out, count, nullptr, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, stream);
     }
-    int wpc = (int)(kStageBudget / (per_draw + 16 * kMaxChunks * 8));      // draws (warps) per CTA that fit
-    if (wpc > 8) wpc = 8;
-    const int spread = (count + kNumSMs - 1) / kNumSMs;                    // small batches: use every SM
+    const int units = 2 * count;
+    int wpc = (int)(kStageBudget / per_unit);                              // units (warps) per CTA that fit
+    if (wpc > 16) wpc = 16;
+    const int spread = (units + kNumSMs - 1) / kNumSMs;                    // one wave: spread evenly over the SMs
     if (spread < wpc) wpc = spread;
-    // A batch that needs several waves runs faster with one draw per CTA (4 CTAs per SM: one CTA's
+    // A batch that needs several waves runs faster with thin CTAs (several CTAs per SM: one CTA's
     // tree descent overlaps another's frame movement; 78 vs 88 us at B=4096), a single-wave batch
     // with fat CTAs (profiles/r01_kernel_experiments.md).
-    if (count > wpc * kNumSMs) wpc = 1;
-    const size_t smem = (size_t)wpc * (per_draw + 16 * kMaxChunks * 8);
+    if (units > wpc * kNumSMs) wpc = 2;
+    const size_t smem = (size_t)wpc * per_unit;
     int rc = ensure_smem((const void *)sample_gather_kernel, smem, h->cfg.device);
     if (rc) return rc;
     SampleArgs sa{u, (unsigned long long)seed, u ? 0ull : h->draw_calls++, idx_out, fsel_out, (unsigned long long *)leaf_out,
                   (unsigned long long *)total_out, u_out};
     GatherArgs ga{idx_out, fsel_out, nullptr, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, count};
-    return launch_step("sample_gather_kernel", sample_gather_kernel, dim3((unsigned)((count + wpc - 1) / wpc)),
+    return launch_step("sample_gather_kernel", sample_gather_kernel, dim3((unsigned)((units + wpc - 1) / wpc)),
                        dim3(wpc * 32), smem, st, h->tree, rv, sa, ga, h->status);
 }
 
@@ -464,15 +475,16 @@ int apexb200_sample_gather_sharded(apexb200_replay_t h, uint64_t seed, int32_t g
     APEX_REQUIRE((((uintptr_t)S_t | (uintptr_t)S_tpn) & 15) == 0, APEXB200_EINVAL,
                  "sample_gather_sharded: output batches must be 16-byte aligned");
     const RingView &rv = h->ring;
-    const size_t per_draw = (size_t)2 * rv.C * rv.F + 16 * kMaxChunks * 8;
-    APEX_REQUIRE(2 * rv.C <= 16 && per_draw <= kStageBudget, APEXB200_ERANGE,
-                 "sample_gather_sharded: a record (2*%d frames of %d bytes) does not fit one CTA's staging", rv.C, rv.F);
-    int wpc = (int)(kStageBudget / per_draw);
-    if (wpc > 8) wpc = 8;
-    const int spread = (max_rows + kNumSMs - 1) / kNumSMs;
+    const size_t per_unit = (size_t)rv.C * rv.F + 8 * kMaxChunks * 8;       // one half row: C frames + their mbarriers
+    APEX_REQUIRE(rv.C <= 8 && per_unit <= kStageBudget, APEXB200_ERANGE,
+                 "sample_gather_sharded: half a record (%d frames of %d bytes) does not fit one CTA's staging", rv.C, rv.F);
+    const int units = 2 * max_rows;
+    int wpc = (int)(kStageBudget / per_unit);
+    if (wpc > 16) wpc = 16;
+    const int spread = (units + kNumSMs - 1) / kNumSMs;
     if (spread < wpc) wpc = spread;
-    const int ctas = (max_rows + wpc - 1) / wpc;
-    const size_t smem = (size_t)wpc * per_draw;
+    const int ctas = (units + wpc - 1) / wpc;
+    const size_t smem = (size_t)wpc * per_unit;
     int rc = ensure_smem((const void *)sample_gather_sharded_kernel, smem, h->cfg.device);
     if (rc) return rc;
     SampleArgs sa{nullptr, (unsigned long long)seed, 0ull, idx_out, fsel_out, nullptr, nullptr, u_out};

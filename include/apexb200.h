@@ -329,7 +329,8 @@ int apexb200_peer_push_on_update(apexb200_replay_t h, int32_t enabled);
  * record into row r of the outputs ([max_rows, ...]).  count_out [1] = rows owned (rows
  * beyond it are stale), pos_out [max_rows] = global draw index j of each row.  A shard
  * that owns more than max_rows draws keeps the first max_rows and sets
- * APEXB200_ST_QUOTA.  Needs 2*frames_per_state <= 16 and a record that fits shared memory. */
+ * APEXB200_ST_QUOTA.  Needs frames_per_state <= 8 and half a record (C frames) fitting in shared
+ * memory. */
 int apexb200_sample_gather_sharded(apexb200_replay_t h, uint64_t seed, int32_t global_count, int32_t max_rows,
                                    int32_t *idx_out, int32_t *fsel_out, int32_t *pos_out, double *u_out,
                                    int32_t *count_out, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R,
