@@ -83,10 +83,18 @@ __global__ void __launch_bounds__(1024)
 td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t *__restrict__ stamp,
                 int32_t *status, PeerView pv, int push) {
     __shared__ float warp_part[32];
+    __shared__ unsigned long long delta_part[32];
     pdl_prologue();
     if (idx != nullptr) bump_epoch(status);
     const int b = threadIdx.x;
     const int live = live_rows(a);
+    // multi-GPU push (see the tail of this kernel): the shard total before this update, read by
+    // warp 0 while the batch rows are being fetched
+    unsigned long long total_before = 0ull;
+    if (push && threadIdx.x < 32) {
+        const int top = tv.n_levels - 1;
+        total_before = threadIdx.x < tv.size[top] ? tv.lvl[top][threadIdx.x] : 0ull;
+    }
     float l = 0.0f;
     long long i = -1;
     bool in_order = true, last_of_run = true;
@@ -112,24 +120,54 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
     }
     float s = block_sum_fixed(l, warp_part);
     if (threadIdx.x == 0) *a.loss_mean = s / mean_div(a);
+    unsigned long long d = 0ull;
     if (winner) {
         unsigned long long nl = leaf_from_prio(a.prio[b]);
         tv.lvl[0][i] = nl;
-        unsigned long long d = nl - old;
+        d = nl - old;
+    }
+    if (!sorted) {
         if (d != 0ull) propagate_delta(tv, i, d);
+    } else if (idx != nullptr) {
+        // Sorted record indices (stratified draws): rows that share an ancestor are adjacent, so the
+        // deltas of a warp are summed per ancestor with a segmented shuffle scan and one atomic per
+        // distinct ancestor is issued (512 rows hit 2 nodes at the top level of a 2M-record tree:
+        // per-row atomics there serialise for ~1 us).  Level 1 ancestors are almost all distinct.
+        const int lane = threadIdx.x & 31;
+        if (d != 0ull && tv.n_levels > 1) atomicAdd(tv.lvl[1] + (i >> 5), d);
+        for (int l = 2; l < tv.n_levels; ++l) {
+            const long long key = i >= 0 ? (i >> (5 * l)) : (long long)(-1 - lane);
+            unsigned long long sum = d;
+            #pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const long long ks = __shfl_up_sync(0xffffffffu, key, o);
+                const unsigned long long vs = __shfl_up_sync(0xffffffffu, sum, o);
+                if (lane >= o && ks == key) sum += vs;
+            }
+            const long long kn = __shfl_down_sync(0xffffffffu, key, 1);
+            if ((lane == 31 || kn != key) && sum != 0ull && key >= 0) atomicAdd(tv.lvl[l] + key, sum);
+        }
     }
     if (!push) return;
     // Fused collective (multi-GPU): publish this shard's new total to every peer from the
     // kernel that produced it — the next step's sharded sample on each rank waits for these
-    // words instead of an all-gather.  All tree updates of this CTA are at L2 before the sum.
-    __threadfence();
+    // words instead of an all-gather.  new total = total before + sum of this batch's leaf
+    // deltas (exact in u64 arithmetic; this CTA is the only writer of the tree while it runs),
+    // so the push does not wait for the ancestor updates above to land.
+    {
+        unsigned long long ds = d;
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ds += __shfl_xor_sync(0xffffffffu, ds, o);
+        if ((threadIdx.x & 31) == 0) delta_part[threadIdx.x >> 5] = ds;
+    }
     __syncthreads();
     if (threadIdx.x < 32) {
         const int lane = threadIdx.x;
-        const int top = tv.n_levels - 1;
-        unsigned long long v = lane < tv.size[top] ? *(volatile unsigned long long *)(tv.lvl[top] + lane) : 0ull;
+        unsigned long long v = total_before;
         #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        const int nw = (blockDim.x + 31) >> 5;
+        for (int k = 0; k < nw; ++k) v += delta_part[k];
         const unsigned long long cur = read_round(status);
         if (lane < pv.world) {
             if (cur > 0ull) peer_wait_round(pv, cur, lane, status);     // already there in the steady state
