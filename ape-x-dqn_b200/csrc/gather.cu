@@ -282,12 +282,29 @@ __device__ __forceinline__ unsigned long long draw_target(unsigned long long see
     return t >= T ? T - 1ull : t;
 }
 
-// Smallest j in [0, Bg] whose target is >= bound (Bg if none): 32-ary search, every lane
-// evaluates one candidate per round.
+// Smallest j in [0, Bg] whose target is >= bound (Bg if none).  Stratified draws put
+// target_j near j * T / Bg, so the answer lies within one draw of bound * Bg / T: the 32
+// lanes first test a window around that estimate in one round; a 32-ary search over the
+// whole range is the fallback.
 __device__ __forceinline__ int first_draw_at_or_above(unsigned long long bound, unsigned long long seed,
                                                       unsigned long long round, unsigned long long call, int Bg,
                                                       unsigned long long T) {
     const int lane = threadIdx.x & 31;
+    if (bound == 0ull) return 0;
+    if (bound >= T) return Bg;
+    {
+        const long long est = (long long)((double)bound / (double)T * (double)Bg);
+        const long long j = est - 15 + lane;                 // window [est-15, est+16]
+        const bool ge = (j >= Bg) || (j >= 0 && draw_target(seed, round, call, (int)j, Bg, T, nullptr) >= bound);
+        const unsigned m = __ballot_sync(0xffffffffu, ge);
+        // monotone predicate: the answer is the first voting lane, provided the lane before it
+        // exists in the window (did not vote) or the window starts at draw 0
+        if (m != 0u) {
+            const int f = __ffs(m) - 1;
+            const long long ans = est - 15 + f;
+            if (f > 0 || ans <= 0) return (int)(ans < 0 ? 0 : (ans > Bg ? Bg : ans));
+        }
+    }
     int lo = 0, hi = Bg;                       // answer in [lo, hi]
     while (lo < hi) {
         const int span = hi - lo;
