@@ -62,6 +62,7 @@ SIGNATURES = {
     "apexb200_set_gather_variant": [_I32],
     "apexb200_sample_gather": [_P, _P, C.c_uint64, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "apexb200_set_pdl": [_I32],
+    "apexb200_set_td_cluster": [_I32],
     "apexb200_td_workspace_bytes": [_I32, C.POINTER(_I64)],
     "apexb200_td_fwd": [_P, _P, _P, _P, _P, _P, _I32, _I32, _F, _F, _I32, _F, _P, _P, _P, _P, _P, _P, _I64, _P],
     "apexb200_is_weights": [_P, _P, _I32, _I64, _F, _P, _P],

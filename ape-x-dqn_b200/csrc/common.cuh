@@ -45,6 +45,7 @@ struct RingView {
 void set_error(const char *fmt, ...);
 int cuda_fail(cudaError_t e, const char *what);
 extern int g_pdl;                            // programmatic dependent launch for the step kernels (default on)
+extern int g_td_cluster;                     // K5+K2 for B <= 1024 as one thread-block cluster (opt-in: measured slower)
 
 #define APEX_CUDA(call)                                                    \
     do {                                                                   \
@@ -73,22 +74,41 @@ __device__ __forceinline__ void pdl_prologue() {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 
+// `cluster` > 1 launches the grid as thread-block clusters of that many CTAs (grid.x must be
+// a multiple of it).
 template <typename... KArgs, typename... Args>
-inline int launch_step(const char *what, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
-                       cudaStream_t st, Args... args) {
+inline int launch_step_cluster(const char *what, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                               cudaStream_t st, int cluster, Args... args) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = block;
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int n = 0;
+    if (g_pdl) {
+        attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n].val.programmaticStreamSerializationAllowed = 1;
+        ++n;
+    }
+    if (cluster > 1) {
+        attr[n].id = cudaLaunchAttributeClusterDimension;
+        attr[n].val.clusterDim.x = (unsigned)cluster;
+        attr[n].val.clusterDim.y = 1;
+        attr[n].val.clusterDim.z = 1;
+        ++n;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = g_pdl ? 1 : 0;
+    cfg.numAttrs = n;
     cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
     if (e != cudaSuccess) return cuda_fail(e, what);
     return APEXB200_OK;
+}
+
+template <typename... KArgs, typename... Args>
+inline int launch_step(const char *what, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                       cudaStream_t st, Args... args) {
+    return launch_step_cluster(what, kernel, grid, block, smem, st, 1, args...);
 }
 
 // fp32 priority^alpha -> u64 fixed-point leaf (exact function of the fp32 value).

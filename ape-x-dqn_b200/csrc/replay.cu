@@ -10,6 +10,7 @@ namespace apexb200 {
 
 static thread_local char g_err[512] = "";
 int g_pdl = 1;
+int g_td_cluster = 0;
 
 void set_error(const char *fmt, ...) {
     va_list ap;
@@ -115,6 +116,11 @@ const char *apexb200_strerror(int code) {
 }
 
 const char *apexb200_last_error(void) { return g_err; }
+
+int apexb200_set_td_cluster(int32_t enabled) {
+    g_td_cluster = enabled ? 1 : 0;
+    return APEXB200_OK;
+}
 
 int apexb200_set_pdl(int32_t enabled) {
     g_pdl = enabled ? 1 : 0;

@@ -2,9 +2,13 @@
 // (+ backward, + in-place priority write-back), K7 n-step returns, and the actor's
 // initial priority.  All fp32, one thread per record; these kernels move a few
 // hundred bytes per record and are launch/latency bound, not bandwidth bound.
+#include <cooperative_groups.h>
+
 #include <mutex>
 
 #include "common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace apexb200 {
 
@@ -178,6 +182,123 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
     }
 }
 
+// ---- B <= 1024 as one thread-block cluster: ceil(B/128) CTAs of 128 rows on as many SMs
+// (opt-in, apexb200_set_td_cluster; measured slower than td_small_kernel on B200, see the header).
+// The single-CTA kernel issues all of a batch's leaf/ancestor atomics and row loads from one
+// SM (~1.6 us of a 5.5 us in-step K5+K2 at B=512); here they issue from up to 8 SMs.  The
+// CTAs meet in CTA 0's shared memory through DSMEM: per-CTA loss partials (summed there in
+// CTA order -> deterministic), the "is the batch sorted" vote and the multi-GPU total delta.
+constexpr int kTdClusterRows = 128;
+constexpr int kTdClusterMax = 8;
+
+__global__ void __launch_bounds__(kTdClusterRows)
+td_cluster_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t *__restrict__ stamp,
+                  int32_t *status, PeerView pv, int push) {
+    cg::cluster_group cluster = cg::this_cluster();
+    const int nc = (int)cluster.num_blocks(), cr = (int)cluster.block_rank();
+    __shared__ float warp_part[kTdClusterRows / 32];
+    __shared__ float cta_loss[kTdClusterMax];                 // filled in CTA 0
+    __shared__ unsigned long long cta_delta[kTdClusterMax];   // filled in CTA 0
+    __shared__ int cta_unsorted[kTdClusterMax];               // filled in every CTA
+    pdl_prologue();
+    if (idx != nullptr) bump_epoch(status);
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int live = live_rows(a);
+    unsigned long long total_before = 0ull;
+    if (push && cr == 0 && threadIdx.x < 32) {
+        const int top = tv.n_levels - 1;
+        total_before = threadIdx.x < tv.size[top] ? tv.lvl[top][threadIdx.x] : 0ull;
+    }
+    float l = 0.0f;
+    long long i = -1;
+    bool in_order = true, last_of_run = true;
+    unsigned long long old = 0ull;
+    if (b < live) {
+        if (idx != nullptr) {
+            i = idx[b];
+            const long long nxt = (b + 1 < live) ? (long long)idx[b + 1] : (1ll << 40);
+            in_order = i <= nxt;
+            last_of_run = i != nxt;
+            if (i < 0 || i >= tv.size[0]) { atomicOr(status, APEXB200_ST_BAD_INDEX); i = -1; }
+            else old = tv.lvl[0][i];
+        }
+        td_one(a, b, &l);
+    }
+    cluster.sync();                                            // every CTA of the cluster is running: DSMEM is usable
+    // cluster-wide vote: is the whole batch in non-decreasing index order?
+    const int cta_sorted = __syncthreads_and(in_order);
+    if (threadIdx.x < nc) *cluster.map_shared_rank(&cta_unsorted[cr], threadIdx.x) = !cta_sorted;
+    const float s = block_sum_fixed(l, warp_part);             // per-CTA loss partial (valid in thread 0)
+    if (threadIdx.x == 0) *cluster.map_shared_rank(&cta_loss[cr], 0) = s;
+    cluster.sync();
+    bool sorted = true;
+    for (int r = 0; r < nc; ++r) sorted = sorted && !cta_unsorted[r];
+    bool winner = (i >= 0) && last_of_run;
+    if (!sorted) {
+        if (i >= 0) atomicMax(stamp + i, (uint32_t)b + 1u);
+        cluster.sync();
+        winner = false;
+        if (i >= 0 && __ldcg(stamp + i) == (uint32_t)b + 1u) { winner = true; stamp[i] = 0u; }
+    }
+    unsigned long long d = 0ull;
+    if (winner) {
+        unsigned long long nl = leaf_from_prio(a.prio[b]);
+        tv.lvl[0][i] = nl;
+        d = nl - old;
+    }
+    if (!sorted) {
+        if (d != 0ull) propagate_delta(tv, i, d);
+    } else if (idx != nullptr) {
+        if (d != 0ull && tv.n_levels > 1) atomicAdd(tv.lvl[1] + (i >> 5), d);
+        for (int lv = 2; lv < tv.n_levels; ++lv) {              // one atomic per distinct ancestor per warp
+            const long long key = i >= 0 ? (i >> (5 * lv)) : (long long)(-1 - lane);
+            unsigned long long sum = d;
+            #pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const long long ks = __shfl_up_sync(0xffffffffu, key, o);
+                const unsigned long long vs = __shfl_up_sync(0xffffffffu, sum, o);
+                if (lane >= o && ks == key) sum += vs;
+            }
+            const long long kn = __shfl_down_sync(0xffffffffu, key, 1);
+            if ((lane == 31 || kn != key) && sum != 0ull && key >= 0) atomicAdd(tv.lvl[lv] + key, sum);
+        }
+    }
+    if (push) {                                                 // this CTA's share of the total delta -> CTA 0
+        __shared__ unsigned long long dpart[kTdClusterRows / 32];
+        unsigned long long ds = d;
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ds += __shfl_xor_sync(0xffffffffu, ds, o);
+        if (lane == 0) dpart[threadIdx.x >> 5] = ds;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned long long t = 0ull;
+            for (int k = 0; k < kTdClusterRows / 32; ++k) t += dpart[k];
+            *cluster.map_shared_rank(&cta_delta[cr], 0) = t;
+        }
+        cluster.sync();
+    }
+    if (cr != 0) return;
+    if (threadIdx.x == 0) {
+        float tot = 0.0f;
+        for (int r = 0; r < nc; ++r) tot += cta_loss[r];        // CTA order: same association every run
+        *a.loss_mean = tot / mean_div(a);
+    }
+    if (push && threadIdx.x < 32) {                            // fused collective, see td_small_kernel
+        unsigned long long v = total_before;
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        for (int r = 0; r < nc; ++r) v += cta_delta[r];
+        const unsigned long long cur = read_round(status);
+        if (lane < pv.world) {
+            if (cur > 0ull) peer_wait_round(pv, cur, lane, status);
+            peer_push_round(pv, cur + 1ull, lane, v);
+        }
+        __syncwarp();
+        if (lane == 0) *(volatile unsigned long long *)(status + 6) = cur + 1ull;
+    }
+}
+
 // ---- any B: 256 records per CTA; per-CTA loss partials go to scratch and the last
 // CTA to finish (ticket counter in scratch) adds them in CTA order.
 // scratch layout: [0] u32 ticket (zeroed by the host before launch), [64..] float partials.
@@ -310,6 +431,14 @@ static int64_t td_ws_bytes(int B) {
 static int td_launch(apexb200_replay *h, const int32_t *idx, const TdArgs &a, void *workspace, int64_t ws_bytes,
                      cudaStream_t st) {
     TreeView tv_none{};
+    if (a.B <= 1024 && g_td_cluster) {
+        PeerView pv_none{};
+        const int nc = (a.B + kTdClusterRows - 1) / kTdClusterRows;
+        return launch_step_cluster("td_cluster_kernel", td_cluster_kernel, dim3(nc), dim3(kTdClusterRows), 0, st, nc, a,
+                                   h ? h->tree : tv_none, idx, h ? h->stamp : (uint32_t *)nullptr,
+                                   h ? h->status : (int32_t *)nullptr, h ? h->peers : pv_none,
+                                   (h && idx && h->push_on_update) ? 1 : 0);
+    }
     if (a.B <= 1024) {
         PeerView pv_none{};
         return launch_step("td_small_kernel", td_small_kernel, dim3(1), dim3(((a.B + 31) / 32) * 32), 0, st, a,

@@ -193,6 +193,12 @@ int apexb200_sample_gather(apexb200_replay_t h, const double *u, uint64_t seed, 
  * scheduled while its predecessor on the stream drains and blocks on
  * griddepcontrol.wait before touching memory.  0 = plain stream-ordered launches. */
 int apexb200_set_pdl(int32_t enabled);
+/* K5 / K5+K2 for B <= 1024 as ONE thread-block cluster of ceil(B/128) CTAs instead of one CTA:
+ * the rows are spread over up to 8 SMs, the loss partials and the multi-GPU total delta meet in
+ * the first CTA's shared memory (distributed shared memory), and cluster barriers order the
+ * duplicate-resolution phases.  Default 0: measured on B200 at B=512 the two cluster barriers
+ * cost more than the extra SMs save (4.7 vs 3.8 us per launch, 16.6 vs 16.2 us per step). */
+int apexb200_set_td_cluster(int32_t enabled);
 
 /* ---- K5 loss / TD / priority: Learner.compute_loss_and_priorities
  * (learner.py:43-52) ---------------------------------------------------------

@@ -456,8 +456,18 @@ def test_td_loss_autograd_matches_torch(apex):
     torch.testing.assert_close(prio, (tgt - qsa).abs().pow(0.6), rtol=RTOL, atol=1e-7)
 
 
-@pytest.mark.parametrize("B", [64, 512, 1024, 3000])
-def test_td_update_writes_priorities_in_place(apex, B):
+@pytest.mark.parametrize("cluster", [1, 0])
+@pytest.mark.parametrize("B", [64, 100, 512, 1024, 3000])
+def test_td_update_writes_priorities_in_place(apex, B, cluster):
+    apex._C.call("apexb200_set_td_cluster", cluster)
+    try:
+        _td_update_case(apex, B, sorted_idx=False)
+        _td_update_case(apex, B, sorted_idx=True)
+    finally:
+        apex._C.call("apexb200_set_td_cluster", 0)
+
+
+def _td_update_case(apex, B, sorted_idx):
     rng = np.random.default_rng(B)
     N, nA = 1 << 16, 4
     mem = make_mem(apex, N)
@@ -465,6 +475,8 @@ def test_td_update_writes_priorities_in_place(apex, B):
     load_leaves(apex, mem, leaves)
     idx = rng.integers(0, N, B).astype(np.int32)
     idx[1::9] = idx[0]                                                             # duplicates: last row wins
+    if sorted_idx:
+        idx = np.sort(idx)                                                         # stratified draws: adjacent duplicates
     q = [rng.standard_normal((B, nA)).astype(np.float32) for _ in range(3)]
     A = rng.integers(0, nA, B).astype(np.int32)
     R, G = rng.standard_normal(B).astype(np.float32), np.full(B, 0.97, np.float32)
