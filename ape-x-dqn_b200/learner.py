@@ -82,6 +82,7 @@ class Learner(object):
         self.replay_memory = shared_replay_memory
         self.optimizer = torch.optim.RMSprop(self.Q.parameters(), lr=0.00025 / 4, weight_decay=0.95, eps=1.5e-7)
         self.num_q_updates = 0
+        self._graph = None
         self.loss_kind = _C.LOSS_HUBER if self.params.get("loss", "half_sq") == "huber" else _C.LOSS_HALF_SQ
         self.kappa = float(self.params.get("huber_kappa", 1.0))
         self.alpha = float(self.params.get("priority_exponent", getattr(shared_replay_memory, "alpha", 0.6)))
@@ -143,7 +144,61 @@ class Learner(object):
         S_t, S_tpn = b.S_t.view(shape).float(), b.S_tpn.view(shape).float()
         loss, delta, prio, _ = self._loss_from_tensors(S_t, S_tpn, b.A, b.R, b.Gamma, replay=self.replay_memory, idx=b.idx)
         self.update_Q(loss)
+        return loss.detach()              # no autograd graph leaves this call (capture_step needs them all gone)
+
+    def _maybe_sync_target(self):
+        freq = self.params["q_target_sync_freq"]
+        literal = bool(self.params.get("literal_target_sync", False))
+        if (self.num_q_updates % freq != 0) if literal else (self.num_q_updates % freq == 0):
+            self.Q_double.load_state_dict(self.Q.state_dict())
+
+    def capture_step(self):
+        """Capture one fast-tier learner step — K3+K4, the three forwards, backward, RMSprop, K5+K2 — in a
+        CUDA graph.  Returns nothing; step_graphed() replays it.  The sampling kernel draws
+        fresh stratified numbers on every replay (device-side epoch), the target-network sync stays outside.
+        Losses returned by earlier compute_loss_and_priorities calls must have been released: a live
+        autograd graph pins gradient-accumulation nodes to the stream they were created on."""
+        dev = self._to_device()
+        for g in self.optimizer.param_groups:
+            g["capturable"] = True                       # keeps RMSprop's step counters on the device
+        for st in self.optimizer.state.values():         # counters created by earlier eager steps live on the host
+            if torch.is_tensor(st.get("step")) and st["step"].device != dev:
+                st["step"] = st["step"].to(dev)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):                            # warm-up: optimizer state, cuDNN plans, output buffers
+                self.optimizer.zero_grad(set_to_none=True)
+                loss = self._step_body()
+                loss.backward()
+                self.optimizer.step()
+                self.num_q_updates += 1
+                del loss
+            side.synchronize()
+            self._graph = torch.cuda.CUDAGraph()
+            self.optimizer.zero_grad(set_to_none=True)
+            with torch.cuda.graph(self._graph, stream=side):
+                self._graph_loss = self._step_body()
+                self._graph_loss.backward()
+                self.optimizer.step()
+        torch.cuda.current_stream().wait_stream(side)
+
+    def _step_body(self):
+        B = int(self.params["replay_sample_size"])
+        b = self.replay_memory.sample_tensors(B)
+        shape = (B,) + tuple(self.state_shape)
+        S_t, S_tpn = b.S_t.view(shape).float(), b.S_tpn.view(shape).float()
+        loss, _delta, _prio, _ = self._loss_from_tensors(S_t, S_tpn, b.A, b.R, b.Gamma, replay=self.replay_memory, idx=b.idx)
         return loss
+
+    def step_graphed(self):
+        """Replay the captured step; returns the (device) loss tensor of that step."""
+        if self._graph is None:
+            self.capture_step()
+        self._graph.replay()
+        self.num_q_updates += 1
+        self._maybe_sync_target()
+        return self._graph_loss.detach()
 
     def learn(self, T):
         """learner.py:63-80."""

@@ -804,6 +804,13 @@ def test_learner_compat_and_fast_tier(apex):
     assert L.num_q_updates == 6 and all(np.isfinite(losses)) and mem.total() != before
     sd_q, sd_t = L.Q.state_dict(), L.Q_double.state_dict()
     assert all(torch.equal(sd_q[k], sd_t[k]) for k in sd_q)                 # target sync at update 6 (freq 3)
+    # the same step captured as one CUDA graph (model included): replays keep learning and keep updating priorities
+    del loss, ref, qsa, g_ref
+    w_before = [p.detach().clone() for p in L.Q.parameters()]
+    t_before = mem.total()
+    g_losses = [float(L.step_graphed()) for _ in range(4)]
+    assert all(np.isfinite(g_losses)) and mem.total() != t_before
+    assert any((a != b).any().item() for a, b in zip(w_before, L.Q.parameters()))
     mem.check_status()
 
 
