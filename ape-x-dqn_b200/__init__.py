@@ -12,7 +12,7 @@ from .learner import Learner, td_loss                         # noqa: F401
 from . import ops                                             # noqa: F401
 from .sharded import ShardedSampler                           # noqa: F401
 from .pipeline import HostStepPipeline                        # noqa: F401
-from .ingest import VectorActorIngest                         # noqa: F401
+from .ingest import VectorActorIngest, ActorStagingRing, RingIngest   # noqa: F401
 
 __all__ = ["ReplayMemory", "Learner", "Actor", "ExperienceBuffer", "N_Step_Transition", "Transition", "Batch",
-           "KeyIndex", "stream_offsets", "td_loss", "ops", "ShardedSampler", "HostStepPipeline", "VectorActorIngest"]
+           "KeyIndex", "stream_offsets", "td_loss", "ops", "ShardedSampler", "HostStepPipeline", "VectorActorIngest", "ActorStagingRing", "RingIngest"]

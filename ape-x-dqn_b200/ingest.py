@@ -24,10 +24,11 @@ from .replay import stream_offsets
 
 
 class VectorActorIngest:
-    def __init__(self, mem, num_envs, n_step=None, gamma=0.99):
+    def __init__(self, mem, num_envs, n_step=None, gamma=0.99, lanes=None):
         mem._ensure()
-        if mem.layout != "stream" or mem.lanes != num_envs:
-            raise ValueError("VectorActorIngest needs a stream-layout replay with one lane per environment")
+        self.lanes = list(range(num_envs)) if lanes is None else [int(x) for x in lanes]
+        if mem.layout != "stream" or len(self.lanes) != num_envs or max(self.lanes) >= mem.lanes:
+            raise ValueError("VectorActorIngest needs a stream-layout replay and one lane per environment")
         self.mem, self.E = mem, int(num_envs)
         self.n = int(n_step if n_step is not None else mem.n_step)
         if mem.lookback < mem.C - 1 + self.n:
@@ -91,11 +92,117 @@ class VectorActorIngest:
         prio = ops.initial_priority(q_t.reshape(E * T, -1), q_tpn.reshape(E * T, -1), A_rec.reshape(-1), R_rec.reshape(-1),
                                     G_rec.reshape(-1)).view(E, T) * prio_mask
         for e in range(E):                                                   # K6, one lane per env
-            mem.insert(e, frames[e].reshape(T, -1), rel[e], A_rec[e], R_rec[e], G_rec[e], prio=prio[e].contiguous())
+            mem.insert(self.lanes[e], frames[e].reshape(T, -1), rel[e], A_rec[e], R_rec[e], G_rec[e],
+                       prio=prio[e].contiguous())
         self.c_act, self.c_rew, self.c_done, self.c_q = (act[:, -n:].contiguous(), rew[:, -n:].contiguous(),
                                                          don[:, -n:].contiguous(), qq[:, -n:].contiguous())
         self.seen += T
         return E * T
 
 
-__all__ = ["VectorActorIngest", "stream_offsets"]
+class ActorStagingRing:
+    """Single-producer / single-consumer ring of step chunks in named shared host memory: the
+    actor -> replay transport (replaces the Manager queue + pickle of main.py:21-25 /
+    actor.py:181-187, 566 KB of pickle per 5 records).  An actor process writes chunks of T env
+    steps (uint8 frames, actions, rewards, dones, Q rows) with plain memcpys; the process that
+    owns the replay maps the same memory, registers it with CUDA (page-locked) and copies each
+    chunk to the device asynchronously before handing it to VectorActorIngest.
+
+    Layout: int64 control[8] = (produced, consumed, closed, ...), then `slots` chunks of
+    frames [T, F] u8 | actions [T] i32 | rewards [T] f32 | dones [T] u8 (padded) | q [T, nA] f32.
+    """
+
+    def __init__(self, name, slots, chunk_steps, frame_bytes, num_actions, create):
+        from multiprocessing import shared_memory
+        self.slots, self.T, self.F, self.nA = int(slots), int(chunk_steps), int(frame_bytes), int(num_actions)
+        T, F, nA = self.T, self.F, self.nA
+        self.off_act = T * F
+        self.off_rew = self.off_act + 4 * T
+        self.off_done = self.off_rew + 4 * T
+        self.off_q = self.off_done + ((T + 15) // 16) * 16
+        self.slot_bytes = ((self.off_q + 4 * T * nA + 255) // 256) * 256
+        total = 256 + self.slots * self.slot_bytes
+        self.shm = shared_memory.SharedMemory(name=name, create=create, size=total if create else 0)
+        self.ctrl = np.ndarray((8,), np.int64, self.shm.buf, 0)
+        if create:
+            self.ctrl[:] = 0
+        self._data = np.ndarray((self.slots, self.slot_bytes), np.uint8, self.shm.buf, 256)
+        self._registered = False
+
+    # views of slot k
+    def _views(self, k):
+        raw, T, F, nA = self._data[k], self.T, self.F, self.nA
+        return (raw[:T * F].reshape(T, F), raw[self.off_act:self.off_act + 4 * T].view(np.int32),
+                raw[self.off_rew:self.off_rew + 4 * T].view(np.float32), raw[self.off_done:self.off_done + T],
+                raw[self.off_q:self.off_q + 4 * T * nA].view(np.float32).reshape(T, nA))
+
+    # ---- producer side (actor process, no CUDA)
+    def push(self, frames, actions, rewards, dones, q):
+        """Write one chunk of T steps; returns False (nothing written) when the ring is full."""
+        produced, consumed = int(self.ctrl[0]), int(self.ctrl[1])
+        if produced - consumed >= self.slots:
+            return False
+        f, a, r, d, qq = self._views(produced % self.slots)
+        f[...] = np.asarray(frames, np.uint8).reshape(self.T, self.F)
+        a[...] = actions
+        r[...] = rewards
+        d[...] = np.asarray(dones).astype(np.uint8)
+        qq[...] = q
+        self.ctrl[0] = produced + 1                       # publish after the payload (x86 store order; SPSC)
+        return True
+
+    # ---- consumer side (process that owns the replay)
+    def register_cuda(self):
+        """Page-lock the shared memory for this process so that H2D copies out of it are asynchronous."""
+        if not self._registered:
+            ptr = self._data.ctypes.data - 256
+            rc = torch.cuda.cudart().cudaHostRegister(ptr, 256 + self.slots * self.slot_bytes, 0)
+            self._registered = int(rc) == 0
+        return self._registered
+
+    def pop(self):
+        """-> (frames, actions, rewards, dones, q) host views of the oldest unread chunk, or None.
+        Call release() after the copies out of the views have been issued and completed."""
+        produced, consumed = int(self.ctrl[0]), int(self.ctrl[1])
+        if produced == consumed:
+            return None
+        return self._views(consumed % self.slots)
+
+    def release(self):
+        self.ctrl[1] = int(self.ctrl[1]) + 1
+
+    def close(self, unlink=False):
+        self.ctrl = self._data = None
+        self.shm.close()
+        if unlink:
+            self.shm.unlink()
+
+
+class RingIngest:
+    """Drains a set of ActorStagingRings (one per actor = one lane each) into a stream-layout replay."""
+
+    def __init__(self, mem, rings, n_step=None, gamma=0.99):
+        self.mem, self.rings = mem, list(rings)
+        self.lane_ingest = [VectorActorIngest(mem, 1, n_step=n_step, gamma=gamma, lanes=[k]) for k in range(len(self.rings))]
+        for r in self.rings:
+            r.register_cuda()
+
+    def poll(self):
+        """Move every chunk that is ready; returns the number of records inserted."""
+        n = 0
+        dev = self.mem.device
+        for ring, ing in zip(self.rings, self.lane_ingest):
+            while True:
+                chunk = ring.pop()
+                if chunk is None:
+                    break
+                f, a, r, d, q = chunk
+                tensors = [torch.from_numpy(x).to(dev, non_blocking=True) for x in (f, a, r, q)]
+                dones = d.copy()
+                torch.cuda.current_stream().synchronize()         # payload is on the device: the slot can be reused
+                ring.release()
+                n += ing.push(tensors[0][None], tensors[1][None], tensors[2][None], dones[None], tensors[3][None])
+        return n
+
+
+__all__ = ["VectorActorIngest", "ActorStagingRing", "RingIngest", "stream_offsets"]

@@ -171,3 +171,54 @@ if __name__ == "__main__":
 ''' % (ROOT, os.path.join(ROOT, "ape-x-dqn_b200", "dropin"))
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
     assert out.returncode == 0 and "proxy ok" in out.stdout, out.stderr[-2000:]
+
+
+def _ring_producer(name, slots, T, F, nA, chunks, seed):
+    import sys
+    sys.path.insert(0, ROOT)
+    import time
+    import numpy as np
+    import apex_b200
+    ring = apex_b200.ActorStagingRing(name, slots, T, F, nA, create=False)
+    rng = np.random.default_rng(seed)
+    for c in range(chunks):
+        payload = (rng.integers(0, 256, (T, F), dtype=np.uint8), rng.integers(0, nA, T).astype(np.int32),
+                   rng.standard_normal(T).astype(np.float32), rng.random(T) < 0.1, rng.standard_normal((T, nA)).astype(np.float32))
+        while not ring.push(*payload):
+            time.sleep(0.001)
+    ring.close()
+
+
+def test_actor_staging_ring_cross_process():
+    """Actor -> replay transport in shared host memory: a producer process writes chunks,
+    this process reads exactly what was written, in order, with back-pressure when the ring is full."""
+    import multiprocessing as mp
+    import apex_b200
+    slots, T, F, nA, chunks, seed = 3, 8, 64, 4, 11, 123
+    name = "apexring_test_%d" % os.getpid()
+    ring = apex_b200.ActorStagingRing(name, slots, T, F, nA, create=True)
+    try:
+        p = mp.get_context("spawn").Process(target=_ring_producer, args=(name, slots, T, F, nA, chunks, seed))
+        p.start()
+        rng = np.random.default_rng(seed)
+        got = 0
+        import time
+        t0 = time.time()
+        while got < chunks and time.time() - t0 < 60:
+            chunk = ring.pop()
+            if chunk is None:
+                time.sleep(0.001)
+                continue
+            f, a, r, d, q = chunk
+            np.testing.assert_array_equal(f, rng.integers(0, 256, (T, F), dtype=np.uint8))
+            np.testing.assert_array_equal(a, rng.integers(0, nA, T).astype(np.int32))
+            np.testing.assert_array_equal(r, rng.standard_normal(T).astype(np.float32))
+            np.testing.assert_array_equal(d.astype(bool), rng.random(T) < 0.1)
+            np.testing.assert_array_equal(q, rng.standard_normal((T, nA)).astype(np.float32))
+            assert int(ring.ctrl[0]) - int(ring.ctrl[1]) <= slots
+            ring.release()
+            got += 1
+        p.join(timeout=30)
+        assert got == chunks and p.exitcode == 0 and ring.pop() is None
+    finally:
+        ring.close(unlink=True)

@@ -684,6 +684,63 @@ def test_vector_actor_ingest_matches_sliding_buffer(apex):
     mem.check_status()
 
 
+def _ring_actor(name, slots, T, F, nA, chunks, seed):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import time
+    import apex_b200
+    ring = apex_b200.ActorStagingRing(name, slots, T, F, nA, create=False)
+    rng = np.random.default_rng(seed)
+    for c in range(chunks):
+        payload = (rng.integers(0, 256, (T, F), dtype=np.uint8), rng.integers(0, nA, T).astype(np.int32),
+                   rng.standard_normal(T).astype(np.float32), rng.random(T) < 0.1, rng.standard_normal((T, nA)).astype(np.float32))
+        while not ring.push(*payload):
+            time.sleep(0.001)
+    ring.close()
+
+
+def test_ring_ingest_from_actor_processes(apex):
+    """Two actor processes (no CUDA) stream step chunks through shared-memory rings; the replay's
+    process drains them into the device ring.  Result == feeding the same chunks directly."""
+    import multiprocessing as mp
+    import time
+    E, T, F, nA, C_, n, chunks, slots, lane_cap = 2, 16, 64, 4, 2, 3, 9, 3, 512
+    params = {"priority_exponent": 0.6, "layout": "stream", "lanes": E, "n_step": n, "state_shape": (C_, 1, F)}
+    mem = apex.ReplayMemory(E * lane_cap, params)
+    ref = apex.ReplayMemory(E * lane_cap, params)
+    names = ["apexring_gpu_%d_%d" % (os.getpid(), e) for e in range(E)]
+    rings = [apex.ActorStagingRing(nm, slots, T, F, nA, create=True) for nm in names]
+    try:
+        procs = [mp.get_context("spawn").Process(target=_ring_actor, args=(names[e], slots, T, F, nA, chunks, 900 + e))
+                 for e in range(E)]
+        for p in procs:
+            p.start()
+        ingest = apex.RingIngest(mem, rings, n_step=n)
+        assert all(r._registered for r in rings)                       # page-locked for async H2D
+        want, t0 = E * chunks * T, time.time()
+        got = 0
+        while got < want and time.time() - t0 < 120:
+            got += ingest.poll()
+            time.sleep(0.002)
+        for p in procs:
+            p.join(timeout=30)
+        assert got == want and all(p.exitcode == 0 for p in procs)
+        direct = [apex.VectorActorIngest(ref, 1, n_step=n, lanes=[e]) for e in range(E)]
+        for e in range(E):
+            rng = np.random.default_rng(900 + e)
+            for c in range(chunks):
+                f, a, r = rng.integers(0, 256, (T, F), dtype=np.uint8), rng.integers(0, nA, T).astype(np.int32), rng.standard_normal(T).astype(np.float32)
+                d, q = rng.random(T) < 0.1, rng.standard_normal((T, nA)).astype(np.float32)
+                direct[e].push(f[None], a[None], r[None], d[None], q[None])
+        for which in (apex._C.BUF_FRAMES, apex._C.BUF_FIDX, apex._C.BUF_ACTION, apex._C.BUF_REWARD, apex._C.BUF_GAMMA, apex._C.BUF_LEAVES):
+            assert torch.equal(mem.buffer(which), ref.buffer(which)), which
+        assert mem.total() == ref.total() and mem.size() == ref.size() == want
+        mem.check_status()
+    finally:
+        for r in rings:
+            r.close(unlink=True)
+
+
 # --------------------------------------------------------------- error behaviour
 def test_argument_errors(apex):
     _C = apex._C
