@@ -15,8 +15,11 @@
  *     (PyTorch) owns every input/output buffer and keeps it alive until the
  *     stream has run past the call;
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
- *     no entry point synchronises or allocates except replay_create/destroy,
- *     replay_status and the *_host accessors;
+ *     the per-step entry points (sample*, gather, td_*, tree_update*, shard_exchange,
+ *     sample_gather_sharded, nstep, initial_priority, is_weights) only enqueue work:
+ *     they never synchronise and never allocate.  Allocation or synchronisation happens
+ *     only in replay_create/destroy, replay_status, peer_connect (maps peer memory) and
+ *     in the first call of host_step (copy streams + staging);
  *   - one replay handle is driven from one host thread at a time; calls on one
  *     stream are totally ordered, which is what gives add/sample/set_priorities
  *     their reference (sequential) semantics.
