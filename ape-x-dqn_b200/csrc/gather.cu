@@ -358,17 +358,13 @@ sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs
     }
     const int Bg = sh.global_count;
     const int j_lo = first_draw_at_or_above(lo, sa.seed, round, sh.call, Bg, T);
-    if (unit == 0) {
-        const int j_hi = first_draw_at_or_above(hi, sa.seed, round, sh.call, Bg, T);
-        int cnt = j_hi - j_lo;
-        if (cnt > sh.max_rows) { cnt = sh.max_rows; if (lane == 0) atomicOr(ctrl, APEXB200_ST_QUOTA); }
-        if (lane == 0) *sh.count_out = cnt;
-    }
     const int j = j_lo + row;
-    if (j >= Bg) return;
-    double uw;
-    const unsigned long long t = draw_target(sa.seed, round, sh.call, j, Bg, T, &uw);
-    if (t >= hi) return;                                     // beyond this rank's run of draws
+    double uw = 0.0;
+    const unsigned long long t = j < Bg ? draw_target(sa.seed, round, sh.call, j, Bg, T, &uw) : hi;
+    if (t >= hi) {                                           // beyond this rank's run of draws
+        if (unit == 0 && lane == 0) *sh.count_out = 0;       // (unit 0 dead: the rank owns no draw)
+        return;
+    }
     unsigned long long leaf, total;
     const long long node = warp_descend(tv, vtop, t - lo, false, 0.0, &leaf, &total, ctrl);
     uint8_t *stage = smem + (size_t)wpc * 8 * kMaxChunks * 8 + (size_t)(wl * C + lane) * rv.F;
@@ -389,6 +385,12 @@ sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs
             if (sa.u_out) sa.u_out[row] = uw;
         }
         if (node >= 0 && lane == 16) copy_meta_row(rv, ga, row, node);
+    }
+    if (unit == 0) {                                         // row count, computed in the shadow of the frame loads
+        const int j_hi = first_draw_at_or_above(hi, sa.seed, round, sh.call, Bg, T);
+        int cnt = j_hi - j_lo;
+        if (cnt > sh.max_rows) { cnt = sh.max_rows; if (lane == 0) atomicOr(ctrl, APEXB200_ST_QUOTA); }
+        if (lane == 0) *sh.count_out = cnt;
     }
     tma_drain_frames(moving, moving ? item_dst(rv, ga, row, k) : nullptr, stage, my_bars, (unsigned)rv.F, nch);
 }

@@ -94,10 +94,16 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
     const int live = live_rows(a);
     // multi-GPU push (see the tail of this kernel): the shard total before this update, read by
     // warp 0 while the batch rows are being fetched
-    unsigned long long total_before = 0ull;
+    unsigned long long total_before = 0ull, cur_round = 0ull, peer_word = 0ull;
     if (push && threadIdx.x < 32) {
         const int top = tv.n_levels - 1;
         total_before = threadIdx.x < tv.size[top] ? tv.lvl[top][threadIdx.x] : 0ull;
+        // the peers' words of the current round (normally consumed by the preceding sample already):
+        // fetched now so that the push at the tail does not wait for this read
+        cur_round = read_round(status);
+        if (threadIdx.x < pv.world && cur_round > 0ull)
+            peer_word = *(volatile unsigned long long *)(pv.xbuf[pv.rank] +
+                                                         (size_t)((int)(cur_round & 1ull) * kMaxShards + threadIdx.x));
     }
     float l = 0.0f;
     long long i = -1;
@@ -172,9 +178,10 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
         for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
         const int nw = (blockDim.x + 31) >> 5;
         for (int k = 0; k < nw; ++k) v += delta_part[k];
-        const unsigned long long cur = read_round(status);
+        const unsigned long long cur = cur_round;
         if (lane < pv.world) {
-            if (cur > 0ull) peer_wait_round(pv, cur, lane, status);     // already there in the steady state
+            if (cur > 0ull && (peer_word & 15ull) != (cur & 15ull))
+                peer_wait_round(pv, cur, lane, status);                 // not there at kernel start: wait now
             peer_push_round(pv, cur + 1ull, lane, v);
         }
         __syncwarp();
