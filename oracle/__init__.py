@@ -14,10 +14,12 @@ Parity status ("pinned" vs "unpinned"), per function:
   reference itself, generated in the build container by
   ``tests/golden/make_golden.py`` (imports /root/reference, writes
   ``tests/golden/*.json|npz``).
-* The learner arithmetic (``td_oracle``) follows learner.py:43-52, which raises
-  ``TypeError`` on this container's torch/numpy and therefore
-  cannot be executed: that part is a restatement with PARITY UNPINNED by the
-  reference (it is cross-checked against an independent torch fp64 evaluation).
+* The learner arithmetic (``td_oracle``) follows learner.py:43-52.  That function
+  raises ``TypeError`` on this container's torch/numpy as written (SURVEY Q14:
+  ndarray * Tensor); make_golden.py runs the unmodified function under an operator
+  shim that restores torch 0.4's ndarray coercion and records its per-row |TD| and
+  loss (``tests/golden/td_reference.npz``), so this part is PINNED too, with that one
+  documented shim; it is also cross-checked against a torch fp64 evaluation.
 * The reference ships no tests, so there are no upstream golden vectors.
 """
 

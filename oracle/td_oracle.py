@@ -1,10 +1,12 @@
 """CPU oracle: learner loss / TD / priority arithmetic (TEST INFRASTRUCTURE).
 
-Restates /root/reference/learner.py:43-52.  PARITY UNPINNED by the reference:
-learner.py:44 raises TypeError under this container's torch 2.11 / numpy 2.3
-(SURVEY Q14), so the reference function cannot be executed to produce vectors;
-this file is checked against an independent torch fp64 evaluation instead
-(tests/test_oracle_cpu.py).
+Restates /root/reference/learner.py:43-52.  Pinned by tests/golden/td_reference.npz:
+learner.py:44 raises TypeError under this container's torch 2.11 / numpy 2.3 as
+written, so tests/golden/make_golden.py executes the unmodified
+Learner.compute_loss_and_priorities under an operator shim (ndarray operands of
+Tensor.__rmul__/__radd__ coerced with torch.from_numpy, as torch 0.4 did) and
+records its outputs; this file is also checked against an independent torch fp64
+evaluation (tests/test_oracle_cpu.py).
 
     a*      = argmax_a Q_online(S_tpn)[b, a]                learner.py:45
     G_b     = R_b + Gamma_b * Q_target(S_tpn)[b, a*]        learner.py:44-45

@@ -122,7 +122,70 @@ def choice_law():
     np.savez_compressed(os.path.join(HERE, "choice_law.npz"), priorities=pri, alpha=alpha, u=u, picks=picks)
 
 
+def td_cases():
+    """Learner.compute_loss_and_priorities (learner.py:29-52) executed for real.
+
+    learner.py:44 multiplies a numpy array by a torch Tensor, which torch 0.4 (the reference's pin)
+    coerced and torch 2.x refuses.  The only thing changed to run it is an operator
+    shim that restores that coercion (ndarray operand -> torch.from_numpy) for Tensor.__rmul__ /
+    __radd__; learner.py itself is imported unmodified.  The three Q tensors the function computes
+    are captured with forward hooks; the returned dict gives every key the LAST row's |TD| (Q12), so
+    the batch is rotated B times to read every row's |TD| (the duelling head's batch-wide advantage
+    sum, Q19, is invariant under row permutation).
+    """
+    import torch
+    import learner as ref_learner
+
+    def coerce(fn):
+        def wrapped(self, other):
+            if isinstance(other, np.ndarray):
+                other = torch.from_numpy(other)
+            return fn(self, other)
+        return wrapped
+    saved = torch.Tensor.__rmul__, torch.Tensor.__radd__
+    torch.Tensor.__rmul__, torch.Tensor.__radd__ = coerce(saved[0]), coerce(saved[1])
+    out = {}
+    try:
+        torch.manual_seed(1234)
+        rng = np.random.RandomState(5)
+        NT = ref_learner.N_Step_Transition
+        L = ref_learner.Learner({"state_shape": [1, 84, 84], "action_dim": 4},
+                                {"load_saved_state": False, "q_target_sync_freq": 2500}, {}, None)
+        for p_, q_ in zip(L.Q_double.parameters(), L.Q.parameters()):       # a target net that differs from the online net
+            p_.data.copy_(q_.data + 0.01 * torch.randn_like(q_))
+        captured = []
+        hooks = [m.register_forward_hook(lambda mod, inp, outp, tag=tag: captured.append((tag, outp[2].detach().numpy().copy())))
+                 for tag, m in (("online", L.Q), ("target", L.Q_double))]
+        for case, B in enumerate((8, 5)):
+            recs = [NT(rng.rand(1, 84, 84) * 4, int(rng.randint(4)), float(rng.randn()),
+                       float(0.99 ** 3 if rng.rand() > 0.25 else 0.0), None, rng.rand(1, 84, 84) * 4, None, "k%d" % i)
+                    for i in range(B)]
+            abs_td = np.zeros(B)
+            for rot in range(B):
+                batch = recs[rot + 1:] + recs[:rot + 1]                      # row `rot` is last
+                del captured[:]
+                loss, prios = L.compute_loss_and_priorities(batch)
+                assert len(set(float(v) for v in prios.values())) == 1       # Q12: one value for every key
+                abs_td[rot] = float(list(prios.values())[0])
+                if rot == B - 1:                                             # batch in original order
+                    tags = [t for t, _ in captured]
+                    assert tags == ["target", "online", "online"], tags     # Q_double(S_tpn), Q(S_tpn), Q(S_t)
+                    out["c%d_q_tg_tpn" % case], out["c%d_q_on_tpn" % case], out["c%d_q_on_t" % case] = (c for _, c in captured)
+                    out["c%d_loss_mean" % case] = np.float64(loss.item())
+            out["c%d_A" % case] = np.array([r.A_t for r in recs], np.int32)
+            out["c%d_R" % case] = np.array([r.R_ttpB for r in recs], np.float64)
+            out["c%d_Gamma" % case] = np.array([r.Gamma_ttpB for r in recs], np.float64)
+            out["c%d_abs_td" % case] = abs_td
+        for h_ in hooks:
+            h_.remove()
+    finally:
+        torch.Tensor.__rmul__, torch.Tensor.__radd__ = saved
+    out["cases"] = np.int32(2)
+    np.savez_compressed(os.path.join(HERE, "td_reference.npz"), **out)
+
+
 def main():
+    td_cases()
     with open(os.path.join(HERE, "nstep_literal.json"), "w") as f:
         json.dump(nstep_cases(), f, indent=1)
     with open(os.path.join(HERE, "initial_priority.json"), "w") as f:

@@ -409,6 +409,19 @@ def test_td_forward_backward(apex, B, kind, nA):
     assert again.item() == mean.item()
 
 
+def test_td_kernel_matches_reference_learner_function(apex, golden_dir):
+    """K5 against the numbers the reference's Learner.compute_loss_and_priorities produced
+    (tests/golden/td_reference.npz, generated by executing learner.py:29-52)."""
+    z = np.load(os.path.join(golden_dir, "td_reference.npz"))
+    for c in range(int(z["cases"])):
+        q = [dev(z["c%d_%s" % (c, k)].astype(np.float32)) for k in ("q_on_t", "q_on_tpn", "q_tg_tpn")]
+        delta, prio, loss, mean = apex.ops.td_forward(q[0], q[1], q[2], dev(z["c%d_A" % c]), dev(z["c%d_R" % c].astype(np.float32)),
+                                                      dev(z["c%d_Gamma" % c].astype(np.float32)), 0.6)
+        np.testing.assert_allclose(delta.abs().cpu().numpy(), z["c%d_abs_td" % c], rtol=RTOL, atol=1e-6)
+        np.testing.assert_allclose(mean.item(), z["c%d_loss_mean" % c], rtol=RTOL)
+        np.testing.assert_allclose(prio.cpu().numpy(), z["c%d_abs_td" % c] ** 0.6, rtol=1e-4, atol=1e-6)
+
+
 def test_importance_weights_and_weighted_loss(apex):
     rng = np.random.default_rng(61)
     N, B, nA, beta = 20000, 512, 4, 0.4

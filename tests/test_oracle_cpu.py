@@ -195,6 +195,18 @@ def test_td_oracle_vs_torch_fp64():
         np.testing.assert_allclose(to.td_backward(o["delta"], act, A, loss_kind=kind), tq1.grad.numpy(), rtol=1e-5, atol=1e-8)
 
 
+def test_td_oracle_matches_reference_learner_function(golden_dir):
+    """td_reference.npz: outputs of the reference's own Learner.compute_loss_and_priorities
+    (learner.py:29-52), run by make_golden.py under an operator shim that restores torch-0.4's
+    ndarray coercion.  Per-row |TD| read from the returned dict by rotating the batch."""
+    z = np.load(os.path.join(golden_dir, "td_reference.npz"))
+    for c in range(int(z["cases"])):
+        o = to.td_forward(z["c%d_q_on_t" % c], z["c%d_q_on_tpn" % c], z["c%d_q_tg_tpn" % c], z["c%d_A" % c],
+                          z["c%d_R" % c], z["c%d_Gamma" % c], alpha=0.6)
+        np.testing.assert_allclose(o["abs_td"], z["c%d_abs_td" % c], rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(o["loss_mean"], z["c%d_loss_mean" % c], rtol=1e-5)
+
+
 def test_shard_split_equals_single_tree():
     rng = np.random.default_rng(5)
     shards = [rng.integers(0, 1 << 28, 1000).astype(np.uint64) for _ in range(4)]
