@@ -105,6 +105,16 @@ def replay_cases():
     u = np.random.random_sample(64)
     out["literal_sample"] = dict(n=37, picked=picked, u=u.tolist(),
                                  probs=[float(v) for v in mem.sample_probabilities.values()])
+    # equal priorities: literal (uniform, Q1) and intended (proportional) laws coincide, so the reference's
+    # own add + sample can be compared end to end with the drop-in class on the same seed
+    mem = ref_replay.ReplayMemory(100, {"priority_exponent": 0.6})
+    recs = [NT(i, i % 4, float(i) / 7, 0.97, None, i + 1, None, "e%d" % i) for i in range(50)]
+    for c in range(0, 50, 5):
+        mem.add({r.key: np.float64(2.5) for r in recs[c:c + 5]}, recs[c:c + 5])
+    np.random.seed(2024)
+    got = mem.sample(40)
+    out["equal_priority_sample"] = dict(n=50, seed=2024, keys=[r.key for r in got], A=[r.A_t for r in got],
+                                        R=[r.R_ttpB for r in got], S_t=[r.S_t for r in got], S_tpn=[r.S_tpn for r in got])
     return out
 
 

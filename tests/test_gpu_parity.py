@@ -369,6 +369,26 @@ def test_compat_api_matches_reference_semantics(apex, golden_dir):
     assert mem.size() == K
 
 
+def test_compat_add_sample_equals_reference_on_equal_priorities(apex, golden_dir):
+    """End to end against the reference's own ReplayMemory.add + sample (replay_literal.json,
+    'equal_priority_sample'): with equal priorities its literal (uniform) law and the intended one
+    coincide, so the same seed must return the same records in the same order."""
+    with open(os.path.join(golden_dir, "replay_literal.json")) as f:
+        g = json.load(f)["equal_priority_sample"]
+    NT = apex.N_Step_Transition
+    mem = apex.ReplayMemory(100, {"priority_exponent": 0.6})
+    frame = lambda v: np.full((1, 84, 84), v % 256, np.uint8)           # the state id, as an image
+    recs = [NT(frame(i), i % 4, float(i) / 7, 0.97, None, frame(i + 1), None, "e%d" % i) for i in range(g["n"])]
+    for c in range(0, g["n"], 5):
+        mem.add({r.key: np.float64(2.5) for r in recs[c:c + 5]}, recs[c:c + 5])
+    np.random.seed(g["seed"])
+    got = mem.sample(len(g["keys"]))
+    assert [r.key for r in got] == g["keys"]
+    assert [r.A_t for r in got] == g["A"]
+    np.testing.assert_allclose([r.R_ttpB for r in got], g["R"], rtol=1e-6)
+    assert [int(r.S_t[0, 0, 0]) for r in got] == g["S_t"] and [int(r.S_tpn[0, 0, 0]) for r in got] == g["S_tpn"]
+
+
 def test_checkpoint_round_trip(apex):
     rng = np.random.default_rng(12)
     mem = make_mem(apex, 256, C=2, F=32, layout="stream", lanes=2, n=2)
