@@ -329,6 +329,63 @@ def test_stream_insert_and_gather_byte_exact(apex, variant, C_, F):
         apex._C.call("apexb200_set_gather_variant", 0)
 
 
+@pytest.mark.parametrize("seed", range(12))
+def test_random_configurations(apex, seed):
+    """Ragged shapes: random frames-per-state (odd, 1, the fused kernels' limit 8 and beyond it), frame
+    sizes, lane counts, layouts and batch sizes; insert -> sample -> gather -> fused update against the oracle."""
+    rng = np.random.default_rng(1000 + seed)
+    C_ = int(rng.choice([1, 2, 3, 4, 5, 8, 9]))
+    F = int(rng.choice([16, 48, 112, 7056])) if C_ < 8 else int(rng.choice([16, 48]))
+    stream = bool(rng.integers(2))
+    lanes = int(rng.choice([1, 3, 8]))
+    n = int(rng.integers(1, 5))
+    nA = int(rng.choice([0, 2, 18]))
+    lane_cap = int(rng.integers(40, 90))
+    N = lanes * lane_cap
+    fpr, W = (1, C_ - 1 + n) if stream else (2 * C_, 0)
+    mem = make_mem(apex, N, C=C_, F=F, layout="stream" if stream else "materialised", lanes=lanes, n=n, nA=nA)
+    ring = ro.RingOracle(N, C_, F, lanes=lanes, fpr=fpr, lookback=W, alpha=0.6, num_actions=nA)
+    for it in range(int(rng.integers(3, 9))):
+        lane = int(rng.integers(lanes))
+        m = int(rng.integers(1, lane_cap - W))
+        frames = rng.integers(0, 256, (m * fpr, F), dtype=np.uint8)
+        if stream:
+            rel = apex.stream_offsets(C_, rng.integers(1, n + 1, m), rng.integers(0, 2 * W + 2, m))
+        else:
+            rel = np.tile(np.arange(-(2 * C_ - 1), 1, dtype=np.int32), (m, 1))
+        A = rng.integers(0, max(nA, 1), m).astype(np.int32)
+        R, G = rng.standard_normal(m).astype(np.float32), rng.random(m).astype(np.float32)
+        prio = (np.abs(rng.standard_normal(m)) * (rng.random(m) > 0.2)).astype(np.float32)      # some zero priorities
+        q = (rng.standard_normal((m, nA)).astype(np.float32), rng.standard_normal((m, nA)).astype(np.float32)) if nA else (None, None)
+        s1 = mem.insert(lane, frames, rel, A, R, G, prio=prio, q_t=q[0], q_tpn=q[1])
+        s2 = ring.insert(lane, frames, rel, A, R, G, prio=prio, q_t=q[0], q_tpn=q[1])
+        np.testing.assert_array_equal(s1, s2)
+    leaves = u64(mem.buffer(apex._C.BUF_LEAVES))
+    ring.leaves[:] = leaves
+    if leaves.sum() == 0:
+        return
+    for B in (1, int(rng.integers(2, 700))):
+        u = rng.random(B)
+        b = mem.sample_tensors(B, u=dev(u), with_q=bool(nA))
+        want = ring.sample(u)
+        np.testing.assert_array_equal(b.idx.cpu().numpy(), want)
+        g = ring.gather(want)
+        np.testing.assert_array_equal(b.S_t.cpu().numpy(), g["S_t"])
+        np.testing.assert_array_equal(b.S_tpn.cpu().numpy(), g["S_tpn"])
+        np.testing.assert_array_equal(b.A.cpu().numpy(), g["A"])
+        np.testing.assert_array_equal(b.Gamma.cpu().numpy(), g["G"])
+        if nA:
+            np.testing.assert_array_equal(mem._last_q[1].cpu().numpy(), g["q_tpn"])
+        nq = max(nA, 3)
+        qs = [rng.standard_normal((B, nq)).astype(np.float32) for _ in range(3)]
+        acts = dev((g["A"] % nq).astype(np.int32))
+        _, prio_d, _, _ = mem.td_update(b.idx, dev(qs[0]), dev(qs[1]), dev(qs[2]), acts, b.R, b.Gamma)
+        ring.set_leaves(want, ro.priority_to_leaf(prio_d.cpu().numpy()))
+        for gl, w in zip(read_levels(apex, mem), ro.build_levels(ring.leaves)):
+            np.testing.assert_array_equal(gl, w)
+    mem.check_status()
+
+
 def test_compat_api_matches_reference_semantics(apex, golden_dir):
     """add / sample / set_priorities / size with reference-shaped records (replay.py:32-83)."""
     z = np.load(os.path.join(golden_dir, "choice_law.npz"))
