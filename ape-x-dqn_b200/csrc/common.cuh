@@ -139,6 +139,32 @@ __device__ __forceinline__ void bump_epoch(int32_t *ctrl) {        // one thread
     if (blockIdx.x == 0 && threadIdx.x == 0) *(volatile unsigned long long *)(ctrl + 4) += 1ull;
 }
 
+// The same for a full warp whose leaves are adjacent in index order (sorted batch rows, or the
+// consecutive slots of an insert): rows that share an ancestor are neighbours, so the deltas are
+// summed per ancestor with a segmented shuffle scan and one atomic per distinct ancestor is issued
+// instead of one per row (hundreds of rows hit 2 nodes at the top level of a 2M-record tree).
+// Must be called by all 32 lanes; lanes without an update pass i < 0 (they never merge) or d = 0.
+// Levels below `first_merged` get one atomic per row (batch rows rarely share a level-1 parent;
+// the consecutive slots of an insert always do: first_merged = 1 there).
+__device__ __forceinline__ void warp_propagate_adjacent(const TreeView &tv, long long i, unsigned long long d,
+                                                        int first_merged = 2) {
+    const int lane = threadIdx.x & 31;
+    for (int l = 1; l < first_merged && l < tv.n_levels; ++l)
+        if (i >= 0 && d != 0ull) atomicAdd(tv.lvl[l] + (i >> (5 * l)), d);
+    for (int l = first_merged; l < tv.n_levels; ++l) {
+        const long long key = i >= 0 ? (i >> (5 * l)) : (long long)(-1 - lane);
+        unsigned long long sum = i >= 0 ? d : 0ull;
+        #pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const long long ks = __shfl_up_sync(0xffffffffu, key, o);
+            const unsigned long long vs = __shfl_up_sync(0xffffffffu, sum, o);
+            if (lane >= o && ks == key) sum += vs;
+        }
+        const long long kn = __shfl_down_sync(0xffffffffu, key, 1);
+        if ((lane == 31 || kn != key) && sum != 0ull && key >= 0) atomicAdd(tv.lvl[l] + key, sum);
+    }
+}
+
 // ---- exchange of shard totals over peer memory (multi-GPU) ---------------------------
 // One 8-byte word per (slot, rank): total << 4 | round & 15.  Total and tag travel in the
 // same naturally aligned word, so no fence is needed between them (a shard total < 2^60).

@@ -25,19 +25,24 @@ int cuda_fail(cudaError_t e, const char *what) {
 }
 
 // ---------------------------------------------------------------------------
-// K6a: stream the new frames into their ring slots (16-byte vectors, coalesced;
-// source is contiguous, destination is contiguous up to the ring wrap).
+// K6a: stream the new frames into their ring slots (16-byte vectors, coalesced; source is
+// contiguous, destination is contiguous up to the ring wrap).  One CTA row (blockIdx.y, strided)
+// per record, two vectors per thread in flight: no index division, ~2 loads outstanding per thread
+// and tens of thousands of CTAs keep HBM busy in both directions.
 __global__ void __launch_bounds__(256)
-insert_frames_kernel(uint4 *__restrict__ ring_frames, const uint4 *__restrict__ src,
-                     long long total_vecs, int vecs_per_record, long long lane_base,
-                     long long head, long long lane_cap) {
-    long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < total_vecs; v += stride) {
-        long long j = v / vecs_per_record;
-        int within = (int)(v - j * vecs_per_record);
-        long long slot = lane_base + (head + j) % lane_cap;
-        uint4 x = __ldcs(src + v);                               // staging data is read once
-        ring_frames[slot * vecs_per_record + within] = x;
+insert_frames_kernel(uint4 *__restrict__ ring_frames, const uint4 *__restrict__ src, int count,
+                     int vecs_per_record, long long lane_base, long long head, long long lane_cap) {
+    const int v0 = blockIdx.x * 512 + threadIdx.x;
+    const int v1 = v0 + 256;
+    for (int j = blockIdx.y; j < count; j += gridDim.y) {
+        const long long slot = lane_base + (head + j) % lane_cap;
+        const uint4 *s = src + (long long)j * vecs_per_record;
+        uint4 *d = ring_frames + slot * vecs_per_record;
+        uint4 a, b;
+        if (v0 < vecs_per_record) a = __ldcs(s + v0);                // staging data is read once
+        if (v1 < vecs_per_record) b = __ldcs(s + v1);
+        if (v0 < vecs_per_record) d[v0] = a;
+        if (v1 < vecs_per_record) d[v1] = b;
     }
 }
 
@@ -52,11 +57,11 @@ insert_meta_kernel(RingView rv, TreeView tv, int lane, long long head, int count
                    const float *__restrict__ q_tpn, int32_t *status) {
     bump_epoch(status);
     int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= count + rv.lookback) return;
-    long long p = (head + j) % rv.lane_cap;
+    const bool active = j < count + rv.lookback;
+    long long p = (head + (active ? j : 0)) % rv.lane_cap;
     long long s = (long long)lane * rv.lane_cap + p;
     unsigned long long new_leaf = 0ull;
-    if (j < count) {
+    if (active && j < count) {
         const int twoC = 2 * rv.C;
         const long long lane_frames = rv.lane_cap * rv.fpr;
         const long long lane_frame_base = (long long)lane * lane_frames;
@@ -90,10 +95,14 @@ insert_meta_kernel(RingView rv, TreeView tv, int lane, long long head, int count
         }
         new_leaf = leaf_from_prio(prio_pow(p0, rv.alpha, 0.0f));
     }
-    unsigned long long old = tv.lvl[0][s];
-    tv.lvl[0][s] = new_leaf;
-    unsigned long long d = new_leaf - old;
-    if (d != 0ull) propagate_delta(tv, s, d);
+    unsigned long long d = 0ull;
+    if (active) {
+        unsigned long long old = tv.lvl[0][s];
+        tv.lvl[0][s] = new_leaf;
+        d = new_leaf - old;
+    }
+    // consecutive slots: neighbours share ancestors -> one atomic per distinct ancestor per warp
+    warp_propagate_adjacent(tv, active ? s : -1, d, 1);
 }
 
 }  // namespace apexb200
@@ -269,12 +278,10 @@ int apexb200_replay_insert(apexb200_replay_t h, int32_t lane, int32_t count, con
     APEX_REQUIRE(((uintptr_t)frames & 15) == 0, APEXB200_EINVAL, "replay_insert: frames must be 16-byte aligned");
     cudaStream_t st = (cudaStream_t)stream;
     const int vpr = rv.fpr * rv.F / 16;
-    const long long total_vecs = (long long)count * vpr;
-    long long blocks = (total_vecs + 255) / 256;
-    const long long max_blocks = (long long)kNumSMs * 16;
-    if (blocks > max_blocks) blocks = max_blocks;
-    insert_frames_kernel<<<(unsigned)blocks, 256, 0, st>>>((uint4 *)rv.frames, (const uint4 *)frames, total_vecs,
-                                                           vpr, (long long)lane * rv.lane_cap, head, rv.lane_cap);
+    const int max_rows = kNumSMs * 8;                          // 8 resident CTAs per SM, each loops over its records
+    const dim3 grid((unsigned)((vpr + 511) / 512), (unsigned)(count < max_rows ? count : max_rows));
+    insert_frames_kernel<<<grid, 256, 0, st>>>((uint4 *)rv.frames, (const uint4 *)frames, count, vpr,
+                                               (long long)lane * rv.lane_cap, head, rv.lane_cap);
     int rc = launch_check("insert_frames_kernel");
     if (rc) return rc;
     const int nmeta = count + rv.lookback;

@@ -139,24 +139,8 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
     if (!sorted) {
         if (d != 0ull) propagate_delta(tv, i, d);
     } else if (idx != nullptr) {
-        // Sorted record indices (stratified draws): rows that share an ancestor are adjacent, so the
-        // deltas of a warp are summed per ancestor with a segmented shuffle scan and one atomic per
-        // distinct ancestor is issued (512 rows hit 2 nodes at the top level of a 2M-record tree:
-        // per-row atomics there serialise for ~1 us).  Level 1 ancestors are almost all distinct.
-        const int lane = threadIdx.x & 31;
-        if (d != 0ull && tv.n_levels > 1) atomicAdd(tv.lvl[1] + (i >> 5), d);
-        for (int l = 2; l < tv.n_levels; ++l) {
-            const long long key = i >= 0 ? (i >> (5 * l)) : (long long)(-1 - lane);
-            unsigned long long sum = d;
-            #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const long long ks = __shfl_up_sync(0xffffffffu, key, o);
-                const unsigned long long vs = __shfl_up_sync(0xffffffffu, sum, o);
-                if (lane >= o && ks == key) sum += vs;
-            }
-            const long long kn = __shfl_down_sync(0xffffffffu, key, 1);
-            if ((lane == 31 || kn != key) && sum != 0ull && key >= 0) atomicAdd(tv.lvl[l] + key, sum);
-        }
+        // Sorted record indices (stratified draws): one atomic per distinct ancestor per warp
+        warp_propagate_adjacent(tv, i, d);
     }
     if (!push) return;
     // Fused collective (multi-GPU): publish this shard's new total to every peer from the
@@ -257,19 +241,7 @@ td_cluster_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32
     if (!sorted) {
         if (d != 0ull) propagate_delta(tv, i, d);
     } else if (idx != nullptr) {
-        if (d != 0ull && tv.n_levels > 1) atomicAdd(tv.lvl[1] + (i >> 5), d);
-        for (int lv = 2; lv < tv.n_levels; ++lv) {              // one atomic per distinct ancestor per warp
-            const long long key = i >= 0 ? (i >> (5 * lv)) : (long long)(-1 - lane);
-            unsigned long long sum = d;
-            #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const long long ks = __shfl_up_sync(0xffffffffu, key, o);
-                const unsigned long long vs = __shfl_up_sync(0xffffffffu, sum, o);
-                if (lane >= o && ks == key) sum += vs;
-            }
-            const long long kn = __shfl_down_sync(0xffffffffu, key, 1);
-            if ((lane == 31 || kn != key) && sum != 0ull && key >= 0) atomicAdd(tv.lvl[lv] + key, sum);
-        }
+        warp_propagate_adjacent(tv, i, d);                      // one atomic per distinct ancestor per warp
     }
     if (push) {                                                 // this CTA's share of the total delta -> CTA 0
         __shared__ unsigned long long dpart[kTdClusterRows / 32];
