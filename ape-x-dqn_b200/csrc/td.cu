@@ -128,13 +128,41 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
         winner = false;
         if (i >= 0 && __ldcg(stamp + i) == (uint32_t)b + 1u) { winner = true; stamp[i] = 0u; }
     }
-    float s = block_sum_fixed(l, warp_part);
-    if (threadIdx.x == 0) *a.loss_mean = s / mean_div(a);
     unsigned long long d = 0ull;
     if (winner) {
         unsigned long long nl = leaf_from_prio(a.prio[b]);
         tv.lvl[0][i] = nl;
         d = nl - old;
+    }
+    if (push) {
+        // Fused collective (multi-GPU): publish this shard's new total to every peer from the
+        // kernel that produced it — the next step's sharded sample on each rank waits for these
+        // words instead of an all-gather.  new total = total before + sum of this batch's leaf
+        // deltas (exact in u64 arithmetic; this CTA is the only writer of the tree while it runs).
+        // It is sent BEFORE the ancestor updates and the loss reduction below, so that the NVLink
+        // flight overlaps them; peers only route draws with it, this shard's own tree is complete
+        // when the kernel ends.
+        unsigned long long ds = d;
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ds += __shfl_xor_sync(0xffffffffu, ds, o);
+        if ((threadIdx.x & 31) == 0) delta_part[threadIdx.x >> 5] = ds;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            const int lane = threadIdx.x;
+            unsigned long long v = total_before;
+            #pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            const int nw = (blockDim.x + 31) >> 5;
+            for (int k = 0; k < nw; ++k) v += delta_part[k];
+            const unsigned long long cur = cur_round;
+            if (lane < pv.world) {
+                if (cur > 0ull && (peer_word & 15ull) != (cur & 15ull))
+                    peer_wait_round(pv, cur, lane, status);             // not there at kernel start: wait now
+                peer_push_round(pv, cur + 1ull, lane, v);
+            }
+            __syncwarp();
+            if (lane == 0) *(volatile unsigned long long *)(status + 6) = cur + 1ull;
+        }
     }
     if (!sorted) {
         if (d != 0ull) propagate_delta(tv, i, d);
@@ -142,35 +170,8 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
         // Sorted record indices (stratified draws): one atomic per distinct ancestor per warp
         warp_propagate_adjacent(tv, i, d);
     }
-    if (!push) return;
-    // Fused collective (multi-GPU): publish this shard's new total to every peer from the
-    // kernel that produced it — the next step's sharded sample on each rank waits for these
-    // words instead of an all-gather.  new total = total before + sum of this batch's leaf
-    // deltas (exact in u64 arithmetic; this CTA is the only writer of the tree while it runs),
-    // so the push does not wait for the ancestor updates above to land.
-    {
-        unsigned long long ds = d;
-        #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) ds += __shfl_xor_sync(0xffffffffu, ds, o);
-        if ((threadIdx.x & 31) == 0) delta_part[threadIdx.x >> 5] = ds;
-    }
-    __syncthreads();
-    if (threadIdx.x < 32) {
-        const int lane = threadIdx.x;
-        unsigned long long v = total_before;
-        #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        const int nw = (blockDim.x + 31) >> 5;
-        for (int k = 0; k < nw; ++k) v += delta_part[k];
-        const unsigned long long cur = cur_round;
-        if (lane < pv.world) {
-            if (cur > 0ull && (peer_word & 15ull) != (cur & 15ull))
-                peer_wait_round(pv, cur, lane, status);                 // not there at kernel start: wait now
-            peer_push_round(pv, cur + 1ull, lane, v);
-        }
-        __syncwarp();
-        if (lane == 0) *(volatile unsigned long long *)(status + 6) = cur + 1ull;
-    }
+    float s = block_sum_fixed(l, warp_part);
+    if (threadIdx.x == 0) *a.loss_mean = s / mean_div(a);
 }
 
 // ---- B <= 1024 as one thread-block cluster: ceil(B/128) CTAs of 128 rows on as many SMs
