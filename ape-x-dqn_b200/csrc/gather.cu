@@ -469,7 +469,10 @@ int apexb200_sample_gather(apexb200_replay_t h, const double *u, uint64_t seed, 
     const int units = 2 * count;
     int wpc = (int)(kStageBudget / per_unit);                              // units (warps) per CTA that fit
     if (wpc > 16) wpc = 16;
-    const int spread = (units + kNumSMs - 1) / kNumSMs;                    // one wave: spread evenly over the SMs
+    // one wave: spread evenly over the SMs, but leave one SM free — the next kernel of the step
+    // (single-CTA K5+K2, launched early by PDL) then has somewhere to wait without queueing behind
+    // a 200 KB CTA (measured: 148 resident CTAs cost the step ~1.3 us)
+    const int spread = (units + kNumSMs - 2) / (kNumSMs - 1);
     if (spread < wpc) wpc = spread;
     // A batch that needs several waves runs faster with thin CTAs (several CTAs per SM: one CTA's
     // tree descent overlaps another's frame movement; 78 vs 88 us at B=4096), a single-wave batch
@@ -500,7 +503,7 @@ int apexb200_sample_gather_sharded(apexb200_replay_t h, uint64_t seed, int32_t g
     const int units = 2 * max_rows;
     int wpc = (int)(kStageBudget / per_unit);
     if (wpc > 16) wpc = 16;
-    const int spread = (units + kNumSMs - 1) / kNumSMs;
+    const int spread = (units + kNumSMs - 2) / (kNumSMs - 1);             // leave one SM free, as in sample_gather
     if (spread < wpc) wpc = spread;
     const int ctas = (units + wpc - 1) / wpc;
     const size_t smem = (size_t)wpc * per_unit;
