@@ -177,8 +177,8 @@ gather_vec_kernel(RingView rv, GatherArgs ga, int32_t *status) {
 
 // Shared-memory budget for frame staging: one fat CTA per SM instead of many thin ones.
 // With ~7 KB frames a thin (1-2 frame) CTA spends longer being launched than moving
-// data; 32 frames per CTA (220.5 KB of the 227 KB an SM offers) puts a whole B=512, C=4
-// batch (4096 frames) in flight at once from 128 CTAs, one launch wave, one CTA per SM.
+// data; up to 32 frames per CTA (220.5 KB of the 227 KB an SM offers), spread so that a
+// whole B=512, C=4 batch (4096 frames) is in flight at once in one launch wave.
 constexpr size_t kStageBudget = 226 * 1024;
 constexpr size_t kBarBytes = 32 * kMaxChunks * 8;           // mbarriers sit in front of the staging area
 

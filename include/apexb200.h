@@ -184,8 +184,10 @@ int apexb200_gather(apexb200_replay_t h, const int32_t *idx, const int32_t *fsel
 int apexb200_set_gather_variant(int32_t variant);
 /* K3 + K4 in one launch: ReplayMemory.sample (replay.py:44-57) as a whole.  u [count]
  * as in apexb200_sample, or NULL for the in-kernel stratified draws of
- * apexb200_sample_stratified (seed, u_out).  One CTA per draw: the warp descends the
- * tree, then moves the record's 2C frames with the TMA engine.  Outputs as in
+ * apexb200_sample_stratified (seed, u_out).  One warp per half draw (S_t or S_tpn): the
+ * warp descends the tree, then moves the C frames of its half with the TMA engine.  Needs
+ * frames_per_state <= 8 and C frames fitting in shared memory (otherwise the two kernels
+ * run back to back).  Outputs as in
  * apexb200_sample + apexb200_gather (fsel_out, leaf_out, total_out, u_out, A, R, Gamma,
  * q_t, q_tpn nullable). */
 int apexb200_sample_gather(apexb200_replay_t h, const double *u, uint64_t seed, int32_t count,
