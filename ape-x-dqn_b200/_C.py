@@ -35,6 +35,10 @@ class ReplayConfig(C.Structure):
                 ("num_actions", C.c_int32), ("alpha", C.c_float), ("device", C.c_int32)]
 
 
+class ParamSpan(C.Structure):
+    _fields_ = [("tensor", C.c_uint64), ("flat_offset", C.c_uint64), ("bytes", C.c_uint64)]
+
+
 _P, _I32, _I64, _F = C.c_void_p, C.c_int32, C.c_int64, C.c_float
 
 # name -> argument types; every function returns int unless listed in _RESTYPE
@@ -79,6 +83,12 @@ SIGNATURES = {
     "apexb200_shard_exchange": [_P, _P, _P],
     "apexb200_peer_push_on_update": [_P, _I32],
     "apexb200_sample_gather_sharded": [_P, C.c_uint64, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "apexb200_params_create": [_I32, _P, _I32, C.c_uint64, C.POINTER(_P)],
+    "apexb200_params_destroy": [_P],
+    "apexb200_params_flat": [_P, C.POINTER(_P), C.POINTER(C.c_uint64)],
+    "apexb200_params_publish": [_P, _P, _P, _I64, _P],
+    "apexb200_params_load": [_P, _P, _I32, _P],
+    "apexb200_actor_policy": [_P, _P, _P, _P, _P, C.c_uint64, C.c_uint64, _I32, _I32, _P, _P, _P, _P],
     "apexb200_replay_buffer": [_P, _I32, C.POINTER(_P), C.POINTER(_I64)],
     "apexb200_replay_get_heads": [_P, C.POINTER(_I64)],
     "apexb200_replay_set_heads": [_P, C.POINTER(_I64)],

@@ -13,6 +13,10 @@ from . import ops                                             # noqa: F401
 from .sharded import ShardedSampler                           # noqa: F401
 from .pipeline import HostStepPipeline                        # noqa: F401
 from .ingest import VectorActorIngest, ActorStagingRing, RingIngest   # noqa: F401
+from .weights import (WeightPublisher, WeightSubscriber, DeviceWeightSubscriber, BatchedActorPolicy,   # noqa: F401
+                      actor_policy, actor_epsilons, param_layout)
 
 __all__ = ["ReplayMemory", "Learner", "Actor", "ExperienceBuffer", "N_Step_Transition", "Transition", "Batch",
-           "KeyIndex", "stream_offsets", "td_loss", "ops", "ShardedSampler", "HostStepPipeline", "VectorActorIngest", "ActorStagingRing", "RingIngest"]
+           "KeyIndex", "stream_offsets", "td_loss", "ops", "ShardedSampler", "HostStepPipeline", "VectorActorIngest", "ActorStagingRing", "RingIngest",
+           "WeightPublisher", "WeightSubscriber", "DeviceWeightSubscriber", "BatchedActorPolicy", "actor_policy",
+           "actor_epsilons", "param_layout"]

@@ -187,6 +187,11 @@ class Actor(mp.Process):
             from .learner import make_q_network
             self.Q = (self._q_factory or make_q_network)(self.state_shape, self.action_dim)
             self.Q.load_state_dict(self.shared_state["Q_state_dict"])                   # actor.py:106
+        self._weights = None
+        if self.params.get("weight_board"):               # K9 board published by the learner (weights.py)
+            from .weights import WeightSubscriber
+            self._weights = WeightSubscriber(self.Q, self.params["weight_board"])
+            self._weights.poll()
         if self.env is None:
             if self._env_factory is not None:
                 self.env = self._env_factory(self.env_name)
@@ -213,5 +218,8 @@ class Actor(mp.Process):
             if self.local_experience_buffer.size >= batch:
                 xp = self.local_experience_buffer.get(batch)
                 self.global_replay_queue.put([self.compute_priorities(xp), xp])          # actor.py:181-187
-            if t % self.params["Q_network_sync_freq"] == 0:
-                self.Q.load_state_dict(self.shared_state["Q_state_dict"])               # actor.py:189-191
+            if t % self.params["Q_network_sync_freq"] == 0:                             # actor.py:189-191
+                if self._weights is not None:
+                    self._weights.poll()
+                else:
+                    self.Q.load_state_dict(self.shared_state["Q_state_dict"])

@@ -208,6 +208,12 @@ class Learner(object):
             time.sleep(1)
         fast = self._fast()
         publish = int(self.params.get("weight_publish_freq", 500 if fast else 1))
+        board = None
+        if self.params.get("weight_board"):                 # K9: versioned shared-memory board instead of a pickle
+            from .weights import WeightPublisher
+            self._to_device()
+            board = WeightPublisher(self.Q, name=self.params["weight_board"], create=True)
+            board.publish()
         for t in range(T):
             if fast:
                 self.step_fast()
@@ -217,6 +223,12 @@ class Learner(object):
                 self.update_Q(loss)
                 self.replay_memory.set_priorities(priorities)
             if t % publish == 0:
-                self.shared_state["Q_state_dict"] = {k: v.detach().cpu() for k, v in self.Q.state_dict().items()}
+                if board is not None:
+                    board.publish()
+                else:
+                    self.shared_state["Q_state_dict"] = {k: v.detach().cpu() for k, v in self.Q.state_dict().items()}
             if t % self.params["remove_old_xp_freq"] == 0:
                 self.replay_memory.remove_to_fit()
+        if board is not None:
+            board.wait(board._issued)
+            board.close(unlink=bool(self.params.get("weight_board_unlink", False)))

@@ -16,10 +16,11 @@
  *     stream has run past the call;
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
  *     the per-step entry points (sample*, gather, td_*, tree_update*, shard_exchange,
- *     sample_gather_sharded, nstep, initial_priority, is_weights) only enqueue work:
- *     they never synchronise and never allocate.  Allocation or synchronisation happens
- *     only in replay_create/destroy, replay_status, peer_connect (maps peer memory) and
- *     in the first call of host_step (copy streams + staging);
+ *     sample_gather_sharded, nstep, initial_priority, is_weights, params_publish/load,
+ *     actor_policy) only enqueue work: they never synchronise and never allocate.
+ *     Allocation or synchronisation happens only in replay_create/destroy,
+ *     params_create/destroy, replay_status, peer_connect (maps peer memory) and in the
+ *     first call of host_step (copy streams + staging);
  *   - one replay handle is driven from one host thread at a time; calls on one
  *     stream are totally ordered, which is what gives add/sample/set_priorities
  *     their reference (sequential) semantics.
@@ -346,6 +347,50 @@ int apexb200_sample_gather_sharded(apexb200_replay_t h, uint64_t seed, int32_t g
                                    int32_t *idx_out, int32_t *fsel_out, int32_t *pos_out, double *u_out,
                                    int32_t *count_out, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R,
                                    float *Gamma, float *q_t, float *q_tpn, void *stream);
+
+/* ---- K9 learner -> actor weight publication ----------------
+ * Replaces shared_state["Q_state_dict"] = Q.state_dict() (learner.py:24, :74 — a 13.3 MB
+ * pickle through a Manager proxy on every step) and Q.load_state_dict(shared_state[...])
+ * (actor.py:106, :189-191).  A "params board" owns one flat device snapshot of a set of
+ * tensors (span i = `bytes` bytes at device address `tensor`, stored at `flat_offset`,
+ * a multiple of 256, inside the snapshot).  create/destroy allocate and synchronise;
+ * publish/load only enqueue. */
+typedef struct apexb200_param_span {
+    uint64_t tensor;        /* device address of the tensor's storage */
+    uint64_t flat_offset;   /* byte offset inside the flat snapshot, multiple of 256 */
+    uint64_t bytes;
+} apexb200_param_span;
+typedef struct apexb200_params *apexb200_params_t;
+int apexb200_params_create(int32_t device, const apexb200_param_span *spans_host, int32_t n_spans, uint64_t flat_bytes,
+                           apexb200_params_t *out);
+int apexb200_params_destroy(apexb200_params_t p);
+/* Device address / size of the snapshot (peers may read it over NVLink or broadcast it). */
+int apexb200_params_flat(apexb200_params_t p, void **flat_dev_host, uint64_t *bytes_host);
+/* Learner side (learner.py:74).  One kernel on `stream` packs the tensors into the snapshot.
+ * With slot_host (page-locked, flat_bytes long) and ctrl_host (int64 [>=2], host) the snapshot
+ * is then copied out on the board's own copy stream — the learner stream does not wait for
+ * PCIe — and when the copy has landed a host callback stores `version` into ctrl_host[0];
+ * ctrl_host[1] = version is stored at once ("begun").  Versions of one board increase by 1 and
+ * alternate between two slots, so a reader that copied slot v&1 after seeing ctrl[0] == v
+ * has a consistent copy iff ctrl[1] <= v + 1 afterwards.  slot_host == ctrl_host == NULL: pack only. */
+int apexb200_params_publish(apexb200_params_t p, void *slot_host, int64_t *ctrl_host, int64_t version, void *stream);
+/* Actor side with a GPU model (actor.py:189-191): copy flat_src (a host slot when src_is_host,
+ * else a device or peer snapshot; NULL = the board's own snapshot as it stands) into the
+ * snapshot and scatter it into the tensors, on `stream`. */
+int apexb200_params_load(apexb200_params_t p, const void *flat_src, int32_t src_is_host, void *stream);
+
+/* ---- K10 batched actor policy (actor.py:121-125, :160-163; duelling_network.py:27) ----
+ * For E environments at once: q[e,a] = value[e] + (adv[e,a] - (1/A) sum_a adv[e,a]) — the
+ * duelling combine with the batch-1 semantics every reference actor has (the model's own
+ * combine couples the rows of a batch) — then epsilon-greedy per environment:
+ * explore iff u_explore[e] < eps[e] (random.random() >= eps is the greedy branch), random
+ * action min(floor(u_action[e]*A), A-1), greedy action = first maximum (np.argmax; NaN counts
+ * as largest).  value == NULL: advantage_or_q already holds Q rows.  u_explore == u_action ==
+ * NULL: the uniforms are splitmix64(seed, step, e).  q_out [E, A] and explored [E] are nullable.
+ * Enqueue only. */
+int apexb200_actor_policy(const float *value, const float *advantage_or_q, const float *eps, const double *u_explore,
+                          const double *u_action, uint64_t seed, uint64_t step, int32_t E, int32_t A, float *q_out,
+                          int32_t *actions, uint8_t *explored, void *stream);
 
 /* ---- raw access for checkpoint / tests (learner.py:18-23 is load-only; the
  * replay itself is never persisted by the reference) ---------------------- */

@@ -20,7 +20,10 @@ Parity status ("pinned" vs "unpinned"), per function:
   shim that restores torch 0.4's ndarray coercion and records its per-row |TD| and
   loss (``tests/golden/td_reference.npz``), so this part is PINNED too, with that one
   documented shim; it is also cross-checked against a torch fp64 evaluation.
+* The batched actor policy (``policy_oracle``: duelling combine at batch 1, epsilon-greedy) is PINNED
+  against the reference model run at batch 1 and ``Actor.epsilon_greedy_Q`` run on its own ``random``
+  stream (``tests/golden/policy_reference.npz``).
 * The reference ships no tests, so there are no upstream golden vectors.
 """
 
-from . import replay_oracle, td_oracle, nstep_oracle  # noqa: F401
+from . import replay_oracle, td_oracle, nstep_oracle, policy_oracle  # noqa: F401

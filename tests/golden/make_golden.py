@@ -194,7 +194,47 @@ def td_cases():
     np.savez_compressed(os.path.join(HERE, "td_reference.npz"), **out)
 
 
+def policy_cases():
+    """The actor's policy executed for real: DuellingDQN at batch 1 (actor.py:160-161 ->
+    duelling_network.py:21-28) and Actor.epsilon_greedy_Q (actor.py:121-125) on the `random`
+    stream it consumes.  A second random.Random with the same seed replays that stream to record
+    the uniform behind every explore decision and the action random.choice returned."""
+    import random
+    import torch
+    from duelling_network import DuellingDQN
+    out = {}
+    for case, (A, E, eps, seed) in enumerate(((4, 24, 0.4, 9), (6, 17, 0.7, 31))):
+        torch.manual_seed(100 + case)
+        net = DuellingDQN((1, 84, 84), A)
+        obs = torch.rand(E, 1, 84, 84) * 255
+        with torch.no_grad():
+            rows = [net(obs[i:i + 1]) for i in range(E)]                 # batch 1, as every actor does
+        value = np.concatenate([r[0].numpy() for r in rows]).reshape(E)
+        adv = np.concatenate([r[1].numpy() for r in rows])
+        q = np.concatenate([r[2].numpy() for r in rows])
+        q_fwd = q.copy()
+        q[3, :] = q[3, 1]                                                # a row of ties: np.argmax -> first
+        stub = types.SimpleNamespace(epsilon=eps)
+        random.seed(seed)
+        acts = [int(ref_actor.Actor.epsilon_greedy_Q(stub, q[i])) for i in range(E)]
+        replay = random.Random(seed)
+        u_explore, u_action = np.zeros(E), np.full(E, 0.5)
+        for i in range(E):
+            u_explore[i] = replay.random()
+            if not (u_explore[i] >= eps):
+                picked = replay.choice(list(range(A)))
+                assert picked == acts[i]
+                u_action[i] = (picked + 0.5) / A
+        out.update({"c%d_value" % case: value, "c%d_adv" % case: adv, "c%d_q_forward" % case: q_fwd,
+                    "c%d_q_policy" % case: q, "c%d_eps" % case: np.float64(eps),
+                    "c%d_u_explore" % case: u_explore, "c%d_u_action" % case: u_action,
+                    "c%d_actions" % case: np.array(acts, np.int32)})
+    out["cases"] = np.int32(2)
+    np.savez_compressed(os.path.join(HERE, "policy_reference.npz"), **out)
+
+
 def main():
+    policy_cases()
     td_cases()
     with open(os.path.join(HERE, "nstep_literal.json"), "w") as f:
         json.dump(nstep_cases(), f, indent=1)
