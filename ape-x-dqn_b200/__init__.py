@@ -15,8 +15,9 @@ from .pipeline import HostStepPipeline                        # noqa: F401
 from .ingest import VectorActorIngest, ActorStagingRing, RingIngest   # noqa: F401
 from .weights import (WeightPublisher, WeightSubscriber, DeviceWeightSubscriber, BatchedActorPolicy,   # noqa: F401
                       actor_policy, actor_epsilons, param_layout)
+from .vector_actor import VectorActor                         # noqa: F401
 
 __all__ = ["ReplayMemory", "Learner", "Actor", "ExperienceBuffer", "N_Step_Transition", "Transition", "Batch",
            "KeyIndex", "stream_offsets", "td_loss", "ops", "ShardedSampler", "HostStepPipeline", "VectorActorIngest", "ActorStagingRing", "RingIngest",
            "WeightPublisher", "WeightSubscriber", "DeviceWeightSubscriber", "BatchedActorPolicy", "actor_policy",
-           "actor_epsilons", "param_layout"]
+           "actor_epsilons", "param_layout", "VectorActor"]

@@ -192,21 +192,20 @@ class WeightSubscriber:
         self.layout, self.flat_bytes = param_layout(module.state_dict())
         self.board = _Board(name, self.flat_bytes, len(self.layout), create=False)
         self.seen = 0
-        self._scratch = np.empty(self.flat_bytes, np.uint8)
 
-    def poll(self):
-        """Load the newest published weights into the module if they changed; -> True when loaded."""
-        if self.board.version <= self.seen:
-            return False
-        v = self.board.read_consistent(lambda slot: np.copyto(self._scratch, slot))
-        if v <= self.seen:
-            return False
+    def _copy_into_module(self, slot):
         sd = self.module.state_dict()
         with torch.no_grad():
             for (name, shape, dtype, off, nbytes) in self.layout:
-                src = torch.from_numpy(self._scratch[off:off + nbytes]).view(dtype).view(shape)
-                sd[name].copy_(src)
-        self.seen = v
+                sd[name].copy_(torch.from_numpy(slot[off:off + nbytes]).view(dtype).view(shape))
+
+    def poll(self):
+        """Load the newest published weights into the module if they changed; -> True when loaded.
+        The slot is copied straight into the parameters (one pass over the bytes) and the copy is
+        repeated if the publisher began overwriting that slot meanwhile."""
+        if self.board.version <= self.seen:
+            return False
+        self.seen = self.board.read_consistent(self._copy_into_module)
         return True
 
     def close(self):
@@ -220,17 +219,23 @@ class DeviceWeightSubscriber(_DeviceBoard):
         super().__init__(module)
         self.board = _Board(name, self.flat_bytes, len(self.layout), create=False)
         self.seen = 0
-        self._pinned = torch.empty(self.flat_bytes, dtype=torch.uint8, pin_memory=True)
-        self._pinned_np = self._pinned.numpy()
+        base = self.board.slots[0].ctypes.data - _HEADER          # page-lock: H2D straight out of the board
+        rc = torch.cuda.cudart().cudaHostRegister(base, _HEADER + 2 * self.board.slot_bytes, 0)
+        if int(rc) != 0:
+            raise RuntimeError("cudaHostRegister of the weight board failed (%d)" % int(rc))
+        self._base = base
 
     def poll(self, stream=None):
+        """Newest published weights -> the module's tensors (H2D from the slot + K9 scatter on `stream`).
+        Waits for the copy so that the seqlock can be checked; repeated if the slot was being rewritten."""
         if self.board.version <= self.seen:
             return False
-        v = self.board.read_consistent(lambda slot: np.copyto(self._pinned_np, slot))
-        if v <= self.seen:
-            return False
-        _C.call("apexb200_params_load", self._h, C.c_void_p(self._pinned.data_ptr()), 1, _C.stream_ptr(stream))
-        self.seen = v
+        st = stream if stream is not None else torch.cuda.current_stream()
+
+        def load(slot):
+            _C.call("apexb200_params_load", self._h, C.c_void_p(slot.ctypes.data), 1, _C.stream_ptr(st))
+            st.synchronize()
+        self.seen = self.board.read_consistent(load)
         return True
 
     def load_from(self, flat_dev, stream=None):
@@ -239,6 +244,9 @@ class DeviceWeightSubscriber(_DeviceBoard):
 
     def close(self):
         self.destroy()
+        if self._base is not None:
+            torch.cuda.cudart().cudaHostUnregister(self._base)
+            self._base = None
         self.board.close()
 
 

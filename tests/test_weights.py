@@ -321,3 +321,108 @@ def test_batched_actor_policy_equals_batch1_actors():
     ue2, ua2 = po.kernel_uniforms(5, 1, E)
     want2, _ = po.epsilon_greedy(q.cpu().numpy(), pol.eps.cpu().numpy(), ue2, ua2)
     np.testing.assert_array_equal(acts2.cpu().numpy(), want2)
+
+
+class _CounterEnv:
+    """Deterministic toy environment (gym protocol): every frame names (env, episode, step)."""
+
+    def __init__(self, eid, episode_len):
+        self.eid, self.L, self.ep, self.k = eid, episode_len, -1, 0
+        self.log = []                                    # (frame tag, action, reward, done) per step
+
+    def _obs(self):
+        f = np.zeros((4, 4), np.uint8)
+        f[0, 0], f[0, 1], f[0, 2] = self.eid, self.ep % 256, self.k % 256
+        f[1:] = (self.eid * 31 + self.ep * 7 + self.k) % 251
+        return f
+
+    def reset(self):
+        self.ep, self.k = self.ep + 1, 0
+        return self._obs()
+
+    def step(self, a):
+        tag = (self.ep, self.k)
+        self.k += 1
+        r = float(((a + 1) * (self.k % 5) - 4) / 4.0)
+        d = self.k >= self.L
+        self.log.append((tag, int(a), r, d))
+        return self._obs(), r, d, {}
+
+
+class _TinyDuelling(torch.nn.Module):
+    def __init__(self, C_, A):
+        super().__init__()
+        self.v = torch.nn.Linear(C_ * 16, 1)
+        self.a = torch.nn.Linear(C_ * 16, A)
+
+    def forward(self, x):
+        x = x.reshape(x.shape[0], -1) / 255.0
+        v, a = self.v(x), self.a(x)
+        return v, a, v + (a - a.sum() / a.shape[1])
+
+
+@pytest.mark.gpu
+def test_vector_actor_end_to_end():
+    """E lock-stepped actors: what lands in the replay is what the environments and the policy produced
+    (frames, stacks with episode-start repeats, actions, sliding n-step returns, Gamma = 0 at terminals,
+    initial priorities from the policy's own Q rows), and the actors' weights follow the learner's board."""
+    import apex_b200 as apex
+    dev = torch.device("cuda")
+    torch.manual_seed(8)
+    E, C_, A, n, gamma, lane_cap, T = 5, 3, 4, 3, 0.9, 256, 90
+    mem = apex.ReplayMemory(E * lane_cap, {"priority_exponent": 0.6, "layout": "stream", "lanes": E, "n_step": n,
+                                           "state_shape": (C_, 4, 4), "num_actions": 0})
+    learner_q, actor_q = _TinyDuelling(C_, A).to(dev), _TinyDuelling(C_, A).to(dev)
+    name = "apexboard_va_%d" % os.getpid()
+    pub = apex.WeightPublisher(learner_q, name=name, create=True)
+    try:
+        pub.wait(pub.publish())
+        sub = apex.DeviceWeightSubscriber(actor_q, name)
+        envs = [_CounterEnv(e, 7 + 3 * e) for e in range(E)]
+        params = {"epsilon": 0.4, "alpha": 7, "num_actors": E, "num_steps": n, "gamma": gamma, "Q_network_sync_freq": 10,
+                  "n_step_transition_batch_size": 4}
+        va = apex.VectorActor(envs, actor_q, mem, params, weights=sub, seed=3)
+        seen_q = []
+        act0 = va.policy.act
+        va.policy.act = lambda obs, **kw: (lambda r: (seen_q.append((obs.clone(), r[1].clone())), r)[1])(act0(obs, **kw))
+        assert va.run(50) == E * 50
+        with torch.no_grad():
+            for t in learner_q.parameters():
+                t.add_(0.125)
+        pub.wait(pub.publish())
+        assert va.run(T - 50) == E * (T - 50)
+        torch.cuda.synchronize()
+        assert sub.seen == 2
+        for a, b in zip(learner_q.state_dict().values(), actor_q.state_dict().values()):
+            assert torch.equal(a, b)
+        assert len(va.episode_returns) == sum(T // env.L for env in envs)
+        A_d, R_d, G_d = (mem.buffer(w).cpu().numpy() for w in (apex._C.BUF_ACTION, apex._C.BUF_REWARD, apex._C.BUF_GAMMA))
+        leaves = mem.buffer(apex._C.BUF_LEAVES).cpu().numpy().view(np.uint64)
+        fidx = mem.buffer(apex._C.BUF_FIDX).cpu().numpy().reshape(-1, 2 * C_)
+        store = mem.buffer(apex._C.BUF_FRAMES).cpu().numpy().reshape(-1, 16)
+        qs = torch.stack([q for _, q in seen_q], 1).cpu().numpy()               # [E, T, A]: Q(s_tau) the policy used
+        stacks = torch.stack([o for o, _ in seen_q], 1).cpu().numpy()           # [E, T, C, 4, 4]
+        for e, env in enumerate(envs):
+            assert len(env.log) == T
+            buf = apex.ExperienceBuffer(n, e, semantics="sliding", gamma=gamma)
+            for t, (tag, a, r, d) in enumerate(env.log):
+                buf.add(apex.Transition(t, a, r, gamma, qs[e, t]))
+                if d:
+                    buf.construct_nstep_transition(apex.Transition(t + 1, 0, 0, gamma, qs[e, min(t + 1, T - 1)]))
+            recs = {r.S_t: r for r in buf.get(buf.size)}
+            for tau in range(n, T):
+                t, slot = tau - n, e * lane_cap + tau
+                r = recs[t]
+                assert A_d[slot] == r.A_t == env.log[t][1]
+                assert R_d[slot] == pytest.approx(r.R_ttpB, rel=1e-5, abs=1e-6)
+                assert G_d[slot] == pytest.approx(r.Gamma_ttpB, rel=1e-5)
+                want_p = abs(r.R_ttpB + r.Gamma_ttpB * float(qs[e, tau].max()) - float(qs[e, t, r.A_t]))
+                assert leaves[slot] / float(1 << 24) == pytest.approx(want_p ** 0.6, rel=1e-4, abs=2e-7)
+                # the state the learner will gather for this record is the state the policy saw at step t
+                np.testing.assert_array_equal(store[fidx[slot, :C_]].reshape(C_, 4, 4), stacks[e, t])
+                if r.Gamma_ttpB != 0.0:
+                    np.testing.assert_array_equal(store[fidx[slot, C_:]].reshape(C_, 4, 4), stacks[e, tau])
+        mem.check_status()
+        sub.close()
+    finally:
+        pub.close(unlink=True)
