@@ -27,6 +27,7 @@ struct ParamChunk {
 struct PublishNode {
     volatile int64_t *ctrl;
     int64_t version;
+    volatile int pending;                     // set at enqueue, cleared by the host callback
 };
 
 }  // namespace apexb200
@@ -40,7 +41,7 @@ struct apexb200_params {
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t packed = nullptr, copied = nullptr;
     bool copy_pending = false;
-    apexb200::PublishNode nodes[apexb200::kPublishNodes];
+    apexb200::PublishNode nodes[apexb200::kPublishNodes] = {};
     unsigned node_next = 0;
 };
 
@@ -130,6 +131,7 @@ actor_policy_kernel(const float *__restrict__ value, const float *__restrict__ a
 static void CUDART_CB publish_done(void *arg) {
     PublishNode *n = static_cast<PublishNode *>(arg);
     *n->ctrl = n->version;                    // "completed" word of the shared-memory board
+    n->pending = 0;
 }
 
 }  // namespace apexb200
@@ -212,8 +214,10 @@ int apexb200_params_publish(apexb200_params_t p, void *slot_host, int64_t *ctrl_
     ctrl_host[1] = version;                                                   // "begun": readers of this slot must re-check
     APEX_CUDA(cudaMemcpyAsync(slot_host, p->flat, p->flat_bytes, cudaMemcpyDeviceToHost, p->copy_stream));
     PublishNode *node = &p->nodes[p->node_next++ % kPublishNodes];
+    if (node->pending) APEX_CUDA(cudaStreamSynchronize(p->copy_stream));      // > kPublishNodes publications in flight
     node->ctrl = ctrl_host;
     node->version = version;
+    node->pending = 1;
     APEX_CUDA(cudaLaunchHostFunc(p->copy_stream, publish_done, node));
     APEX_CUDA(cudaEventRecord(p->copied, p->copy_stream));
     p->copy_pending = true;

@@ -286,6 +286,18 @@ def test_weight_board_odd_tensors():
         torch.cuda.synchronize()
         for a, b in zip(src.state_dict().values(), dst.state_dict().values()):
             assert torch.equal(a, b)
+        # a burst of publications without waiting (more than the library keeps callback slots for):
+        # versions complete in order and the last slot holds the last state
+        for k in range(20):
+            with torch.no_grad():
+                src.b.add_(1.0)
+            last = pub.publish()
+        pub.wait(last)
+        assert pub.version == last == v + 20 and int(pub.board.ctrl[1]) == last
+        np.testing.assert_array_equal(pub.board.slots[last & 1], po.pack_flat([t.cpu().numpy() for t in src.state_dict().values()]))
+        assert sub.poll() and sub.seen == last
+        torch.cuda.synchronize()
+        assert torch.equal(src.b, dst.b)
         sub.close()
     finally:
         pub.close(unlink=True)
