@@ -8,7 +8,7 @@ the repository root (``import apex_b200``).
 from . import _C                                              # noqa: F401
 from .replay import ReplayMemory, N_Step_Transition, Batch, KeyIndex, stream_offsets   # noqa: F401
 from .actor import ExperienceBuffer, Actor, Transition        # noqa: F401
-from .learner import Learner, td_loss                         # noqa: F401
+from .learner import Learner, ShardedLearner, FlatGradients, td_loss   # noqa: F401
 from . import ops                                             # noqa: F401
 from .sharded import ShardedSampler                           # noqa: F401
 from .pipeline import HostStepPipeline                        # noqa: F401
@@ -20,4 +20,4 @@ from .vector_actor import VectorActor                         # noqa: F401
 __all__ = ["ReplayMemory", "Learner", "Actor", "ExperienceBuffer", "N_Step_Transition", "Transition", "Batch",
            "KeyIndex", "stream_offsets", "td_loss", "ops", "ShardedSampler", "HostStepPipeline", "VectorActorIngest", "ActorStagingRing", "RingIngest",
            "WeightPublisher", "WeightSubscriber", "DeviceWeightSubscriber", "BatchedActorPolicy", "actor_policy",
-           "actor_epsilons", "param_layout", "VectorActor"]
+           "actor_epsilons", "param_layout", "VectorActor", "ShardedLearner", "FlatGradients"]

@@ -32,34 +32,41 @@ class _TDLoss(torch.autograd.Function):
     (learner.py:43-48: the target is built under no_grad)."""
 
     @staticmethod
-    def forward(ctx, q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, replay, idx, alpha, eps, loss_kind, kappa, weights=None):
+    def forward(ctx, q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, replay, idx, alpha, eps, loss_kind, kappa, weights=None,
+                count_dev=None, mean_divisor=0.0):
         q_on_t, q_on_tpn, q_tg_tpn = (x.detach().contiguous().float() for x in (q_on_t, q_on_tpn, q_tg_tpn))
         if replay is not None:
             delta, prio, loss, mean = replay.td_update(idx, q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, loss_kind, kappa,
-                                                       weights=weights)
+                                                       weights=weights, count_dev=count_dev, mean_divisor=mean_divisor)
         else:
+            if count_dev is not None:
+                raise ValueError("count_dev / mean_divisor need a replay (sharded batches)")
             delta, prio, loss, mean = ops.td_forward(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, alpha, eps, loss_kind, kappa,
                                                      weights=weights)
         ctx.save_for_backward(delta, A)
-        ctx.weights = weights
-        ctx.meta = (q_on_t.shape[1], loss_kind, kappa)
+        ctx.weights, ctx.count_dev = weights, count_dev
+        ctx.meta = (q_on_t.shape[1], loss_kind, kappa, float(mean_divisor))
         ctx.mark_non_differentiable(delta, prio, loss)
         return mean.reshape(()), delta, prio, loss
 
     @staticmethod
     def backward(ctx, g_mean, _gd, _gp, _gl):
         delta, A = ctx.saved_tensors
-        nA, loss_kind, kappa = ctx.meta
+        nA, loss_kind, kappa, mean_divisor = ctx.meta
         g = g_mean.detach().reshape(1).float().contiguous()
-        return (ops.td_backward(delta, A, g, nA, loss_kind, kappa, weights=ctx.weights),) + (None,) * 12
+        return (ops.td_backward(delta, A, g, nA, loss_kind, kappa, count_dev=ctx.count_dev, mean_divisor=mean_divisor,
+                                weights=ctx.weights),) + (None,) * 14
 
 
 def td_loss(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, alpha=0.6, eps=0.0, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0,
-            replay=None, idx=None, weights=None):
+            replay=None, idx=None, weights=None, count_dev=None, mean_divisor=0.0):
     """Differentiable fused loss.  Returns (loss_mean, delta, prio, loss).  With `replay` and `idx`
     the new priorities are also written into the replay's sum tree in the same call; `weights`
-    (f32 [B], e.g. ops.is_weights) multiply the per-record loss and gradient."""
-    return _TDLoss.apply(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, replay, idx, alpha, eps, loss_kind, kappa, weights)
+    (f32 [B], e.g. ops.is_weights) multiply the per-record loss and gradient.  Sharded batches:
+    count_dev (int32 [1], device) = live rows, mean_divisor = global batch size, so that the sum of
+    the ranks' loss_mean (and of their gradients) is the mean over the global batch."""
+    return _TDLoss.apply(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, replay, idx, alpha, eps, loss_kind, kappa, weights,
+                         count_dev, mean_divisor)
 
 
 class Learner(object):
@@ -102,13 +109,13 @@ class Learner(object):
     def _fast(self):
         return isinstance(self.replay_memory, ReplayMemory)
 
-    def _loss_from_tensors(self, S_t, S_tpn, A, R, Gamma, replay=None, idx=None):
+    def _loss_from_tensors(self, S_t, S_tpn, A, R, Gamma, replay=None, idx=None, count_dev=None, mean_divisor=0.0):
         with torch.no_grad():                                                  # learner.py:43-45
             q_tg_tpn = self.Q_double(S_tpn)[2]
             q_on_tpn = self.Q(S_tpn)[2]
         q_on_t = self.Q(S_t)[2]                                                # learner.py:46
         return td_loss(q_on_t, q_on_tpn, q_tg_tpn, A, R, Gamma, self.alpha, 0.0, self.loss_kind, self.kappa,
-                       replay=replay, idx=idx)
+                       replay=replay, idx=idx, count_dev=count_dev, mean_divisor=mean_divisor)
 
     # ------------------------------------------------------------- reference API
     def compute_loss_and_priorities(self, xp_batch):
@@ -232,3 +239,94 @@ class Learner(object):
         if board is not None:
             board.wait(board._issued)
             board.close(unlink=bool(self.params.get("weight_board_unlink", False)))
+
+
+class FlatGradients:
+    """All parameter gradients as views of one flat buffer, so that the data-parallel reduction is one
+    collective call (and zeroing is one memset).  Device-agnostic (tested with gloo on the CPU)."""
+
+    def __init__(self, parameters):
+        self.params = [p for p in parameters if p.requires_grad]
+        total = sum(p.numel() for p in self.params)
+        first = self.params[0]
+        self.flat = torch.zeros(total, dtype=first.dtype, device=first.device)
+        off = 0
+        for p in self.params:
+            p.grad = self.flat[off:off + p.numel()].view_as(p)
+            off += p.numel()
+
+    def zero(self):
+        self.flat.zero_()
+
+    def all_reduce(self, group=None):
+        import torch.distributed as dist
+        if dist.is_initialized() and dist.get_world_size(group) > 1:
+            dist.all_reduce(self.flat, group=group)                      # sum: every rank divided by the global batch
+        return self.flat
+
+
+class ShardedLearner(Learner):
+    """One rank of the data-parallel learner over a sharded replay (BASELINE configs[3]; no
+    counterpart in the single-process reference).  Every rank owns a replay shard and a replica of
+    the networks; per step it takes its share of the global stratified batch (fused K8+K3+K4 over
+    peer memory), runs the unchanged model on it, all-reduces the flat gradient (NCCL) and applies
+    the identical RMSprop step; K5+K2 write the new priorities into the local shard and push the
+    shard's new total to the peers.  loss_mean is divided by the global batch on every rank."""
+
+    def __init__(self, env_conf, learner_params, shared_state, shared_replay_memory, group=None, quota=None):
+        super().__init__(env_conf, learner_params, shared_state, shared_replay_memory)
+        import torch.distributed as dist
+        from .sharded import ShardedSampler
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.sampler = ShardedSampler(shared_replay_memory, group=group, rank=self.rank, world_size=self.world)
+        B = int(self.params["replay_sample_size"])
+        self.global_batch = B * self.world
+        # rows this rank may own in one step: its fair share plus slack for uneven shard totals
+        # (a multiple of 147, the CTAs the fused kernel spreads a B=512 share over: 588 rows there)
+        self.max_rows = int(quota) if quota else (-(-int(B * 1.14) // 147) * 147 if B >= 256 else int(B * 1.5) + 8)
+        self._ready = False
+
+    def setup(self):
+        """Collective: move the networks to the device, make every replica equal to rank 0's
+        (K9 snapshot -> broadcast -> K9 scatter), lay the gradients out flat, connect the shards."""
+        import torch.distributed as dist
+        from .weights import _DeviceBoard
+        dev = self._to_device()
+        for net in (self.Q, self.Q_double):
+            board = _DeviceBoard(net)
+            from . import _C as C_
+            C_.call("apexb200_params_publish", board._h, None, None, 0, C_.stream_ptr())      # pack
+            flat = board.flat()
+            if self.world > 1:
+                dist.broadcast(flat, src=dist.get_global_rank(self.group, 0) if self.group is not None else 0, group=self.group)
+            C_.call("apexb200_params_load", board._h, None, 0, C_.stream_ptr())                # scatter
+            torch.cuda.current_stream().synchronize()
+            board.destroy()
+        self.grads = FlatGradients(self.Q.parameters())
+        self.sampler.connect_peers()
+        self.sampler.push_on_update(True)
+        self.sampler.exchange()
+        self._ready = True
+        return dev
+
+    def after_insert(self):
+        """Collective: inserts changed the shard totals at different rates; re-publish them."""
+        self.sampler.exchange()
+
+    def step_sharded(self):
+        if not self._ready:
+            self.setup()
+        batch, _pos, cnt = self.sampler.sample_fused(self.global_batch, self.max_rows)
+        shape = (self.max_rows,) + tuple(self.state_shape)
+        S_t, S_tpn = batch.S_t.view(shape).float(), batch.S_tpn.view(shape).float()
+        loss, _delta, _prio, _ = self._loss_from_tensors(S_t, S_tpn, batch.A, batch.R, batch.Gamma, replay=self.replay_memory,
+                                                         idx=batch.idx, count_dev=cnt, mean_divisor=float(self.global_batch))
+        self.grads.zero()
+        loss.backward()
+        self.grads.all_reduce(self.group)
+        self.optimizer.step()
+        self.num_q_updates += 1
+        self._maybe_sync_target()
+        return loss.detach()              # this rank's share; the sum over ranks is the global mean loss

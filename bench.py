@@ -567,10 +567,15 @@ def run_reference(args):
 
 
 def run_learner(args):
-    """BASELINE configs[2]: Ape-X learner loop, 2M-record replay, batch 512, n=3 double-DQN, 1 GPU.
+    """BASELINE configs[2]: Ape-X learner loop, 2M-record replay, batch 512, n=3 double-DQN, 1 GPU; under
+    torchrun (N > 1) configs[3]: the replay sharded over N GPUs (2M records each), data-parallel learner with
+    a gradient all-reduce, and 256/8 = 32 synthetic actors per GPU inserting through K7 + K6 every step.
     Not the headline metric's workload; prints its own JSON line."""
     import torch
     import apex_b200
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1:
+        return run_learner_sharded(args, world)
     torch.cuda.set_device(0)
     dev = torch.device("cuda:0")
     B, C, nA, N = args.batch, args.frames_per_state, args.actions, args.capacity
@@ -619,6 +624,72 @@ def run_learner(args):
                       "config": {"workload": "learner loop: sample+gather -> 3 forwards + backward + RMSprop (PyTorch/cuDNN fp32) -> "
                                              "fused TD/priority update; whole step replayed from one CUDA graph",
                                  "model": "duelling conv net 3.33M params (unchanged)"}}))
+
+
+def run_learner_sharded(args, world):
+    import torch
+    import torch.distributed as dist
+    import apex_b200
+    rank, local = int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    B, C, nA, N = args.batch, args.frames_per_state, args.actions, args.capacity
+    mem = apex_b200.ReplayMemory(N, {"priority_exponent": ALPHA, "layout": "stream", "lanes": args.lanes, "n_step": 3,
+                                     "state_shape": (C, 84, 84), "seed": 4321})
+    fill_shard(torch, apex_b200, mem, args, dev, 1234 + rank)
+    lp = {"remove_old_xp_freq": 100, "q_target_sync_freq": 2500, "min_replay_mem_size": 20000, "replay_sample_size": B,
+          "load_saved_state": False}
+    L = apex_b200.ShardedLearner({"state_shape": [C, 84, 84], "action_dim": nA}, lp, {}, mem)
+    L.setup()
+    # 256 actors over the box = 256 / world per GPU, one ring lane each, T env steps per learner step
+    E, T, every = min(max(256 // world, 1), args.lanes), 8, 4        # chunks of 8 env steps every 4th learner step
+    ingest = apex_b200.VectorActorIngest(mem, E, n_step=3, gamma=0.99, lanes=list(range(E)))
+    gen = torch.Generator(device=dev).manual_seed(77 + rank)
+    pool = [(torch.randint(0, 256, (E, T, F_BYTES), dtype=torch.uint8, device=dev, generator=gen),
+             torch.randint(0, nA, (E, T), dtype=torch.int32, device=dev, generator=gen),
+             torch.randn(E, T, device=dev, generator=gen).clamp_(-1, 1),
+             np.zeros((E, T), bool), torch.randn(E, T, nA, device=dev, generator=gen)) for _ in range(4)]
+
+    def step(k):
+        if k % every == 0:
+            ingest.push(*pool[(k // every) % 4])                  # K7 + initial priority + K6 into E lanes
+            L.after_insert()                                      # totals changed at different rates: one exchange launch
+        return L.step_sharded()
+
+    for k in range(max(args.warmup, 3)):
+        step(k)
+    K = min(args.steps, 200)
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for k in range(K):
+        loss = step(k)
+    e1.record()
+    dist.barrier()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    total = loss.clone().reshape(1)
+    dist.all_reduce(total)
+    mem.check_status()
+    csum = torch.stack([p.double().sum() for p in L.Q.parameters()]).sum().reshape(1)
+    both = [torch.zeros_like(csum) for _ in range(world)]
+    dist.all_gather(both, csum)
+    if rank == 0:
+        ms = float(ms)
+        print(json.dumps({"metric": "Ape-X sharded learner loop transitions/s (2M cap per GPU, B=512 per GPU, duelling net fp32)",
+                          "value": round(K * B * world / (ms * 1e-3), 1), "unit": "transitions/s", "n_gpus": world, "steps": K,
+                          "ms_per_step": round(ms / K, 4), "final_global_loss": float(total), "scaling": "weak",
+                          "replicas_equal": len({float(x) for x in both}) == 1,
+                          "inserted_per_step_per_gpu": E * T / every, "higher_is_better": True, "data": "synthetic",
+                          "config": {"workload": "sharded learner loop: %d actors x %d env steps inserted per GPU every 4th step (K7+K6) -> "
+                                                 "shard exchange -> fused sharded sample+gather (peer memory) -> 3 forwards + backward "
+                                                 "(cuDNN fp32) -> flat gradient all-reduce (NCCL) -> RMSprop -> fused TD/priority "
+                                                 "update with total push; eager launches" % (E, T),
+                                     "model": "duelling conv net 3.33M params (unchanged)"}}))
+    dist.destroy_process_group()
 
 
 if __name__ == "__main__":

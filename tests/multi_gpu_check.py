@@ -42,6 +42,85 @@ def shard_data(rank, n, C, F, lanes):
     return ring, ops
 
 
+def sharded_learner_check(rank, world, dev):
+    """BASELINE configs[3] in small: data-parallel learner over a sharded replay.  The all-reduced
+    gradient equals the gradient of one process evaluating the whole global batch (torch autograd on
+    the all-gathered rows), every replica holds the same weights after the step, and the ranks'
+    losses add up to the global mean."""
+    import copy
+    tf32 = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    ok = True
+    n, C, lanes, B, nA = 4096, 1, 4, 32, 4
+    mem = apex_b200.ReplayMemory(n, {"priority_exponent": 0.6, "layout": "stream", "lanes": lanes, "n_step": 3,
+                                     "state_shape": (C, 84, 84), "seed": 99})
+    g = torch.Generator(device=dev).manual_seed(500 + rank)
+    m = n // lanes - 8                                               # one insert call must leave the lookback zone free
+    rel = torch.as_tensor(apex_b200.stream_offsets(C, np.full(m, 3), np.minimum(np.arange(m) + 10, 200))).to(dev)
+    for lane in range(lanes):
+        mem.insert(lane, torch.randint(0, 256, (m, 7056), dtype=torch.uint8, device=dev, generator=g), rel,
+                   torch.randint(0, nA, (m,), dtype=torch.int32, device=dev, generator=g),
+                   torch.randn(m, device=dev, generator=g), torch.full((m,), 0.97, device=dev),
+                   prio=torch.rand(m, device=dev, generator=g) * (1 + rank) + 0.01)
+    torch.manual_seed(1000 + rank)                                   # replicas start different: setup() must equalise them
+    lp = {"remove_old_xp_freq": 100, "q_target_sync_freq": 2500, "min_replay_mem_size": 10, "replay_sample_size": B,
+          "load_saved_state": False}
+    L = apex_b200.ShardedLearner({"state_shape": [C, 84, 84], "action_dim": nA}, lp, {}, mem)
+    L.Q.batch_coupled_mean = L.Q_double.batch_coupled_mean = False   # per-row duelling mean: rows are independent (Q19)
+    L.setup()
+    Bg, rows = B * world, L.max_rows
+
+    def checksum(net):
+        s = torch.stack([p.double().sum() for p in net.state_dict().values()]).sum().reshape(1)
+        both = [torch.zeros_like(s) for _ in range(world)]
+        dist.all_gather(both, s)
+        return [float(x) for x in both]
+    equal_start = len(set(checksum(L.Q))) == 1 and len(set(checksum(L.Q_double))) == 1
+    if not equal_start:
+        print("sharded_learner_check rank %d: replicas differ after setup()" % rank, flush=True)
+    ok &= equal_start
+    for step in range(2):
+        q_before, qd_before = copy.deepcopy(L.Q), copy.deepcopy(L.Q_double)
+        loss = L.step_sharded()
+        o = mem._outputs(rows, False)
+        cnt = o["count"].clone()
+        parts = []
+        for name in ("S_t", "S_tpn", "A", "R", "Gamma"):
+            mine = o[name].clone()
+            every = [torch.zeros_like(mine) for _ in range(world)]
+            dist.all_gather(every, mine)
+            parts.append(every)
+        counts = [torch.zeros_like(cnt) for _ in range(world)]
+        dist.all_gather(counts, cnt)
+        counts = [int(c.item()) for c in counts]
+        report = {"counts": sum(counts) == Bg}
+        S_t, S_tpn, A, R, G = (torch.cat([e[r][:counts[r]] for r in range(world)]) for e in parts)
+        S_t, S_tpn = S_t.view(Bg, C, 84, 84).float(), S_tpn.view(Bg, C, 84, 84).float()
+        with torch.no_grad():
+            q_tg, q_on_n = qd_before(S_tpn)[2], q_before(S_tpn)[2]
+        q_on = q_before(S_t)[2]
+        target = R + G * q_tg.gather(1, q_on_n.argmax(1, keepdim=True)).squeeze(1)
+        delta = target - q_on.gather(1, A.long().view(-1, 1)).squeeze(1)
+        ref_loss = (0.5 * delta * delta).mean()
+        ref_loss.backward()
+        ref_grad = torch.cat([p.grad.reshape(-1) for p in q_before.parameters()])
+        got = L.grads.flat
+        scale = float(ref_grad.abs().max())
+        report["grad"] = bool(((got - ref_grad).abs().max() <= 2e-3 * scale + 1e-7).item())
+        total = loss.clone().reshape(1)
+        dist.all_reduce(total)
+        ref_loss = float(ref_loss.detach())
+        report["loss"] = abs(float(total) - ref_loss) <= 1e-4 * abs(ref_loss) + 1e-6
+        report["replicas"] = len(set(checksum(L.Q))) == 1
+        if not all(report.values()):
+            print("sharded_learner_check rank %d step %d: %s  grad err %.3e of %.3e, loss %.6f vs %.6f" %
+                  (rank, step, report, float((got - ref_grad).abs().max()), scale, float(total), ref_loss), flush=True)
+        ok &= all(report.values())
+    mem.check_status()
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = tf32
+    return bool(ok)
+
+
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -180,6 +259,9 @@ def main():
             sampler.exchange()
             rnd += 1
     mem.check_status()
+    if not ok:
+        print("multi_gpu_check rank %d: replay sections failed" % rank, flush=True)
+    ok &= sharded_learner_check(rank, world, dev)
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
