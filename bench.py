@@ -52,6 +52,8 @@ def parse():
     ap.add_argument("--no-push", action="store_true",
                     help="multi-GPU: exchange the totals with one shard_exchange launch per step instead of "
                          "publishing them from the TD/update kernel")
+    ap.add_argument("--sharded-loop", action="store_true",
+                    help="--workload learner at N=1: run the eager sharded-learner loop (the N>1 code path) on one GPU")
     ap.add_argument("--workload", default="replay", choices=["replay", "learner"],
                     help="replay = BASELINE configs[1] microbench (default, the metric's workload); "
                          "learner = configs[2]: the same loop with the duelling network fwd/bwd + RMSprop in it")
@@ -574,7 +576,7 @@ def run_learner(args):
     import torch
     import apex_b200
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    if world > 1:
+    if world > 1 or args.sharded_loop:
         return run_learner_sharded(args, world)
     torch.cuda.set_device(0)
     dev = torch.device("cuda:0")
@@ -633,7 +635,18 @@ def run_learner_sharded(args, world):
     rank, local = int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    dist.init_process_group("nccl", device_id=dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce_(t, op=None):
+        if world > 1:
+            dist.all_reduce(t, op=op if op is not None else dist.ReduceOp.SUM)
+        return t
     B, C, nA, N = args.batch, args.frames_per_state, args.actions, args.capacity
     mem = apex_b200.ReplayMemory(N, {"priority_exponent": ALPHA, "layout": "stream", "lanes": args.lanes, "n_step": 3,
                                      "state_shape": (C, 84, 84), "seed": 4321})
@@ -660,23 +673,20 @@ def run_learner_sharded(args, world):
     for k in range(max(args.warmup, 3)):
         step(k)
     K = min(args.steps, 200)
-    dist.barrier()
-    torch.cuda.synchronize()
+    barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for k in range(K):
         loss = step(k)
     e1.record()
-    dist.barrier()
-    torch.cuda.synchronize()
-    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    total = loss.clone().reshape(1)
-    dist.all_reduce(total)
+    barrier()
+    ms = reduce_(torch.tensor([e0.elapsed_time(e1)], device=dev), dist.ReduceOp.MAX)
+    total = reduce_(loss.clone().reshape(1))
     mem.check_status()
     csum = torch.stack([p.double().sum() for p in L.Q.parameters()]).sum().reshape(1)
     both = [torch.zeros_like(csum) for _ in range(world)]
-    dist.all_gather(both, csum)
+    if world > 1:
+        dist.all_gather(both, csum)
     if rank == 0:
         ms = float(ms)
         print(json.dumps({"metric": "Ape-X sharded learner loop transitions/s (2M cap per GPU, B=512 per GPU, duelling net fp32)",
@@ -689,7 +699,8 @@ def run_learner_sharded(args, world):
                                                  "(cuDNN fp32) -> flat gradient all-reduce (NCCL) -> RMSprop -> fused TD/priority "
                                                  "update with total push; eager launches" % (E, T),
                                      "model": "duelling conv net 3.33M params (unchanged)"}}))
-    dist.destroy_process_group()
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
