@@ -20,6 +20,7 @@ FRAC_BITS = 24
 LEAF_MAX = (1 << 36) - 1
 MAX_CAPACITY = 1 << 24
 TD_NOALLOC_MAX_B = 262144
+HOST_STEP_SLOTS = 4
 BUF_FRAMES, BUF_FIDX, BUF_ACTION, BUF_REWARD, BUF_GAMMA, BUF_QT, BUF_QTPN, BUF_LEAVES = range(8)
 
 
@@ -89,6 +90,8 @@ SIGNATURES = {
     "apexb200_params_publish": [_P, _P, _P, _I64, _P],
     "apexb200_params_load": [_P, _P, _I32, _P],
     "apexb200_actor_policy": [_P, _P, _P, _P, _P, C.c_uint64, C.c_uint64, _I32, _I32, _P, _P, _P, _P],
+    "apexb200_host_register": [_P, C.c_uint64],
+    "apexb200_host_unregister": [_P],
     "apexb200_replay_buffer": [_P, _I32, C.POINTER(_P), C.POINTER(_I64)],
     "apexb200_replay_get_heads": [_P, C.POINTER(_I64)],
     "apexb200_replay_set_heads": [_P, C.POINTER(_I64)],
@@ -135,3 +138,12 @@ def stream_ptr(stream=None):
     import torch
     s = stream if stream is not None else torch.cuda.current_stream()
     return C.c_void_p(s.cuda_stream)
+
+
+def host_register(address, nbytes):
+    """Page-lock [address, address + nbytes) for this process so that copies to and from it are asynchronous."""
+    call("apexb200_host_register", C.c_void_p(address), int(nbytes))
+
+
+def host_unregister(address):
+    call("apexb200_host_unregister", C.c_void_p(address))

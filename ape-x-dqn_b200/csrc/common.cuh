@@ -281,11 +281,12 @@ struct apexb200_replay {
     int push_on_update = 0;            // td_fwd_update also publishes the new total to the peers
     // apexb200_host_step: two sets of device staging + copy streams, so that the H2D copy of step
     // k+1 and the D2H copy of step k overlap the kernels of the other step
-    unsigned char *hs_in[2] = {nullptr, nullptr};
-    float *hs_out[2] = {nullptr, nullptr};
+    unsigned char *hs_in[APEXB200_HOST_STEP_SLOTS] = {};
+    float *hs_out[APEXB200_HOST_STEP_SLOTS] = {};
     size_t hs_in_cap = 0, hs_out_cap = 0;
     cudaStream_t hs_copy_in = nullptr, hs_copy_out = nullptr;
-    cudaEvent_t hs_ev_in[2] = {nullptr, nullptr}, hs_ev_k[2] = {nullptr, nullptr}, hs_ev_out[2] = {nullptr, nullptr};
+    cudaEvent_t hs_ev_in[APEXB200_HOST_STEP_SLOTS] = {}, hs_ev_k[APEXB200_HOST_STEP_SLOTS] = {},
+                hs_ev_out[APEXB200_HOST_STEP_SLOTS] = {};
     unsigned long long draw_calls = 0; // host: stratified-draw calls issued (the `call` of strat_uniform)
     std::vector<long long> lane_count; // host ring heads
     int64_t device_bytes = 0;

@@ -224,12 +224,14 @@ int apexb200_replay_destroy(apexb200_replay_t h) {
     for (void *m : h->opened) if (m) cudaIpcCloseMemHandle(m);
     if (h->hs_copy_in) cudaStreamDestroy(h->hs_copy_in);
     if (h->hs_copy_out) cudaStreamDestroy(h->hs_copy_out);
-    for (int k = 0; k < 2; ++k) {
+    for (int k = 0; k < APEXB200_HOST_STEP_SLOTS; ++k) {
         if (h->hs_ev_in[k]) cudaEventDestroy(h->hs_ev_in[k]);
         if (h->hs_ev_k[k]) cudaEventDestroy(h->hs_ev_k[k]);
         if (h->hs_ev_out[k]) cudaEventDestroy(h->hs_ev_out[k]);
+        if (h->hs_in[k]) cudaFree(h->hs_in[k]);
+        if (h->hs_out[k]) cudaFree(h->hs_out[k]);
     }
-    void *ptrs[] = {h->hs_in[0], h->hs_in[1], h->hs_out[0], h->hs_out[1], h->xbuf, h->tree_block, h->stamp, h->status, h->ring.frames, h->ring.fidx, h->ring.A,
+    void *ptrs[] = {h->xbuf, h->tree_block, h->stamp, h->status, h->ring.frames, h->ring.fidx, h->ring.A,
                     h->ring.R, h->ring.G, h->ring.q_t, h->ring.q_tpn};
     for (void *p : ptrs) if (p) cudaFree(p);
     delete h;
@@ -326,42 +328,56 @@ int apexb200_peer_connect(apexb200_replay_t h, int32_t rank, int32_t world, cons
     return APEXB200_OK;
 }
 
-int apexb200_host_step(apexb200_replay_t h, int32_t slot, const double *u_host, const float *q_host, int32_t B,
-                       int32_t num_actions, float eps, int32_t loss_kind, float kappa, uint8_t *S_t, uint8_t *S_tpn,
-                       int32_t *A, float *R, float *Gamma, float *result_host, void *done_event, void *stream) {
-    APEX_REQUIRE(h && u_host && q_host && result_host && S_t && S_tpn && A && R && Gamma, APEXB200_EINVAL,
-                 "host_step: null argument");
-    APEX_REQUIRE(slot == 0 || slot == 1, APEXB200_EINVAL, "host_step: slot must be 0 or 1");
-    APEX_REQUIRE(B > 0 && B <= 1024 && num_actions >= 1 && num_actions <= APEXB200_MAX_ACTIONS, APEXB200_ERANGE,
-                 "host_step: B=%d (max 1024) / num_actions=%d out of range", B, num_actions);
-    cudaStream_t st = (cudaStream_t)stream;
-    const size_t in_bytes = (size_t)B * 8 + (size_t)3 * B * num_actions * 4;
-    const size_t out_words = (size_t)4 * B + 4;
-    if (!h->hs_copy_in) {                                        // first call: copy streams and events
+}  // extern "C"
+
+namespace apexb200 {
+// Copy streams, events and device staging of the host-facing step (first call / larger batch).
+static int host_step_prepare(apexb200_replay *h, size_t in_bytes, size_t out_bytes) {
+    if (!h->hs_copy_in) {
         APEX_CUDA(cudaSetDevice(h->cfg.device));
         APEX_CUDA(cudaStreamCreateWithFlags(&h->hs_copy_in, cudaStreamNonBlocking));
         APEX_CUDA(cudaStreamCreateWithFlags(&h->hs_copy_out, cudaStreamNonBlocking));
-        for (int k = 0; k < 2; ++k) {
+        for (int k = 0; k < APEXB200_HOST_STEP_SLOTS; ++k) {
             APEX_CUDA(cudaEventCreateWithFlags(&h->hs_ev_in[k], cudaEventDisableTiming));
             APEX_CUDA(cudaEventCreateWithFlags(&h->hs_ev_k[k], cudaEventDisableTiming));
             APEX_CUDA(cudaEventCreateWithFlags(&h->hs_ev_out[k], cudaEventDisableTiming));
         }
     }
-    if (in_bytes > h->hs_in_cap || out_words * 4 > h->hs_out_cap) {          // first call / larger batch: grow staging
+    if (in_bytes > h->hs_in_cap || out_bytes > h->hs_out_cap) {
         APEX_CUDA(cudaDeviceSynchronize());
-        for (int k = 0; k < 2; ++k) {
+        for (int k = 0; k < APEXB200_HOST_STEP_SLOTS; ++k) {
             if (h->hs_in[k]) cudaFree(h->hs_in[k]);
             if (h->hs_out[k]) cudaFree(h->hs_out[k]);
             h->hs_in[k] = nullptr; h->hs_out[k] = nullptr;
         }
         h->hs_in_cap = h->hs_out_cap = 0;
-        for (int k = 0; k < 2; ++k) {
+        for (int k = 0; k < APEXB200_HOST_STEP_SLOTS; ++k) {
             APEX_CUDA(cudaMalloc((void **)&h->hs_in[k], in_bytes));
-            APEX_CUDA(cudaMalloc((void **)&h->hs_out[k], out_words * 4));
+            APEX_CUDA(cudaMalloc((void **)&h->hs_out[k], out_bytes));
         }
         h->hs_in_cap = in_bytes;
-        h->hs_out_cap = out_words * 4;
+        h->hs_out_cap = out_bytes;
     }
+    return APEXB200_OK;
+}
+}  // namespace apexb200
+
+extern "C" {
+
+int apexb200_host_step(apexb200_replay_t h, int32_t slot, const double *u_host, const float *q_host, int32_t B,
+                       int32_t num_actions, float eps, int32_t loss_kind, float kappa, uint8_t *S_t, uint8_t *S_tpn,
+                       int32_t *A, float *R, float *Gamma, float *result_host, void *done_event, void *stream) {
+    APEX_REQUIRE(h && u_host && q_host && result_host && S_t && S_tpn && A && R && Gamma, APEXB200_EINVAL,
+                 "host_step: null argument");
+    APEX_REQUIRE(slot >= 0 && slot < APEXB200_HOST_STEP_SLOTS, APEXB200_EINVAL, "host_step: slot must be in [0, %d)",
+                 APEXB200_HOST_STEP_SLOTS);
+    APEX_REQUIRE(B > 0 && B <= 1024 && num_actions >= 1 && num_actions <= APEXB200_MAX_ACTIONS, APEXB200_ERANGE,
+                 "host_step: B=%d (max 1024) / num_actions=%d out of range", B, num_actions);
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t in_bytes = (size_t)B * 8 + (size_t)3 * B * num_actions * 4;
+    const size_t out_words = (size_t)4 * B + 4;
+    int prc = host_step_prepare(h, in_bytes, out_words * 4);
+    if (prc) return prc;
     unsigned char *d_in = h->hs_in[slot];
     float *d_res = h->hs_out[slot];
     // copy-in stream: the staging of this slot is free once the kernels of its previous use are done
@@ -393,6 +409,27 @@ int apexb200_host_step(apexb200_replay_t h, int32_t slot, const double *u_host, 
     APEX_CUDA(cudaMemcpyAsync(result_host, d_res, out_words * 4, cudaMemcpyDeviceToHost, h->hs_copy_out));
     APEX_CUDA(cudaEventRecord(h->hs_ev_out[slot], h->hs_copy_out));
     if (done_event) APEX_CUDA(cudaEventRecord((cudaEvent_t)done_event, h->hs_copy_out));
+    return APEXB200_OK;
+}
+
+int apexb200_host_register(void *address_host, uint64_t bytes) {
+    APEX_REQUIRE(address_host && bytes > 0, APEXB200_EINVAL, "host_register: null or empty range");
+    cudaError_t e = cudaHostRegister(address_host, bytes, cudaHostRegisterDefault);
+    if (e == cudaErrorHostMemoryAlreadyRegistered) {
+        // a registration left behind by an earlier mapping of this virtual range (unmapped without unregister)
+        cudaGetLastError();
+        cudaHostUnregister(address_host);
+        cudaGetLastError();
+        e = cudaHostRegister(address_host, bytes, cudaHostRegisterDefault);
+    }
+    if (e != cudaSuccess) { cudaGetLastError(); return cuda_fail(e, "cudaHostRegister"); }
+    return APEXB200_OK;
+}
+
+int apexb200_host_unregister(void *address_host) {
+    APEX_REQUIRE(address_host, APEXB200_EINVAL, "host_unregister: null argument");
+    cudaError_t e = cudaHostUnregister(address_host);
+    if (e != cudaSuccess) { cudaGetLastError(); return cuda_fail(e, "cudaHostUnregister"); }
     return APEXB200_OK;
 }
 

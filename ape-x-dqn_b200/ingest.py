@@ -155,9 +155,10 @@ class ActorStagingRing:
     def register_cuda(self):
         """Page-lock the shared memory for this process so that H2D copies out of it are asynchronous."""
         if not self._registered:
-            ptr = self._data.ctypes.data - 256
-            rc = torch.cuda.cudart().cudaHostRegister(ptr, 256 + self.slots * self.slot_bytes, 0)
-            self._registered = int(rc) == 0
+            from . import _C
+            self._reg_base = self._data.ctypes.data - 256
+            _C.host_register(self._reg_base, 256 + self.slots * self.slot_bytes)
+            self._registered = True
         return self._registered
 
     def pop(self):
@@ -172,6 +173,10 @@ class ActorStagingRing:
         self.ctrl[1] = int(self.ctrl[1]) + 1
 
     def close(self, unlink=False):
+        if self._registered:                              # before the mapping goes away: the range may be reused
+            from . import _C
+            _C.host_unregister(self._reg_base)
+            self._registered = False
         self.ctrl = self._data = None
         self.shm.close()
         if unlink:

@@ -5,7 +5,9 @@ use_graph=True replays a torch CUDA graph of the tensor-API calls instead.
 
 Replaces, for a caller that keeps its numbers on the host like the reference does, the
 round trip learner.py:68 (sample) -> :70 (loss, priorities) -> :76 (set_priorities).
-Two buffer sets are used alternately, so the host can fill step k+1 while step k runs.
+`depth` buffer sets (default 3, at most _C.HOST_STEP_SLOTS) are used in turn, so the host can fill and
+submit steps k+1 .. k+depth-1 while step k runs; with depth 2 the device idles whenever the
+host's wake-up + submit latency exceeds one step (measured: 5 us of every 22).
 """
 from __future__ import annotations
 
@@ -16,10 +18,14 @@ from . import _C
 
 
 class HostStepPipeline:
-    DEPTH = 2
+    DEPTH = 3
 
-    def __init__(self, mem, batch_size, num_actions, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0, use_graph=False):
+    def __init__(self, mem, batch_size, num_actions, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0, use_graph=False, depth=None):
         mem._ensure()
+        if depth is not None:
+            if not 1 <= int(depth) <= _C.HOST_STEP_SLOTS:
+                raise ValueError("depth must be in [1, %d]" % _C.HOST_STEP_SLOTS)
+            self.DEPTH = int(depth)
         self.mem, self.B, self.nA = mem, int(batch_size), int(num_actions)
         B, nA, dev = self.B, self.nA, mem.device
         self.in_bytes = B * 8 + 3 * B * nA * 4

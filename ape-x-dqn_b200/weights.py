@@ -144,9 +144,7 @@ class WeightPublisher(_DeviceBoard):
         self.board = _Board(name, self.flat_bytes, len(self.layout), create)
         self.name = self.board.name
         base = self.board.slots[0].ctypes.data - _HEADER
-        rc = torch.cuda.cudart().cudaHostRegister(base, _HEADER + 2 * self.board.slot_bytes, 0)
-        if int(rc) != 0:
-            raise RuntimeError("cudaHostRegister of the weight board failed (%d)" % int(rc))
+        _C.host_register(base, _HEADER + 2 * self.board.slot_bytes)
         self._base = base
         self._issued = int(self.board.ctrl[1])
 
@@ -179,7 +177,7 @@ class WeightPublisher(_DeviceBoard):
     def close(self, unlink=True):
         self.destroy()                                          # drains the copy stream
         if self._base is not None:
-            torch.cuda.cudart().cudaHostUnregister(self._base)
+            _C.host_unregister(self._base)
             self._base = None
         self.board.close(unlink=unlink)
 
@@ -220,9 +218,7 @@ class DeviceWeightSubscriber(_DeviceBoard):
         self.board = _Board(name, self.flat_bytes, len(self.layout), create=False)
         self.seen = 0
         base = self.board.slots[0].ctypes.data - _HEADER          # page-lock: H2D straight out of the board
-        rc = torch.cuda.cudart().cudaHostRegister(base, _HEADER + 2 * self.board.slot_bytes, 0)
-        if int(rc) != 0:
-            raise RuntimeError("cudaHostRegister of the weight board failed (%d)" % int(rc))
+        _C.host_register(base, _HEADER + 2 * self.board.slot_bytes)
         self._base = base
 
     def poll(self, stream=None):
@@ -245,7 +241,7 @@ class DeviceWeightSubscriber(_DeviceBoard):
     def close(self):
         self.destroy()
         if self._base is not None:
-            torch.cuda.cudart().cudaHostUnregister(self._base)
+            _C.host_unregister(self._base)
             self._base = None
         self.board.close()
 

@@ -10,6 +10,7 @@ K3 proportional search -> K4 frame gather -> K5 double-DQN TD/loss/|delta|^alpha
 Under torchrun every rank owns a 2M shard and the global batch is 512 x N (weak scaling).
 """
 import argparse
+import collections
 import json
 import os
 import subprocess
@@ -369,19 +370,20 @@ def run_ours(args):
             pipe.result(pipe.submit(u_host[k % 64], q_host[k % P]))
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        prev = None
+        pending = collections.deque()
         for k in range(n_e):
-            t = pipe.submit(u_host[k % 64], q_host[k % P])        # fills the pinned inputs, one graph launch
-            if prev is not None:
-                losses += pipe.result(prev)[0]                    # host reads step k-1 while step k runs
-            prev = t
-        losses += pipe.result(prev)[0]
+            pending.append(pipe.submit(u_host[k % 64], q_host[k % P]))   # fills the pinned inputs, one C call
+            if len(pending) == pipe.DEPTH:
+                losses += pipe.result(pending.popleft())[0]       # host reads step k-2 while steps k-1, k are queued
+        while pending:
+            losses += pipe.result(pending.popleft())[0]
         dt = time.perf_counter() - t0
         e2e = {"value": round(n_e * B / dt, 1), "unit": "transitions/s", "h2d_bytes_per_step": pipe.in_bytes,
                "d2h_bytes_per_step": pipe.out_words * 4, "steps": n_e, "ms_per_step": round(dt / n_e * 1e3, 4),
                "api": "apex_b200.HostStepPipeline.submit(u_host, q_host)/result() -> C ABI apexb200_host_step: pinned H2D of "
                       "draws+Q on a copy stream, fused sample+gather, TD+update, D2H of loss/priorities/indices on a copy "
-                      "stream, ordered by events; results read on the host one step behind (2 buffer sets)",
+                      "stream, ordered by events; every step's results are read on the host, %d steps behind (%d buffer sets)"
+                      % (pipe.DEPTH - 1, pipe.DEPTH),
                "mean_loss": round(losses / n_e, 6)}
     clk = clocks.stop()
     mem.check_status()

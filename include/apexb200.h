@@ -53,6 +53,7 @@ extern "C" {
 #define APEXB200_MAX_CAPACITY (1ll << 24)   /* records per handle (shard) */
 #define APEXB200_MAX_ACTIONS 64
 
+#define APEXB200_HOST_STEP_SLOTS 4           /* buffer sets of apexb200_host_step */
 #define APEXB200_TD_NOALLOC_MAX_B 262144    /* rows per call of apexb200_td_fwd_noalloc */
 
 #define APEXB200_LOSS_HALF_SQ 0         /* 1/2 delta^2, learner.py:48 */
@@ -278,8 +279,8 @@ int apexb200_td_fwd_update(apexb200_replay_t h, const int32_t *idx,
  * the learner's device batch tensors; result_host [4B+4] fp32, pinned, receives
  * delta[B] | priority[B] | loss[B] | record index[B] (int32 bits) | loss_mean.  The kernels
  * run on `stream`; the two copies run on copy streams owned by the handle and are ordered
- * with events, so with alternating slot = 0, 1 the H2D copy of one step and the D2H copy of
- * the previous one overlap the kernels.  done_event (cudaEvent_t, nullable) is recorded
+ * with events, so with slot cycling through 0 .. APEXB200_HOST_STEP_SLOTS-1 (or a prefix of
+ * them) the H2D copies of later steps and the D2H copies of earlier ones overlap the kernels.  done_event (cudaEvent_t, nullable) is recorded
  * after the D2H copy; the call returns without synchronising.  A slot's host buffers may be
  * refilled once its done_event has completed.  B <= 1024.  The first call (and any call
  * with a larger B) creates the copy streams and allocates the device staging. */
@@ -391,6 +392,13 @@ int apexb200_params_load(apexb200_params_t p, const void *flat_src, int32_t src_
 int apexb200_actor_policy(const float *value, const float *advantage_or_q, const float *eps, const double *u_explore,
                           const double *u_action, uint64_t seed, uint64_t step, int32_t E, int32_t A, float *q_out,
                           int32_t *actions, uint8_t *explored, void *stream);
+
+/* ---- page-locking of shared host memory (actor staging rings, weight boards: the transport that
+ * replaces the Manager queue / dict of main.py:21-25, 40-47).  Registers [address, address+bytes)
+ * with CUDA so that copies to and from it are asynchronous; a stale registration of the same
+ * virtual range is replaced.  Unregister before unmapping the memory. */
+int apexb200_host_register(void *address_host, uint64_t bytes);
+int apexb200_host_unregister(void *address_host);
 
 /* ---- raw access for checkpoint / tests (learner.py:18-23 is load-only; the
  * replay itself is never persisted by the reference) ---------------------- */

@@ -679,8 +679,8 @@ def test_peer_exchange_and_fused_sharded_sample_world1(apex):
     mem.check_status()
 
 
-@pytest.mark.parametrize("use_graph", [False, True])
-def test_host_step_pipeline(apex, use_graph):
+@pytest.mark.parametrize("use_graph,depth", [(False, 1), (False, 2), (True, 2), (False, 3), (False, 4), (True, 3)])
+def test_host_step_pipeline(apex, use_graph, depth):
     """apexb200_host_step / HostStepPipeline: host draws + Q in, host loss / priorities / indices out,
     equal to the oracle's sample -> TD -> write-back on the same numbers, step after step."""
     rng = np.random.default_rng(41)
@@ -695,24 +695,33 @@ def test_host_step_pipeline(apex, use_graph):
         mem.insert(*args, prio=prio)
         ring.insert(*args, prio=prio)
     ring.leaves[:] = u64(mem.buffer(apex._C.BUF_LEAVES))
-    pipe = apex.HostStepPipeline(mem, B, nA, use_graph=use_graph)
-    tickets, inputs = [], []
-    for k in range(5):
+    pipe = apex.HostStepPipeline(mem, B, nA, use_graph=use_graph, depth=depth)
+    with pytest.raises(ValueError):
+        apex.HostStepPipeline(mem, B, nA, depth=apex._C.HOST_STEP_SLOTS + 1)
+    tickets, inputs, steps, checked = [], [], 11, 0
+
+    def check(k):
+        t, (u0, q0) = tickets[k], inputs[k]
+        loss_mean, prio, idx = pipe.result(t)
+        want = ring.sample(u0)
+        np.testing.assert_array_equal(idx, want)
+        g = ring.gather(want)
+        o = to.td_forward(q0[0], q0[1], q0[2], g["A"], g["R"], g["G"], alpha=0.6)
+        np.testing.assert_allclose(prio, o["prio"], rtol=RTOL, atol=1e-7)
+        assert loss_mean == pytest.approx(o["loss_mean"], rel=RTOL)
+        ring.set_leaves(want, ro.priority_to_leaf(prio.copy()))
+
+    for k in range(steps):
         u = ro.stratified_uniforms(B, rng)
         q = rng.standard_normal((3, B, nA)).astype(np.float32)
         tickets.append(pipe.submit(u, q))
         inputs.append((u, q))
-        if k >= 1:                                                   # read one step behind, as the bench does
-            t, (u0, q0) = tickets[k - 1], inputs[k - 1]
-            loss_mean, prio, idx = pipe.result(t)
-            want = ring.sample(u0)
-            np.testing.assert_array_equal(idx, want)
-            g = ring.gather(want)
-            o = to.td_forward(q0[0], q0[1], q0[2], g["A"], g["R"], g["G"], alpha=0.6)
-            np.testing.assert_allclose(prio, o["prio"], rtol=RTOL, atol=1e-7)
-            assert loss_mean == pytest.approx(o["loss_mean"], rel=RTOL)
-            ring.set_leaves(want, ro.priority_to_leaf(prio.copy()))
-    pipe.result(tickets[-1])
+        if k >= depth - 1:                                           # read depth-1 steps behind, as the bench does
+            check(checked)
+            checked += 1
+    while checked < steps:
+        check(checked)
+        checked += 1
     mem.check_status()
 
 
