@@ -147,3 +147,26 @@ def host_register(address, nbytes):
 
 def host_unregister(address):
     call("apexb200_host_unregister", C.c_void_p(address))
+
+
+def open_shared_memory(name, create, size=0):
+    """multiprocessing.shared_memory.SharedMemory whose lifetime is explicit: the segment is taken off the
+    resource tracker, which would otherwise unlink it when *any* process that merely attached to it (or the
+    learner that created it) exits — rings and boards outlive the processes that come and go around them.
+    The owner unlinks it with .unlink()."""
+    from multiprocessing import resource_tracker, shared_memory
+    shm = shared_memory.SharedMemory(name=name, create=create, size=size if create else 0)
+    try:
+        resource_tracker.unregister(shm._name, "shared_memory")
+    except Exception:
+        pass
+    return shm
+
+
+def unlink_shared_memory(shm):
+    """shm.unlink() without the resource-tracker bookkeeping that open_shared_memory removed."""
+    import _posixshmem
+    try:
+        _posixshmem.shm_unlink(shm._name)
+    except FileNotFoundError:
+        pass

@@ -189,8 +189,17 @@ class Actor(mp.Process):
             self.Q.load_state_dict(self.shared_state["Q_state_dict"])                   # actor.py:106
         self._weights = None
         if self.params.get("weight_board"):               # K9 board published by the learner (weights.py)
+            import time
             from .weights import WeightSubscriber
-            self._weights = WeightSubscriber(self.Q, self.params["weight_board"])
+            deadline = time.time() + float(self.params.get("weight_board_wait_s", 60.0))
+            while True:                                   # the learner creates the board inside learn() (its own process)
+                try:
+                    self._weights = WeightSubscriber(self.Q, self.params["weight_board"])
+                    break
+                except FileNotFoundError:
+                    if time.time() > deadline:
+                        raise
+                    time.sleep(0.05)
             self._weights.poll()
         if self.env is None:
             if self._env_factory is not None:

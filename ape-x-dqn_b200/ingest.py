@@ -113,7 +113,7 @@ class ActorStagingRing:
     """
 
     def __init__(self, name, slots, chunk_steps, frame_bytes, num_actions, create):
-        from multiprocessing import shared_memory
+        from . import _C
         self.slots, self.T, self.F, self.nA = int(slots), int(chunk_steps), int(frame_bytes), int(num_actions)
         T, F, nA = self.T, self.F, self.nA
         self.off_act = T * F
@@ -122,7 +122,7 @@ class ActorStagingRing:
         self.off_q = self.off_done + ((T + 15) // 16) * 16
         self.slot_bytes = ((self.off_q + 4 * T * nA + 255) // 256) * 256
         total = 256 + self.slots * self.slot_bytes
-        self.shm = shared_memory.SharedMemory(name=name, create=create, size=total if create else 0)
+        self.shm = _C.open_shared_memory(name, create, total)
         self.ctrl = np.ndarray((8,), np.int64, self.shm.buf, 0)
         if create:
             self.ctrl[:] = 0
@@ -180,7 +180,8 @@ class ActorStagingRing:
         self.ctrl = self._data = None
         self.shm.close()
         if unlink:
-            self.shm.unlink()
+            from . import _C
+            _C.unlink_shared_memory(self.shm)
 
 
 class RingIngest:

@@ -211,16 +211,16 @@ class Learner(object):
         """learner.py:63-80."""
         if self.device is None:
             torch.set_num_threads(1)      # forked child (main.py:46): the parent's OpenMP pool is unusable here
+        board = None
+        if self.params.get("weight_board"):                 # K9: versioned shared-memory board instead of a pickle
+            from .weights import WeightPublisher            # (created first: the actors wait for it before they step)
+            self._to_device()
+            board = WeightPublisher(self.Q, name=self.params["weight_board"], create=True)
+            board.publish()
         while self.replay_memory.size() <= self.params["min_replay_mem_size"]:
             time.sleep(1)
         fast = self._fast()
         publish = int(self.params.get("weight_publish_freq", 500 if fast else 1))
-        board = None
-        if self.params.get("weight_board"):                 # K9: versioned shared-memory board instead of a pickle
-            from .weights import WeightPublisher
-            self._to_device()
-            board = WeightPublisher(self.Q, name=self.params["weight_board"], create=True)
-            board.publish()
         for t in range(T):
             if fast:
                 self.step_fast()

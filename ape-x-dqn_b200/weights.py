@@ -49,10 +49,9 @@ class _Board:
     """The shared-memory side, common to publisher and subscribers."""
 
     def __init__(self, name, flat_bytes, n_tensors, create):
-        from multiprocessing import shared_memory
         self.flat_bytes = int(flat_bytes)
         self.slot_bytes, total = _board_bytes(self.flat_bytes)
-        self.shm = shared_memory.SharedMemory(name=name, create=create, size=total if create else 0)
+        self.shm = _C.open_shared_memory(name, create, total)
         self.name = self.shm.name
         self.ctrl = np.ndarray((_CTRL_WORDS,), np.int64, self.shm.buf, 0)
         if create:
@@ -82,7 +81,7 @@ class _Board:
         self.ctrl = self.slots = None
         self.shm.close()
         if unlink:
-            self.shm.unlink()
+            _C.unlink_shared_memory(self.shm)
 
 
 def _spans_of(tensors, layout):

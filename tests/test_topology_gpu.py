@@ -52,6 +52,11 @@ SCRIPT = textwrap.dedent(r'''
         learner_params = {"remove_old_xp_freq": 10, "q_target_sync_freq": 10, "min_replay_mem_size": 40,
                           "replay_sample_size": 32, "load_saved_state": False}
         replay_params = {"soft_capacity": 2000, "priority_exponent": 0.6, "importance_sampling_exponent": 0.4}
+        import os
+        board = os.environ.get("APEX_TEST_BOARD")       # weights through the shared-memory board instead of the Manager dict
+        if board:
+            learner_params["weight_board"] = actor_params["weight_board"] = board
+            learner_params["weight_publish_freq"] = 5
         mp_manager = mp.Manager()                      # main.py:37-42
         shared_state, shared_mem, stop = mp_manager.dict(), mp_manager.Queue(), mp_manager.Event()
         replay_manager = BaseManager(); replay_manager.start()
@@ -71,18 +76,33 @@ SCRIPT = textwrap.dedent(r'''
         size = replay_mem.size()
         w1 = shared_state["Q_state_dict"]
         changed = any((w0[k] != w1[k]).any().item() for k in w0)
-        print("RESULT learner_exit=%%s actors_exit=%%s size=%%d weights_changed=%%s" %% (
-            learner_proc.exitcode, [a.exitcode for a in actors], size, changed))
+        version = -1
+        if board:
+            import apex_b200
+            shm = apex_b200._C.open_shared_memory(board, False)
+            version = int(np.ndarray((2,), np.int64, shm.buf, 0)[0])
+            shm.close(); apex_b200._C.unlink_shared_memory(shm)
+        print("RESULT learner_exit=%%s actors_exit=%%s size=%%d weights_changed=%%s board_version=%%d" %% (
+            learner_proc.exitcode, [a.exitcode for a in actors], size, changed, version))
         replay_manager.shutdown()
 ''') % (ROOT, os.path.join(ROOT, "ape-x-dqn_b200", "dropin"))
 
 
-def test_reference_topology_runs_on_dropin_classes(tmp_path):
+@pytest.mark.parametrize("use_board", [False, True])
+def test_reference_topology_runs_on_dropin_classes(tmp_path, use_board):
     script = tmp_path / "topology.py"
     script.write_text(SCRIPT)
-    out = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, timeout=300)
+    env = dict(os.environ)
+    env.pop("APEX_TEST_BOARD", None)
+    if use_board:
+        env["APEX_TEST_BOARD"] = "apexboard_topo_%d" % os.getpid()
+    out = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, timeout=300, env=env)
     line = [l for l in out.stdout.splitlines() if l.startswith("RESULT")]
     assert out.returncode == 0 and line, (out.stdout[-1500:], out.stderr[-3000:])
-    assert "learner_exit=0" in line[0] and "actors_exit=[0, 0]" in line[0] and "weights_changed=True" in line[0], line[0]
+    assert "learner_exit=0" in line[0] and "actors_exit=[0, 0]" in line[0], line[0]
     size = int(line[0].split("size=")[1].split()[0])
     assert size > 40
+    if use_board:       # learner.py:74 went through K9: 25 steps, one publication at start-up + every 5th step
+        assert int(line[0].split("board_version=")[1]) >= 5, line[0]
+    else:
+        assert "weights_changed=True" in line[0], line[0]

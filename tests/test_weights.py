@@ -438,3 +438,19 @@ def test_vector_actor_end_to_end():
         sub.close()
     finally:
         pub.close(unlink=True)
+
+
+@pytest.mark.gpu
+def test_host_register_replaces_a_stale_registration():
+    """A shared-memory mapping that went away without cudaHostUnregister leaves its virtual range registered;
+    apexb200_host_register of a later mapping at the same address must still succeed (and leave no error behind)."""
+    from apex_b200 import _C
+    buf = np.zeros(1 << 20, np.uint8)
+    addr = buf.ctypes.data & ~4095
+    _C.host_register(addr + 4096, 1 << 18)
+    _C.host_register(addr + 4096, 1 << 18)               # same range again: replaced, not an error
+    _C.host_unregister(addr + 4096)
+    with pytest.raises(_C.ApexError):
+        _C.host_unregister(addr + 4096)                  # not registered any more
+    x = torch.ones(8, device="cuda")                     # the CUDA error state is clean
+    assert float(x.sum()) == 8.0
