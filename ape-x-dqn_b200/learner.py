@@ -238,7 +238,9 @@ class Learner(object):
                 self.replay_memory.remove_to_fit()
         if board is not None:
             board.wait(board._issued)
-            board.close(unlink=bool(self.params.get("weight_board_unlink", False)))
+            # attached actors keep their mapping after the unlink; set weight_board_unlink=False to leave
+            # the segment for a supervisor to inspect and remove
+            board.close(unlink=bool(self.params.get("weight_board_unlink", True)))
 
 
 class FlatGradients:

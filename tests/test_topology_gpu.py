@@ -57,6 +57,7 @@ SCRIPT = textwrap.dedent(r'''
         if board:
             learner_params["weight_board"] = actor_params["weight_board"] = board
             learner_params["weight_publish_freq"] = 5
+            learner_params["weight_board_unlink"] = False   # this script reads the final version, then removes the board
         mp_manager = mp.Manager()                      # main.py:37-42
         shared_state, shared_mem, stop = mp_manager.dict(), mp_manager.Queue(), mp_manager.Event()
         replay_manager = BaseManager(); replay_manager.start()
