@@ -279,8 +279,53 @@ td_cluster_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32
     }
 }
 
-// ---- any B: 256 records per CTA; per-CTA loss partials go to scratch and the last
-// CTA to finish (ticket counter in scratch) adds them in CTA order.
+// td_one with every load issued before the first use (rows of up to kWideActions actions live in
+// registers; the selected entries are picked with compare-selects): one memory round trip per
+// record instead of two dependent ones.  Same operations on the same values as td_one.
+constexpr int kWideActions = 8;
+__device__ __forceinline__ void td_one_wide(const TdArgs &a, int b, float *loss_out) {
+    const float *row_t = a.q_on_t + (long long)b * a.nA;
+    const float *row_n = a.q_on_tpn + (long long)b * a.nA;
+    const float *row_g = a.q_tg_tpn + (long long)b * a.nA;
+    float qt[kWideActions], qn[kWideActions], qg[kWideActions];
+    #pragma unroll
+    for (int k = 0; k < kWideActions; ++k) {
+        const bool in = k < a.nA;
+        qn[k] = in ? __ldcs(row_n + k) : 0.0f;
+        qg[k] = in ? __ldcs(row_g + k) : 0.0f;
+        qt[k] = in ? __ldcs(row_t + k) : 0.0f;
+    }
+    int act = a.A[b];
+    const float r = a.R[b], g = a.G[b];
+    const float w = a.weights ? a.weights[b] : 1.0f;
+    act = act < 0 ? 0 : (act >= a.nA ? a.nA - 1 : act);
+    int arg = 0;
+    float best = qn[0];
+    #pragma unroll
+    for (int k = 1; k < kWideActions; ++k)
+        if (k < a.nA && qn[k] > best) { best = qn[k]; arg = k; }   // first maximum on ties (argmax, learner.py:45)
+    float g_sel = qg[0], t_sel = qt[0];
+    #pragma unroll
+    for (int k = 1; k < kWideActions; ++k) {
+        if (k == arg) g_sel = qg[k];
+        if (k == act) t_sel = qt[k];
+    }
+    const float target = __fadd_rn(r, __fmul_rn(g, g_sel));                      // learner.py:44
+    const float d = __fsub_rn(target, t_sel);                                    // learner.py:47
+    const float ad = fabsf(d);
+    float l;
+    if (a.loss_kind == APEXB200_LOSS_HALF_SQ) l = __fmul_rn(__fmul_rn(0.5f, d), d);   // learner.py:48
+    else l = ad <= a.kappa ? __fmul_rn(__fmul_rn(0.5f, d), d) : __fmul_rn(a.kappa, __fsub_rn(ad, 0.5f * a.kappa));
+    if (a.weights) l = __fmul_rn(l, w);
+    a.delta[b] = d;
+    a.prio[b] = prio_pow(ad, a.alpha, a.eps);
+    a.loss[b] = l;
+    *loss_out = l;
+}
+
+// ---- any B: 256 records per CTA; per-CTA loss partials go to scratch and the last CTA to finish
+// (ticket counter in scratch) adds them: thread t sums partials t, t+256, ... in that order, then
+// the fixed-shape block sum -> the same association for a given grid, whichever CTA is last.
 // scratch layout: [0] u32 ticket (zeroed by the host before launch), [64..] float partials.
 __global__ void __launch_bounds__(256)
 td_multi_kernel(TdArgs a, const int32_t *__restrict__ idx, uint32_t *__restrict__ stamp, long long N,
@@ -291,9 +336,11 @@ td_multi_kernel(TdArgs a, const int32_t *__restrict__ idx, uint32_t *__restrict_
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     float l = 0.0f;
     if (b < live_rows(a)) {
-        td_one(a, b, &l);
+        long long i = -1;
+        if (idx != nullptr) i = idx[b];                       // in flight with the rows
+        if (a.nA <= kWideActions) td_one_wide(a, b, &l);
+        else td_one(a, b, &l);
         if (idx != nullptr) {
-            long long i = idx[b];
             if (i < 0 || i >= N) atomicOr(status, APEXB200_ST_BAD_INDEX);
             else atomicMax(stamp + i, (uint32_t)b + 1u);
         }
@@ -306,11 +353,13 @@ td_multi_kernel(TdArgs a, const int32_t *__restrict__ idx, uint32_t *__restrict_
         is_last = (t == gridDim.x - 1);
     }
     __syncthreads();
-    if (is_last && threadIdx.x == 0) {
+    if (is_last) {
         __threadfence();
         float tot = 0.0f;
-        for (unsigned k = 0; k < gridDim.x; ++k) tot += __ldcg(partials + k);
-        *a.loss_mean = tot / mean_div(a);
+        for (unsigned k = threadIdx.x; k < gridDim.x; k += blockDim.x) tot += __ldcg(partials + k);
+        __syncthreads();                                      // warp_part is reused
+        tot = block_sum_fixed(tot, warp_part);
+        if (threadIdx.x == 0) *a.loss_mean = tot / mean_div(a);
     }
 }
 
