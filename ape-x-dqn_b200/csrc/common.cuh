@@ -287,7 +287,18 @@ struct apexb200_replay {
     cudaStream_t hs_copy_in = nullptr, hs_copy_out = nullptr;
     cudaEvent_t hs_ev_in[APEXB200_HOST_STEP_SLOTS] = {}, hs_ev_k[APEXB200_HOST_STEP_SLOTS] = {},
                 hs_ev_out[APEXB200_HOST_STEP_SLOTS] = {};
+    unsigned *hs_seq_host = nullptr;   // pinned [APEXB200_HOST_STEP_SLOTS]: source of the "inputs landed" words
+    unsigned hs_seq[APEXB200_HOST_STEP_SLOTS] = {};
     unsigned long long draw_calls = 0; // host: stratified-draw calls issued (the `call` of strat_uniform)
     std::vector<long long> lane_count; // host ring heads
     int64_t device_bytes = 0;
 };
+
+namespace apexb200 {
+// fused K3+K4 launcher shared with the host-facing step (gather.cu -> replay.cu)
+bool sample_gather_is_fused(const apexb200_replay *h);
+int run_sample_gather(apexb200_replay *h, const double *u, uint64_t seed, int32_t count, int32_t *idx_out,
+                      int32_t *fsel_out, uint64_t *leaf_out, uint64_t *total_out, double *u_out, uint8_t *S_t,
+                      uint8_t *S_tpn, int32_t *A, float *R, float *Gamma, float *q_t, float *q_tpn,
+                      const unsigned *ready, unsigned ready_value, cudaStream_t stream);
+}  // namespace apexb200

@@ -215,8 +215,10 @@ gather_tma_kernel(RingView rv, GatherArgs ga, int per_cta, int32_t *status) {
 // index and metadata outputs.  Half draws as the unit of work balance the frames over the
 // SMs: a B=512, C=4 batch is 1024 units = 147 CTAs of 7 warps (28 frames, 193 KB of
 // staging each), one CTA per SM, every frame of the batch in flight at once.
-__global__ void __launch_bounds__(512)
-sample_gather_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int32_t *ctrl) {
+template <bool kPolled>
+__device__ __forceinline__ void sample_gather_body(const TreeView &tv, const RingView &rv, const SampleArgs &sa,
+                                                   const GatherArgs &ga, int32_t *ctrl, const unsigned *ready,
+                                                   unsigned ready_value) {
     extern __shared__ __align__(128) uint8_t smem[];
     unsigned long long *bars = (unsigned long long *)smem;
     pdl_prologue();
@@ -237,8 +239,23 @@ sample_gather_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int
     if (strat) {
         uw = strat_uniform(sa.seed, read_epoch(ctrl), sa.call, w, count);
         if (sa.u_out && lane == 0 && half == 0) sa.u_out[w] = uw;
-    } else {
+    } else if (!kPolled) {
         uw = sa.u[w];
+    } else {
+        // apexb200_host_step: the draws arrive by an H2D copy on another stream, followed by a stream-ordered
+        // write of `ready_value` to *ready.  Polling it here keeps every cross-stream wait off the compute
+        // stream, so this kernel still chains to its predecessor by programmatic dependent launch.  The copy
+        // was issued a step or more ahead: normally the first load already sees the value.
+        if (lane == 0) {
+            const volatile unsigned *flag = ready;
+            const long long t0 = clock64();
+            while ((int)(*flag - ready_value) < 0) {
+                if (clock64() - t0 > (5ll << 31)) { atomicOr(ctrl, APEXB200_ST_PEER_TIMEOUT); break; }   // ~5 s
+            }
+            __threadfence();
+        }
+        __syncwarp();
+        uw = __ldcg(sa.u + w);                               // bypass L1: written by DMA while this CTA was resident
     }
     unsigned long long leaf, total;
     const long long node = warp_descend(tv, vtop, 0ull, true, uw, &leaf, &total, ctrl);
@@ -261,6 +278,18 @@ sample_gather_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int
         if (node >= 0 && lane == 16) copy_meta_row(rv, ga, w, node);
     }
     tma_drain_frames(moving, moving ? item_dst(rv, ga, w, k) : nullptr, stage, my_bars, (unsigned)rv.F, nch);
+}
+
+__global__ void __launch_bounds__(512)
+sample_gather_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int32_t *ctrl) {
+    sample_gather_body<false>(tv, rv, sa, ga, ctrl, nullptr, 0u);
+}
+
+// Same kernel for the host-facing step: waits in-kernel for the arrival word of its draws.
+__global__ void __launch_bounds__(512)
+sample_gather_polled_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int32_t *ctrl,
+                            const unsigned *ready, unsigned ready_value) {
+    sample_gather_body<true>(tv, rv, sa, ga, ctrl, ready, ready_value);
 }
 
 // ---- fused K8 + K3 + K4 for one rank of a sharded replay (after shard_exchange_kernel).
@@ -396,8 +425,9 @@ sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs
 }
 
 static int ensure_smem(const void *fn, size_t smem, int device) {
-    static size_t configured[3][64] = {};
-    const int which = (fn == (const void *)gather_tma_kernel) ? 0 : (fn == (const void *)sample_gather_kernel) ? 1 : 2;
+    static size_t configured[4][64] = {};
+    const int which = (fn == (const void *)gather_tma_kernel) ? 0 : (fn == (const void *)sample_gather_kernel) ? 1
+                    : (fn == (const void *)sample_gather_polled_kernel) ? 3 : 2;
     if (smem > 48 * 1024 && device >= 0 && device < 64 && smem > configured[which][device]) {
         APEX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[which][device] = smem;
@@ -451,6 +481,23 @@ int apexb200_sample_gather(apexb200_replay_t h, const double *u, uint64_t seed, 
                            int32_t *fsel_out, uint64_t *leaf_out, uint64_t *total_out, double *u_out, uint8_t *S_t,
                            uint8_t *S_tpn, int32_t *A, float *R, float *Gamma, float *q_t, float *q_tpn,
                            void *stream) {
+    return apexb200::run_sample_gather(h, u, seed, count, idx_out, fsel_out, leaf_out, total_out, u_out, S_t, S_tpn, A, R,
+                                       Gamma, q_t, q_tpn, nullptr, 0u, (cudaStream_t)stream);
+}
+
+}  // extern "C"
+
+namespace apexb200 {
+bool sample_gather_is_fused(const apexb200_replay *h) {
+    const RingView &rv = h->ring;
+    return rv.C <= 8 && (size_t)rv.C * rv.F + 8 * kMaxChunks * 8 <= kStageBudget;
+}
+
+// ready != null: the draws `u` land by a copy on another stream; the kernel polls *ready for ready_value.
+int run_sample_gather(apexb200_replay *h, const double *u, uint64_t seed, int32_t count, int32_t *idx_out,
+                      int32_t *fsel_out, uint64_t *leaf_out, uint64_t *total_out, double *u_out, uint8_t *S_t,
+                      uint8_t *S_tpn, int32_t *A, float *R, float *Gamma, float *q_t, float *q_tpn,
+                      const unsigned *ready, unsigned ready_value, cudaStream_t stream) {
     APEX_REQUIRE(h && count >= 0, APEXB200_EINVAL, "sample_gather: bad argument");
     if (count == 0) return APEXB200_OK;
     APEX_REQUIRE(idx_out && S_t && S_tpn, APEXB200_EINVAL, "sample_gather: null idx_out/S_t/S_tpn");
@@ -458,8 +505,9 @@ int apexb200_sample_gather(apexb200_replay_t h, const double *u, uint64_t seed, 
                  "sample_gather: output batches must be 16-byte aligned");
     const RingView &rv = h->ring;
     const size_t per_unit = (size_t)rv.C * rv.F + 8 * kMaxChunks * 8;       // one half draw: C frames + their mbarriers
-    cudaStream_t st = (cudaStream_t)stream;
+    cudaStream_t st = stream;
     if (rv.C > 8 || per_unit > kStageBudget) {
+        APEX_REQUIRE(!ready, APEXB200_ERANGE, "sample_gather: the polled variant needs the fused kernel");
         // staging for half a record does not fit one CTA: run the two kernels back to back
         int rc = u ? apexb200_sample(h, u, count, idx_out, leaf_out, total_out, fsel_out, stream)
                    : apexb200_sample_stratified(h, seed, count, idx_out, leaf_out, total_out, fsel_out, u_out, stream);
@@ -484,9 +532,20 @@ int apexb200_sample_gather(apexb200_replay_t h, const double *u, uint64_t seed, 
     SampleArgs sa{u, (unsigned long long)seed, u ? 0ull : h->draw_calls++, idx_out, fsel_out, (unsigned long long *)leaf_out,
                   (unsigned long long *)total_out, u_out};
     GatherArgs ga{idx_out, fsel_out, nullptr, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, count};
+    if (ready) {
+        APEX_REQUIRE(u, APEXB200_EINVAL, "sample_gather: the polled variant takes caller draws");
+        rc = ensure_smem((const void *)sample_gather_polled_kernel, smem, h->cfg.device);
+        if (rc) return rc;
+        return launch_step("sample_gather_polled_kernel", sample_gather_polled_kernel,
+                           dim3((unsigned)((units + wpc - 1) / wpc)), dim3(wpc * 32), smem, st, h->tree, rv, sa, ga,
+                           h->status, ready, ready_value);
+    }
     return launch_step("sample_gather_kernel", sample_gather_kernel, dim3((unsigned)((units + wpc - 1) / wpc)),
                        dim3(wpc * 32), smem, st, h->tree, rv, sa, ga, h->status);
 }
+}  // namespace apexb200
+
+extern "C" {
 
 int apexb200_sample_gather_sharded(apexb200_replay_t h, uint64_t seed, int32_t global_count, int32_t max_rows,
                                    int32_t *idx_out, int32_t *fsel_out, int32_t *pos_out, double *u_out,

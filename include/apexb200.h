@@ -278,9 +278,12 @@ int apexb200_td_fwd_update(apexb200_replay_t h, const int32_t *idx,
  * are in pinned HOST memory (one H2D copy if q_host == u_host + B); S_t/S_tpn/A/R/Gamma are
  * the learner's device batch tensors; result_host [4B+4] fp32, pinned, receives
  * delta[B] | priority[B] | loss[B] | record index[B] (int32 bits) | loss_mean.  The kernels
- * run on `stream`; the two copies run on copy streams owned by the handle and are ordered
- * with events, so with slot cycling through 0 .. APEXB200_HOST_STEP_SLOTS-1 (or a prefix of
- * them) the H2D copies of later steps and the D2H copies of earlier ones overlap the kernels.  done_event (cudaEvent_t, nullable) is recorded
+ * run on `stream`; the two copies run on copy streams owned by the handle, so with slot cycling
+ * through 0 .. APEXB200_HOST_STEP_SLOTS-1 (or a prefix of them) the H2D copies of later steps
+ * and the D2H copies of earlier ones overlap the kernels.  The D2H copy is ordered after the
+ * kernels by an event; the arrival of the inputs is signalled by a stream-ordered write of a
+ * device word behind the H2D copy, which the sampling kernel polls (no cross-stream wait on
+ * `stream`, so the kernels keep chaining by programmatic dependent launch across steps).  done_event (cudaEvent_t, nullable) is recorded
  * after the D2H copy; the call returns without synchronising.  A slot's host buffers may be
  * refilled once its done_event has completed.  B <= 1024.  The first call (and any call
  * with a larger B) creates the copy streams and allocates the device staging. */
