@@ -13,6 +13,7 @@ constexpr int kBuildParents = 8;
 __global__ void __launch_bounds__(256)
 tree_build_level_kernel(const unsigned long long *__restrict__ child, unsigned long long *__restrict__ parent,
                         long long n_child, long long n_parent) {
+    pdl_prologue();                                          // the level below was written by the previous launch
     const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     const long long p0 = w * kBuildParents;
@@ -289,8 +290,8 @@ int apexb200_tree_build(apexb200_replay_t h, void *stream) {
         long long np = tv.size[l + 1];
         long long warps = (np + kBuildParents - 1) / kBuildParents;
         long long blocks = (warps * 32 + 255) / 256;
-        tree_build_level_kernel<<<(unsigned)blocks, 256, 0, st>>>(tv.lvl[l], tv.lvl[l + 1], tv.size[l], np);
-        int rc = launch_check("tree_build_level_kernel");
+        int rc = launch_step("tree_build_level_kernel", tree_build_level_kernel, dim3((unsigned)blocks), dim3(256), 0, st,
+                             (const unsigned long long *)tv.lvl[l], tv.lvl[l + 1], tv.size[l], np);
         if (rc) return rc;
     }
     return APEXB200_OK;
