@@ -53,6 +53,7 @@ SIGNATURES = {
     "apexb200_replay_device_bytes": [_P, C.POINTER(_I64)],
     "apexb200_replay_status": [_P, C.POINTER(_I32), _P],
     "apexb200_replay_insert": [_P, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P, C.POINTER(_I64), _P],
+    "apexb200_replay_insert_lanes": [_P, _P, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "apexb200_tree_build": [_P, _P],
     "apexb200_tree_update": [_P, _P, _P, _I32, _F, _P],
     "apexb200_tree_set_leaves": [_P, _P, _P, _I32, _P],

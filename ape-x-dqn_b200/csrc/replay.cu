@@ -29,11 +29,22 @@ int cuda_fail(cudaError_t e, const char *what) {
 // contiguous, destination is contiguous up to the ring wrap).  One CTA row (blockIdx.y, strided)
 // per record, two vectors per thread in flight: no index division, ~2 loads outstanding per thread
 // and tens of thousands of CTAs keep HBM busy in both directions.
+// Up to kInsertLanes lanes per launch: lane ids and ring heads travel as a kernel parameter (blockIdx.z / .y
+// selects the entry), so E lock-stepped actors insert with one launch pair instead of E.
+constexpr int kInsertLanes = 64;
+struct LaneTable {
+    long long head[kInsertLanes];
+    int lane[kInsertLanes];
+};
+
 __global__ void __launch_bounds__(256)
 insert_frames_kernel(uint4 *__restrict__ ring_frames, const uint4 *__restrict__ src, int count,
-                     int vecs_per_record, long long lane_base, long long head, long long lane_cap) {
+                     int vecs_per_record, LaneTable lt, long long lane_cap) {
     const int v0 = blockIdx.x * 512 + threadIdx.x;
     const int v1 = v0 + 256;
+    const int e = blockIdx.z;
+    const long long lane_base = (long long)lt.lane[e] * lane_cap, head = lt.head[e];
+    src += (long long)e * count * vecs_per_record;
     for (int j = blockIdx.y; j < count; j += gridDim.y) {
         const long long slot = lane_base + (head + j) % lane_cap;
         const uint4 *s = src + (long long)j * vecs_per_record;
@@ -50,12 +61,21 @@ insert_frames_kernel(uint4 *__restrict__ ring_frames, const uint4 *__restrict__ 
 // and ancestor update for the `count` new records, plus invalidation of the
 // `lookback` records behind the new head.
 __global__ void __launch_bounds__(128)
-insert_meta_kernel(RingView rv, TreeView tv, int lane, long long head, int count,
+insert_meta_kernel(RingView rv, TreeView tv, LaneTable lt, int count,
                    const int32_t *__restrict__ rel, const int32_t *__restrict__ A,
                    const float *__restrict__ R, const float *__restrict__ G,
                    const float *__restrict__ prio, const float *__restrict__ q_t,
                    const float *__restrict__ q_tpn, int32_t *status) {
     bump_epoch(status);
+    const int e = blockIdx.y;                                   // inputs of entry e start at record e * count
+    const int lane = lt.lane[e];
+    const long long head = lt.head[e];
+    {
+        const long long o = (long long)e * count;
+        rel += o * 2 * rv.C; A += o; R += o; G += o;
+        if (prio) prio += o;
+        if (q_t) { q_t += o * rv.nA; q_tpn += o * rv.nA; }
+    }
     int j = blockIdx.x * blockDim.x + threadIdx.x;
     const bool active = j < count + rv.lookback;
     long long p = (head + (active ? j : 0)) % rv.lane_cap;
@@ -262,6 +282,51 @@ int apexb200_replay_status(apexb200_replay_t h, int32_t *status_host, void *stre
     return APEXB200_OK;
 }
 
+}  // extern "C"
+
+namespace apexb200 {
+// `n_lanes` lanes, `count` records each; inputs are [n_lanes, count, ...] contiguous.
+static int insert_lanes(apexb200_replay *h, const int32_t *lanes, int n_lanes, int32_t count, const uint8_t *frames,
+                        const int32_t *rel, const int32_t *A, const float *R, const float *Gamma, const float *prio,
+                        const float *q_t, const float *q_tpn, cudaStream_t st) {
+    const RingView &rv = h->ring;
+    APEX_REQUIRE((long long)count + rv.lookback <= rv.lane_cap, APEXB200_ERANGE,
+                 "replay_insert: count %d + lookback %d exceeds lane capacity %lld", count, rv.lookback, rv.lane_cap);
+    APEX_REQUIRE(frames && rel && A && R && Gamma, APEXB200_EINVAL, "replay_insert: null input");
+    APEX_REQUIRE(prio || (q_t && q_tpn && rv.nA > 0), APEXB200_EINVAL,
+                 "replay_insert: need prio, or q_t/q_tpn on a handle created with num_actions > 0");
+    APEX_REQUIRE(((uintptr_t)frames & 15) == 0, APEXB200_EINVAL, "replay_insert: frames must be 16-byte aligned");
+    const int vpr = rv.fpr * rv.F / 16;
+    const int twoC = 2 * rv.C;
+    for (int first = 0; first < n_lanes; first += kInsertLanes) {
+        const int m = n_lanes - first < kInsertLanes ? n_lanes - first : kInsertLanes;
+        LaneTable lt;
+        for (int e = 0; e < m; ++e) {
+            lt.lane[e] = lanes[first + e];
+            lt.head[e] = h->lane_count[lanes[first + e]] % rv.lane_cap;
+        }
+        const long long o = (long long)first * count;                // records before this group of lanes
+        int max_rows = kNumSMs * 8 / m;                              // ~8 resident CTAs per SM over all lanes
+        if (max_rows < 1) max_rows = 1;
+        const dim3 grid((unsigned)((vpr + 511) / 512), (unsigned)(count < max_rows ? count : max_rows), (unsigned)m);
+        insert_frames_kernel<<<grid, 256, 0, st>>>((uint4 *)rv.frames, (const uint4 *)frames + o * vpr, count, vpr, lt,
+                                                   rv.lane_cap);
+        int rc = launch_check("insert_frames_kernel");
+        if (rc) return rc;
+        const int nmeta = count + rv.lookback;
+        insert_meta_kernel<<<dim3((unsigned)((nmeta + 127) / 128), (unsigned)m), 128, 0, st>>>(
+            rv, h->tree, lt, count, rel + o * twoC, A + o, R + o, Gamma + o, prio ? prio + o : nullptr,
+            q_t ? q_t + o * rv.nA : nullptr, q_tpn ? q_tpn + o * rv.nA : nullptr, h->status);
+        rc = launch_check("insert_meta_kernel");
+        if (rc) return rc;
+        for (int e = 0; e < m; ++e) h->lane_count[lanes[first + e]] += count;
+    }
+    return APEXB200_OK;
+}
+}  // namespace apexb200
+
+extern "C" {
+
 int apexb200_replay_insert(apexb200_replay_t h, int32_t lane, int32_t count, const uint8_t *frames,
                            const int32_t *rel, const int32_t *A, const float *R, const float *Gamma,
                            const float *prio, const float *q_t, const float *q_tpn,
@@ -273,27 +338,26 @@ int apexb200_replay_insert(apexb200_replay_t h, int32_t lane, int32_t count, con
     const long long head = h->lane_count[lane] % rv.lane_cap;
     if (first_slot_host) *first_slot_host = (long long)lane * rv.lane_cap + head;
     if (count == 0) return APEXB200_OK;
-    APEX_REQUIRE((long long)count + rv.lookback <= rv.lane_cap, APEXB200_ERANGE,
-                 "replay_insert: count %d + lookback %d exceeds lane capacity %lld", count, rv.lookback, rv.lane_cap);
-    APEX_REQUIRE(frames && rel && A && R && Gamma, APEXB200_EINVAL, "replay_insert: null input");
-    APEX_REQUIRE(prio || (q_t && q_tpn && rv.nA > 0), APEXB200_EINVAL,
-                 "replay_insert: need prio, or q_t/q_tpn on a handle created with num_actions > 0");
-    APEX_REQUIRE(((uintptr_t)frames & 15) == 0, APEXB200_EINVAL, "replay_insert: frames must be 16-byte aligned");
-    cudaStream_t st = (cudaStream_t)stream;
-    const int vpr = rv.fpr * rv.F / 16;
-    const int max_rows = kNumSMs * 8;                          // 8 resident CTAs per SM, each loops over its records
-    const dim3 grid((unsigned)((vpr + 511) / 512), (unsigned)(count < max_rows ? count : max_rows));
-    insert_frames_kernel<<<grid, 256, 0, st>>>((uint4 *)rv.frames, (const uint4 *)frames, count, vpr,
-                                               (long long)lane * rv.lane_cap, head, rv.lane_cap);
-    int rc = launch_check("insert_frames_kernel");
-    if (rc) return rc;
-    const int nmeta = count + rv.lookback;
-    insert_meta_kernel<<<(nmeta + 127) / 128, 128, 0, st>>>(rv, h->tree, lane, head, count, rel, A, R, Gamma, prio,
-                                                            q_t, q_tpn, h->status);
-    rc = launch_check("insert_meta_kernel");
-    if (rc) return rc;
-    h->lane_count[lane] += count;
-    return APEXB200_OK;
+    return insert_lanes(h, &lane, 1, count, frames, rel, A, R, Gamma, prio, q_t, q_tpn, (cudaStream_t)stream);
+}
+
+int apexb200_replay_insert_lanes(apexb200_replay_t h, const int32_t *lanes_host, int32_t n_lanes, int32_t count,
+                                 const uint8_t *frames, const int32_t *rel, const int32_t *A, const float *R,
+                                 const float *Gamma, const float *prio, const float *q_t, const float *q_tpn,
+                                 void *stream) {
+    APEX_REQUIRE(h && lanes_host, APEXB200_EINVAL, "replay_insert_lanes: null argument");
+    const RingView &rv = h->ring;
+    APEX_REQUIRE(n_lanes >= 0 && n_lanes <= rv.lanes && count >= 0, APEXB200_EINVAL,
+                 "replay_insert_lanes: n_lanes %d / count %d out of range", n_lanes, count);
+    std::vector<char> seen((size_t)rv.lanes, 0);
+    for (int e = 0; e < n_lanes; ++e) {
+        const int l = lanes_host[e];
+        APEX_REQUIRE(l >= 0 && l < rv.lanes && !seen[l], APEXB200_EINVAL,
+                     "replay_insert_lanes: lane %d outside [0,%d) or listed twice", l, rv.lanes);
+        seen[l] = 1;
+    }
+    if (n_lanes == 0 || count == 0) return APEXB200_OK;
+    return insert_lanes(h, lanes_host, n_lanes, count, frames, rel, A, R, Gamma, prio, q_t, q_tpn, (cudaStream_t)stream);
 }
 
 int apexb200_peer_export(apexb200_replay_t h, void *ipc_handle_host) {

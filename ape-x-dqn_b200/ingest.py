@@ -91,9 +91,7 @@ class VectorActorIngest:
         rel = torch.as_tensor(np.concatenate([s_t, s_tpn], 2).astype(np.int32)).to(dev)
         prio = ops.initial_priority(q_t.reshape(E * T, -1), q_tpn.reshape(E * T, -1), A_rec.reshape(-1), R_rec.reshape(-1),
                                     G_rec.reshape(-1)).view(E, T) * prio_mask
-        for e in range(E):                                                   # K6, one lane per env
-            mem.insert(self.lanes[e], frames[e].reshape(T, -1), rel[e], A_rec[e], R_rec[e], G_rec[e],
-                       prio=prio[e].contiguous())
+        mem.insert_lanes(self.lanes, frames.reshape(E, T, -1), rel, A_rec, R_rec, G_rec, prio=prio.contiguous())   # K6, all lanes
         self.c_act, self.c_rew, self.c_done, self.c_q = (act[:, -n:].contiguous(), rew[:, -n:].contiguous(),
                                                          don[:, -n:].contiguous(), qq[:, -n:].contiguous())
         self.seen += T

@@ -273,6 +273,27 @@ class ReplayMemory(object):
         base = int(lane) * lane_cap
         return base + (first.value - base + np.arange(count, dtype=np.int64)) % lane_cap
 
+    def insert_lanes(self, lanes, frames, rel, A, R, Gamma, prio=None, q_t=None, q_tpn=None):
+        """K6 for several lanes in one launch pair (lock-stepped actors).  lanes: distinct lane ids [E];
+        every other argument carries a leading lane dimension: frames [E, T*frames_per_record, F],
+        rel [E, T, 2C], A/R/Gamma/prio [E, T], q_t/q_tpn [E, T, num_actions] — contiguous CUDA tensors
+        or host arrays."""
+        import torch
+        self._ensure()
+
+        def dev(x, dt):
+            if x is None:
+                return None
+            return x.contiguous() if isinstance(x, torch.Tensor) else self._dev(np.ascontiguousarray(x), dt)
+        lanes = (C.c_int32 * len(lanes))(*[int(x) for x in lanes])
+        E, T = int(A.shape[0]), int(A.shape[1])
+        if E != len(lanes):
+            raise ValueError("insert_lanes: %d lanes but inputs for %d" % (len(lanes), E))
+        frames, rel, A, R, Gamma = dev(frames, np.uint8), dev(rel, np.int32), dev(A, np.int32), dev(R, np.float32), dev(Gamma, np.float32)
+        prio, q_t, q_tpn = dev(prio, np.float32), dev(q_t, np.float32), dev(q_tpn, np.float32)
+        _C.call("apexb200_replay_insert_lanes", self._h, lanes, E, T, _C.ptr(frames), _C.ptr(rel), _C.ptr(A), _C.ptr(R),
+                _C.ptr(Gamma), _C.ptr(prio), _C.ptr(q_t), _C.ptr(q_tpn), self._stream())
+
     def _outputs(self, B, with_q):
         import torch
         key = (B, with_q)

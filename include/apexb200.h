@@ -122,6 +122,15 @@ int apexb200_replay_insert(apexb200_replay_t h, int32_t lane, int32_t count,
                            const float *prio, const float *q_t, const float *q_tpn,
                            int64_t *first_slot_host, void *stream);
 
+/* The same for `n_lanes` distinct lanes at once, `count` records each (E lock-stepped actors: one
+ * launch pair instead of E).  lanes_host [n_lanes] (host); every device input carries a leading
+ * lane dimension: frames [n_lanes, count*frames_per_record, frame_bytes], rel [n_lanes, count, 2C],
+ * A/R/Gamma/prio [n_lanes, count], q_t/q_tpn [n_lanes, count, num_actions]. */
+int apexb200_replay_insert_lanes(apexb200_replay_t h, const int32_t *lanes_host, int32_t n_lanes, int32_t count,
+                                 const uint8_t *frames, const int32_t *rel,
+                                 const int32_t *A, const float *R, const float *Gamma,
+                                 const float *prio, const float *q_t, const float *q_tpn, void *stream);
+
 /* ---- K1 build: ReplayMemory.update_sample_probabilities (replay.py:18-30) --
  * Recomputes every inner level from the leaves, level by level. */
 int apexb200_tree_build(apexb200_replay_t h, void *stream);

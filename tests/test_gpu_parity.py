@@ -783,6 +783,46 @@ def test_vector_actor_ingest_matches_sliding_buffer(apex):
     mem.check_status()
 
 
+@pytest.mark.parametrize("E,lane_cap,T,rounds", [(3, 64, 10, 9), (70, 32, 5, 4), (1, 128, 40, 5)])
+def test_insert_lanes_equals_per_lane_inserts(apex, E, lane_cap, T, rounds):
+    """apexb200_replay_insert_lanes (one launch pair for E lanes, 64 lanes per launch) == E single-lane inserts,
+    through several ring wrap-arounds, with given priorities and with priorities computed from stored Q rows."""
+    rng = np.random.default_rng(E * 1000 + T)
+    C_, F, nA, n = 2, 32, 3, 3
+    params = {"priority_exponent": 0.6, "layout": "stream", "lanes": E, "n_step": n, "state_shape": (C_, 1, F),
+              "num_actions": nA}
+    a, b = apex.ReplayMemory(E * lane_cap, params), apex.ReplayMemory(E * lane_cap, params)
+    lanes = list(rng.permutation(E))                                       # any order, each lane once
+    for r in range(rounds):
+        frames = rng.integers(0, 256, (E, T, F), dtype=np.uint8)
+        rel = np.stack([apex.stream_offsets(C_, np.full(T, n), np.arange(T) + r * T) for _ in range(E)])
+        A = rng.integers(0, nA, (E, T)).astype(np.int32)
+        R = rng.standard_normal((E, T)).astype(np.float32)
+        G = np.where(rng.random((E, T)) < 0.1, 0.0, 0.97).astype(np.float32)
+        q_t, q_tpn = (rng.standard_normal((E, T, nA)).astype(np.float32) for _ in range(2))
+        prio = None if r % 2 else (np.abs(rng.standard_normal((E, T))) + 1e-3).astype(np.float32)
+        a.insert_lanes(lanes, frames, rel, A, R, G, prio=prio, q_t=q_t, q_tpn=q_tpn)
+        for k, lane in enumerate(lanes):
+            b.insert(lane, frames[k], rel[k], A[k], R[k], G[k], prio=None if prio is None else prio[k], q_t=q_t[k], q_tpn=q_tpn[k])
+        assert a.size() == b.size() and a.total() == b.total()
+    written = min(rounds * T, lane_cap)
+    for which in (apex._C.BUF_FRAMES, apex._C.BUF_FIDX, apex._C.BUF_ACTION, apex._C.BUF_REWARD, apex._C.BUF_GAMMA,
+                  apex._C.BUF_QT, apex._C.BUF_QTPN):
+        x, y = (m_.buffer(which).view(E, lane_cap, -1)[:, :written] for m_ in (a, b))
+        assert torch.equal(x, y), which
+    assert torch.equal(a.buffer(apex._C.BUF_LEAVES), b.buffer(apex._C.BUF_LEAVES))
+    # the tree above the leaves is what a rebuild gives
+    top_a = a.total()
+    apex._C.call("apexb200_tree_build", a._h, apex._C.stream_ptr())
+    assert a.total() == top_a
+    with pytest.raises(apex._C.ApexError):
+        a.insert_lanes([0, 0][:min(2, E)] if E > 1 else [5], np.zeros((min(2, E), 1, F), np.uint8), np.zeros((min(2, E), 1, 2 * C_), np.int32),
+                       np.zeros((min(2, E), 1), np.int32), np.zeros((min(2, E), 1), np.float32), np.zeros((min(2, E), 1), np.float32),
+                       prio=np.ones((min(2, E), 1), np.float32))           # a lane listed twice / out of range
+    a.check_status()
+    b.check_status()
+
+
 def _ring_actor(name, slots, T, F, nA, chunks, seed):
     import sys
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
