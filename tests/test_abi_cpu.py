@@ -44,6 +44,22 @@ def test_argument_validation_without_a_gpu():
     cfg = _C.ReplayConfig(100, 3, 1, 0, 1, 7056, 0, 0.6, 0)
     assert lib.apexb200_replay_create(ctypes.byref(h), ctypes.byref(cfg)) == _C.EINVAL
     assert lib.apexb200_sample(None, None, 4, None, None, None, None, None) == _C.EINVAL
+    # entry points added for ingest, weight publication and the batched actor policy
+    assert lib.apexb200_replay_insert_lanes(None, None, 1, 1, None, None, None, None, None, None, None, None, None) == _C.EINVAL
+    p = ctypes.c_void_p()
+    assert lib.apexb200_params_create(0, None, 0, 0, ctypes.byref(p)) == _C.EINVAL and not p.value
+    span = (_C.ParamSpan * 1)()
+    span[0].tensor, span[0].flat_offset, span[0].bytes = 4096, 128, 64                   # offset not a multiple of 256
+    assert lib.apexb200_params_create(0, ctypes.cast(span, ctypes.c_void_p), 1, 4096, ctypes.byref(p)) == _C.EINVAL
+    assert b"256-byte aligned" in lib.apexb200_last_error()
+    span[0].flat_offset, span[0].bytes = 0, 8192                                         # beyond flat_bytes
+    assert lib.apexb200_params_create(0, ctypes.cast(span, ctypes.c_void_p), 1, 4096, ctypes.byref(p)) == _C.EINVAL
+    assert lib.apexb200_params_destroy(None) == 0
+    assert lib.apexb200_params_publish(None, None, None, 1, None) == _C.EINVAL
+    assert lib.apexb200_params_load(None, None, 0, None) == _C.EINVAL
+    assert lib.apexb200_actor_policy(None, None, None, None, None, 0, 0, 4, 4, None, None, None, None) == _C.EINVAL
+    assert lib.apexb200_host_register(None, 0) == _C.EINVAL and lib.apexb200_host_unregister(None) == _C.EINVAL
+    assert _C.HOST_STEP_SLOTS == 4
 
 
 def test_product_does_not_import_the_oracle():
