@@ -238,3 +238,27 @@ def test_actor_staging_ring_cross_process():
         assert got == chunks and p.exitcode == 0 and ring.pop() is None
     finally:
         ring.close(unlink=True)
+
+
+def test_header_is_plain_c(tmp_path):
+    """include/apexb200.h is the drop-in boundary: it must compile as C99 (cgo / JNI / any FFI generator) and
+    as C++, and a C program must link against the library with nothing but the header."""
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("gcc not available")
+    hdr = os.path.join(ROOT, "include", "apexb200.h")
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c", hdr])
+    subprocess.check_call(["g++", "-std=c++17", "-Wall", "-Werror", "-fsyntax-only", "-x", "c++", hdr])
+    src = tmp_path / "probe.c"
+    src.write_text('#include "apexb200.h"\n#include <stdio.h>\n'
+                   'int main(void) { int64_t n = 0; int rc = apexb200_td_workspace_bytes(4096, &n);\n'
+                   '  printf("%d %d %lld %s\\n", apexb200_version(), rc, (long long)n, apexb200_strerror(APEXB200_ERANGE));\n'
+                   '  return apexb200_sample(0, 0, 4, 0, 0, 0, 0, 0) == APEXB200_EINVAL ? 0 : 1; }\n')
+    import apex_b200
+    lib = apex_b200._C.LIB_PATH
+    exe = tmp_path / "probe"
+    subprocess.check_call(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe), lib,
+                           "-Wl,-rpath," + os.path.dirname(lib)])
+    out = subprocess.run([str(exe)], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 0 and out.stdout.split()[:3] == ["100", "0", "512"], (out.stdout, out.stderr)
