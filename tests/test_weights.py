@@ -454,3 +454,26 @@ def test_host_register_replaces_a_stale_registration():
         _C.host_unregister(addr + 4096)                  # not registered any more
     x = torch.ones(8, device="cuda")                     # the CUDA error state is clean
     assert float(x.sum()) == 8.0
+
+
+def test_policy_oracle_properties():
+    """Size-independent properties of the policy restatement: eps = 0 is always greedy, eps = 1 always explores,
+    the duelling combine is centred per row and invariant to what other rows hold (batch-1 semantics)."""
+    rng = np.random.default_rng(0)
+    for E, A in ((1, 2), (33, 4), (500, 18)):
+        value, adv = rng.standard_normal(E).astype(np.float32), rng.standard_normal((E, A)).astype(np.float32)
+        q = po.duelling_q_batch1(value, adv)
+        np.testing.assert_allclose((q - value[:, None]).mean(1), 0, atol=2e-6)
+        other = adv.copy()
+        other[1:] += 100.0                                           # other rows change: row 0 must not (Q19)
+        np.testing.assert_array_equal(po.duelling_q_batch1(value, other)[0], q[0])
+        ue, ua = rng.random(E), rng.random(E)
+        greedy, ex0 = po.epsilon_greedy(q, 0.0, ue, ua)
+        np.testing.assert_array_equal(greedy, q.argmax(1))
+        assert not ex0.any()
+        rnd, ex1 = po.epsilon_greedy(q, 1.0, ue, ua)
+        assert ex1.all() and (rnd == np.minimum((ua * A).astype(np.int64), A - 1)).all()
+        assert rnd.min() >= 0 and rnd.max() < A
+    u1, u2 = po.kernel_uniforms(7, 3, 1000)
+    assert 0 <= u1.min() and u1.max() < 1 and 0 <= u2.min() and u2.max() < 1 and abs(u1.mean() - 0.5) < 0.05
+    assert not np.array_equal(u1, u2) and not np.array_equal(u1, po.kernel_uniforms(7, 4, 1000)[0])
