@@ -224,40 +224,93 @@ __device__ __forceinline__ double strat_uniform(unsigned long long seed, unsigne
 // child and the remaining target are broadcast by shuffle; no shared memory.
 // The top-level load does not depend on the draw, so callers fetch it first
 // (top_level_value) and compute the draw while it is in flight.
-__device__ __forceinline__ unsigned long long top_level_value(const TreeView &tv) {
-    return tv.lvl[tv.n_levels - 1][threadIdx.x & 31];
+// When the level below the top has at most 64 entries (N in (32^k, 2*32^k]: 2M, 64k records ...) the top
+// level is nearly empty; its children are then fetched together with it (two values per lane) and the two
+// levels are searched as one 64-entry level: one dependent L2 round trip less per draw (0.33 us).  The flat
+// right-sided search over the 64 prefix sums selects exactly the entry the two-level search selects.
+struct TopValues {
+    unsigned long long top;        // lvl[top][lane]
+    unsigned long long a, b;       // merged mode: lvl[top-1][lane], lvl[top-1][lane + 32]
+};
+__device__ __forceinline__ bool top_is_merged(const TreeView &tv) {
+    return tv.n_levels >= 2 && tv.size[tv.n_levels - 2] <= 2 * kFanout;
+}
+__device__ __forceinline__ TopValues top_level_value(const TreeView &tv) {
+    const int lane = threadIdx.x & 31;
+    TopValues tvv;
+    tvv.top = tv.lvl[tv.n_levels - 1][lane];
+    tvv.a = tvv.b = 0ull;
+    if (top_is_merged(tv)) {                                   // padded to a multiple of 32: lane + 32 only if it exists
+        const unsigned long long *l2 = tv.lvl[tv.n_levels - 2];
+        tvv.a = l2[lane];
+        if (tv.size[tv.n_levels - 2] > kFanout) tvv.b = l2[lane + kFanout];
+    }
+    return tvv;
 }
 
-__device__ __forceinline__ long long warp_descend(const TreeView &tv, unsigned long long vtop, unsigned long long t,
+__device__ __forceinline__ unsigned long long warp_inclusive_scan(unsigned long long v, int lane) {
+    unsigned long long incl = v;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned long long n = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += n;
+    }
+    return incl;
+}
+
+__device__ __forceinline__ long long warp_descend(const TreeView &tv, const TopValues &vtop, unsigned long long t,
                                                   bool from_u, double u, unsigned long long *leaf,
                                                   unsigned long long *total, int32_t *status) {
     const int lane = threadIdx.x & 31;
     const int top = tv.n_levels - 1;
+    const bool merged = top_is_merged(tv);
     long long node = 0;
     unsigned long long lf = 0ull;
-    for (int l = top; l >= 0; --l) {
-        unsigned long long v = (l == top) ? vtop : tv.lvl[l][node * kFanout + lane];   // padded levels: in bounds
-        unsigned long long incl = v;
-        #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            unsigned long long n = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += n;
+    int first = top;                                           // first level the loop below has to visit
+    {
+        // total and target from the top level (or from its 64 children: the same sum)
+        const unsigned long long v1 = merged ? vtop.a : vtop.top;
+        const unsigned long long incl1 = warp_inclusive_scan(v1, lane);
+        const unsigned long long sum1 = __shfl_sync(0xffffffffu, incl1, 31);
+        unsigned long long incl2 = 0ull, tot = sum1;
+        if (merged) {
+            incl2 = sum1 + warp_inclusive_scan(vtop.b, lane);
+            tot = __shfl_sync(0xffffffffu, incl2, 31);
         }
-        if (l == top) {
-            unsigned long long tot = __shfl_sync(0xffffffffu, incl, 31);
-            *total = tot;
-            if (tot == 0ull) { if (lane == 0) atomicOr(status, APEXB200_ST_EMPTY_TREE); return -1; }
-            if (from_u) {
-                t = (unsigned long long)(u * (double)tot);              // one fp64 multiply, truncation
-                if (t >= tot) t = tot - 1ull;
-            } else if (t >= tot) {
-                if (lane == 0) atomicOr(status, APEXB200_ST_BAD_TARGET);
-                t = tot - 1ull;
-            }
+        *total = tot;
+        if (tot == 0ull) { if (lane == 0) atomicOr(status, APEXB200_ST_EMPTY_TREE); return -1; }
+        if (from_u) {
+            t = (unsigned long long)(u * (double)tot);              // one fp64 multiply, truncation
+            if (t >= tot) t = tot - 1ull;
+        } else if (t >= tot) {
+            if (lane == 0) atomicOr(status, APEXB200_ST_BAD_TARGET);
+            t = tot - 1ull;
         }
+        int c = __popc(__ballot_sync(0xffffffffu, incl1 <= t));
+        unsigned long long excl, val;
+        if (merged) {
+            c += __popc(__ballot_sync(0xffffffffu, incl2 <= t));
+            c = min(c, 2 * kFanout - 1);
+            const bool hi = c >= kFanout;
+            excl = __shfl_sync(0xffffffffu, hi ? incl2 - vtop.b : incl1 - v1, c & 31);
+            val = __shfl_sync(0xffffffffu, hi ? vtop.b : v1, c & 31);
+            first = top - 2;
+        } else {
+            c = min(c, 31);
+            excl = __shfl_sync(0xffffffffu, incl1 - v1, c);
+            val = __shfl_sync(0xffffffffu, v1, c);
+            first = top - 1;
+        }
+        if (first < 0) lf = val;                                   // the searched level was the leaf level
+        t -= excl;
+        node = c;
+    }
+    for (int l = first; l >= 0; --l) {
+        const unsigned long long v = tv.lvl[l][node * kFanout + lane];      // padded levels: in bounds
+        const unsigned long long incl = warp_inclusive_scan(v, lane);
         int c = __popc(__ballot_sync(0xffffffffu, incl <= t));
         c = min(c, 31);
-        unsigned long long excl = __shfl_sync(0xffffffffu, incl - v, c);
+        const unsigned long long excl = __shfl_sync(0xffffffffu, incl - v, c);
         if (l == 0) lf = __shfl_sync(0xffffffffu, v, c);
         t -= excl;
         node = node * kFanout + c;

@@ -234,7 +234,7 @@ __device__ __forceinline__ void sample_gather_body(const TreeView &tv, const Rin
     uint8_t *stage = smem + (size_t)wpc * 8 * kMaxChunks * 8 + (size_t)(wl * C + lane) * rv.F;
     unsigned long long *my_bars = bars + (wl * 8 + lane) * kMaxChunks;
     const bool strat = (sa.u == nullptr);
-    const unsigned long long vtop = top_level_value(tv);     // in flight while the draw is formed
+    const TopValues vtop = top_level_value(tv);     // in flight while the draw is formed
     double uw;
     if (strat) {
         uw = strat_uniform(sa.seed, read_epoch(ctrl), sa.call, w, count);
@@ -362,7 +362,7 @@ sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs
     const int unit = blockIdx.x + wl * gridDim.x;            // half rows dealt round-robin over the CTAs
     const int row = unit >> 1, half = unit & 1;
     const int C = rv.C, twoC = 2 * rv.C;
-    const unsigned long long vtop = top_level_value(tv);
+    const TopValues vtop = top_level_value(tv);
     const int world = pv.world, rank = pv.rank;
     // the shard totals of the current round (pushed by shard_exchange_kernel or by the peers'
     // td_small_kernel) -> global total T and this rank's prefix interval [lo, hi).  One warp per

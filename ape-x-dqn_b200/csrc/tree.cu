@@ -137,7 +137,7 @@ tree_sample_kernel(TreeView tv, const double *__restrict__ u, const unsigned lon
     unsigned long long leaf, total;
     const bool strat = (u == nullptr && targets == nullptr);
     const bool from_u = strat || (u != nullptr);
-    const unsigned long long vtop = top_level_value(tv);     // in flight while the draw is formed
+    const TopValues vtop = top_level_value(tv);     // in flight while the draw is formed
     double uw = 0.0;
     if (strat) {
         uw = strat_uniform(seed, read_epoch(ctrl), call, w, count);
