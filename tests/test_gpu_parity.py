@@ -236,9 +236,9 @@ def test_step_loop_in_cuda_graph_equals_eager(apex, pdl):
         apex._C.call("apexb200_set_pdl", 1)
 
 
-def test_sample_targets_and_device_count(apex):
+@pytest.mark.parametrize("N", [3000, 2048, 50000, 40])       # 2048 / 50000: the two top levels are searched as one
+def test_sample_targets_and_device_count(apex, N):
     rng = np.random.default_rng(9)
-    N = 3000
     leaves = rng.integers(1, 1 << 28, N, dtype=np.uint64)
     mem = make_mem(apex, N)
     load_leaves(apex, mem, leaves)
@@ -634,11 +634,12 @@ def test_shard_routing_equals_single_tree(apex):
     np.testing.assert_array_equal(got, whole)
 
 
-def test_peer_exchange_and_fused_sharded_sample_world1(apex):
+@pytest.mark.parametrize("N", [1 << 13, 1 << 11, 1 << 16])   # 2048 / 65536: merged top levels in the sharded kernel
+def test_peer_exchange_and_fused_sharded_sample_world1(apex, N):
     """The peer-memory exchange and the fused routing+search+gather kernel with a group of one
     (the multi-rank behaviour is checked by tests/multi_gpu_check.py under torchrun)."""
     rng = np.random.default_rng(15)
-    N, C_, F, B = 1 << 13, 2, 256, 300
+    C_, F, B = 2, 256, 300
     mem = make_mem(apex, N, C=C_, F=F, layout="stream", lanes=2, n=3)
     ring = ro.RingOracle(N, C_, F, lanes=2, fpr=1, lookback=C_ - 1 + 3, alpha=0.6)
     for lane in range(2):
