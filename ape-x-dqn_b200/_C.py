@@ -82,7 +82,9 @@ SIGNATURES = {
     "apexb200_shard_targets": [_P, _I32, _I32, _P, _I32, _P, _P, _P, _P],
     "apexb200_peer_export": [_P, _P],
     "apexb200_peer_connect": [_P, _I32, _I32, _P],
+    "apexb200_peer_connect_local": [_P, _I32, _I32, _P],
     "apexb200_shard_exchange": [_P, _P, _P],
+    "apexb200_shard_push": [_P, _P],
     "apexb200_peer_push_on_update": [_P, _I32],
     "apexb200_sample_gather_sharded": [_P, C.c_uint64, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "apexb200_params_create": [_I32, _P, _I32, C.c_uint64, C.POINTER(_P)],

@@ -136,7 +136,8 @@ __device__ __forceinline__ unsigned long long read_epoch(const int32_t *ctrl) {
     return *(const volatile unsigned long long *)(ctrl + 4);
 }
 __device__ __forceinline__ void bump_epoch(int32_t *ctrl) {        // one thread of a tree-changing kernel
-    if (blockIdx.x == 0 && threadIdx.x == 0) *(volatile unsigned long long *)(ctrl + 4) += 1ull;
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0)
+        *(volatile unsigned long long *)(ctrl + 4) += 1ull;
 }
 
 // The same for a full warp whose leaves are adjacent in index order (sorted batch rows, or the
@@ -154,14 +155,21 @@ __device__ __forceinline__ void warp_propagate_adjacent(const TreeView &tv, long
     for (int l = first_merged; l < tv.n_levels; ++l) {
         const long long key = i >= 0 ? (i >> (5 * l)) : (long long)(-1 - lane);
         unsigned long long sum = i >= 0 ? d : 0ull;
+        // Segmented inclusive scan with head flags: a segment is a run of neighbouring lanes with the same
+        // ancestor.  Accumulation stops at a segment head, so a key that reappears later in the warp (ring
+        // wrap inside the warp: A.. B.. A..) forms a second segment with its own atomic instead of pulling
+        // in the first run's sum (comparing keys at distance o would add it twice).
+        const long long kp = __shfl_up_sync(0xffffffffu, key, 1);
+        unsigned flag = (lane == 0 || kp != key) ? 1u : 0u;
+        const unsigned heads = __ballot_sync(0xffffffffu, flag != 0u);
         #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const long long ks = __shfl_up_sync(0xffffffffu, key, o);
             const unsigned long long vs = __shfl_up_sync(0xffffffffu, sum, o);
-            if (lane >= o && ks == key) sum += vs;
+            const unsigned fs = __shfl_up_sync(0xffffffffu, flag, o);
+            if (lane >= o && !flag) { sum += vs; flag |= fs; }
         }
-        const long long kn = __shfl_down_sync(0xffffffffu, key, 1);
-        if ((lane == 31 || kn != key) && sum != 0ull && key >= 0) atomicAdd(tv.lvl[l] + key, sum);
+        const bool tail = lane == 31 || ((heads >> (lane + 1)) & 1u);
+        if (tail && sum != 0ull && key >= 0) atomicAdd(tv.lvl[l] + key, sum);
     }
 }
 
@@ -354,4 +362,10 @@ int run_sample_gather(apexb200_replay *h, const double *u, uint64_t seed, int32_
                       int32_t *fsel_out, uint64_t *leaf_out, uint64_t *total_out, double *u_out, uint8_t *S_t,
                       uint8_t *S_tpn, int32_t *A, float *R, float *Gamma, float *q_t, float *q_tpn,
                       const unsigned *ready, unsigned ready_value, cudaStream_t stream);
+int sharded_wave_rows(const apexb200_replay *h, int global_count, int max_rows);
+int run_sample_gather_sharded(apexb200_replay *h, uint64_t seed, int32_t global_count, int32_t max_rows,
+                              int32_t *idx_out, int32_t *fsel_out, int32_t *pos_out, double *u_out,
+                              int32_t *count_out, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R, float *Gamma,
+                              float *q_t, float *q_tpn, const unsigned *ready, unsigned ready_value,
+                              cudaStream_t stream);
 }  // namespace apexb200

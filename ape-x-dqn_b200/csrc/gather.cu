@@ -113,12 +113,35 @@ __device__ __forceinline__ void tma_load_frame(const uint8_t *src, uint8_t *stag
     }
 }
 
+// The same in two steps for kernels that reuse a lane's staging buffer over several waves: the
+// mbarriers are initialised once, every wave arms them again (phase parity = wave & 1).
+__device__ __forceinline__ void tma_init_bars(unsigned long long *bars, int nch) {
+    for (int c = 0; c < nch; ++c) {
+        const unsigned bar_s = (unsigned)__cvta_generic_to_shared(bars + c);
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s));
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void tma_issue_frame(const uint8_t *src, uint8_t *stage, unsigned long long *bars,
+                                                unsigned bytes, int nch) {
+    const unsigned buf_s = (unsigned)__cvta_generic_to_shared(stage);
+    const unsigned chunk = bytes / nch;
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    for (int c = 0; c < nch; ++c) {
+        const unsigned bar_s = (unsigned)__cvta_generic_to_shared(bars + c);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(chunk) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                     ::"r"(buf_s + c * chunk), "l"(src + c * chunk), "r"(chunk), "r"(bar_s), "l"(pol) : "memory");
+    }
+}
+
 // Drain: every lane that moves a frame polls its own mbarriers without blocking and
 // issues the shared -> global copy of a chunk the moment that chunk has landed, so the
 // stores of early frames overlap the loads of late ones (a blocking wait would hold the
 // whole warp until its slowest frame arrived).  Must be called by all 32 lanes.
 __device__ __forceinline__ void tma_drain_frames(bool moving, uint8_t *dst, uint8_t *stage, unsigned long long *bars,
-                                                 unsigned bytes, int nch) {
+                                                 unsigned bytes, int nch, unsigned parity = 0u) {
     const unsigned buf_s = (unsigned)__cvta_generic_to_shared(stage);
     const unsigned chunk = bytes / nch;
     int next = moving ? 0 : nch;                     // next chunk this lane has to store
@@ -126,8 +149,8 @@ __device__ __forceinline__ void tma_drain_frames(bool moving, uint8_t *dst, uint
         if (next < nch) {
             const unsigned bar_s = (unsigned)__cvta_generic_to_shared(bars + next);
             unsigned done;
-            asm volatile("{\n .reg .pred p;\n mbarrier.test_wait.parity.shared::cta.b64 p, [%1], 0;\n"
-                         " selp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(bar_s) : "memory");
+            asm volatile("{\n .reg .pred p;\n mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+                         " selp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(bar_s), "r"(parity) : "memory");
             if (done) {
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
@@ -349,9 +372,16 @@ __device__ __forceinline__ int first_draw_at_or_above(unsigned long long bound, 
     return lo;
 }
 
-__global__ void __launch_bounds__(512)
-sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, ShardArgs sh, PeerView pv,
-                             int32_t *ctrl) {
+// Every draw the rank owns is delivered, whatever the split of priority mass between the shards
+// (replay.py:52-57: B requested, B returned): the grid covers `wave_rows` rows at a time — sized by the
+// launcher for the rank's expected share plus head-room — and a warp whose row is live goes on to row
+// + wave_rows, + 2 wave_rows, ... until it passes the end of the rank's run of draws.  Targets are
+// non-decreasing in the draw index, so the first dead row of a warp ends its loop.  The staging buffer
+// and mbarriers of a lane are reused from wave to wave (phase parity = wave & 1).
+template <bool kPolled>
+__device__ __forceinline__ void sample_gather_sharded_body(const TreeView &tv, const RingView &rv, const SampleArgs &sa,
+                                                           const GatherArgs &ga, const ShardArgs &sh, const PeerView &pv,
+                                                           int32_t *ctrl, const unsigned *ready, unsigned ready_value) {
     extern __shared__ __align__(128) uint8_t smem[];
     unsigned long long *bars = (unsigned long long *)smem;
     pdl_prologue();
@@ -359,8 +389,6 @@ sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs
     const int wl = threadIdx.x >> 5;
     const int wpc = blockDim.x >> 5;
     const int nch = frame_chunks(rv.F);
-    const int unit = blockIdx.x + wl * gridDim.x;            // half rows dealt round-robin over the CTAs
-    const int row = unit >> 1, half = unit & 1;
     const int C = rv.C, twoC = 2 * rv.C;
     const TopValues vtop = top_level_value(tv);
     const int world = pv.world, rank = pv.rank;
@@ -370,8 +398,18 @@ sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs
     __shared__ unsigned long long s_totals[kMaxShards];
     const unsigned long long round = read_round(ctrl);
     if (wl == 0 && lane < world) s_totals[lane] = peer_wait_round(pv, round, lane, ctrl);
+    if (kPolled && wl == 0 && lane == 0) {
+        // apexb200_host_step_sharded: the Q rows of the following TD kernel arrive by an H2D copy on another
+        // stream, followed by a stream-ordered write of `ready_value`; waiting for it here (the copy was issued
+        // a step or more ahead) keeps every cross-stream wait off the compute stream.
+        const volatile unsigned *flag = ready;
+        const long long t0 = clock64();
+        while ((int)(*flag - ready_value) < 0) {
+            if (clock64() - t0 > (5ll << 31)) { atomicOr(ctrl, APEXB200_ST_PEER_TIMEOUT); break; }   // ~5 s
+        }
+        __threadfence();
+    }
     __syncthreads();
-    if (row >= sh.max_rows) return;
     unsigned long long tg = lane < world ? s_totals[lane] : 0ull, incl = tg;
     #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -381,53 +419,76 @@ sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs
     const unsigned long long T = __shfl_sync(0xffffffffu, incl, 31);
     const unsigned long long hi = __shfl_sync(0xffffffffu, incl, rank);
     const unsigned long long lo = hi - __shfl_sync(0xffffffffu, tg, rank);
+    const int unit0 = blockIdx.x + wl * gridDim.x;           // half rows dealt round-robin over the CTAs
     if (T == 0ull) {
-        if (lane == 0) { atomicOr(ctrl, APEXB200_ST_EMPTY_TREE); if (unit == 0) *sh.count_out = 0; }
+        if (lane == 0) { atomicOr(ctrl, APEXB200_ST_EMPTY_TREE); if (unit0 == 0) *sh.count_out = 0; }
         return;
     }
     const int Bg = sh.global_count;
     const int j_lo = first_draw_at_or_above(lo, sa.seed, round, sh.call, Bg, T);
-    const int j = j_lo + row;
-    double uw = 0.0;
-    const unsigned long long t = j < Bg ? draw_target(sa.seed, round, sh.call, j, Bg, T, &uw) : hi;
-    if (t >= hi) {                                           // beyond this rank's run of draws
-        if (unit == 0 && lane == 0) *sh.count_out = 0;       // (unit 0 dead: the rank owns no draw)
-        return;
-    }
-    unsigned long long leaf, total;
-    const long long node = warp_descend(tv, vtop, t - lo, false, 0.0, &leaf, &total, ctrl);
     uint8_t *stage = smem + (size_t)wpc * 8 * kMaxChunks * 8 + (size_t)(wl * C + lane) * rv.F;
     unsigned long long *my_bars = bars + (wl * 8 + lane) * kMaxChunks;
-    const int k = half * C + lane;
-    long long f = -1;
-    if (node >= 0 && lane < C) f = rv.fidx[node * twoC + k];
-    bool moving = false;
-    if (node >= 0 && lane < C) {
-        if (f < 0 || f >= rv.N * rv.fpr) atomicOr(ctrl, APEXB200_ST_BAD_INDEX);
-        else { moving = true; tma_load_frame(rv.frames + f * rv.F, stage, my_bars, (unsigned)rv.F, nch); }
-    }
-    if (lane < C && sa.fsel_out) sa.fsel_out[(long long)row * twoC + k] = (int32_t)f;
-    if (half == 0) {
-        if (lane == 0) {
-            sa.idx_out[row] = (int32_t)node;
-            if (sh.pos_out) sh.pos_out[row] = j;
-            if (sa.u_out) sa.u_out[row] = uw;
+    if (lane < C) tma_init_bars(my_bars, nch);
+    const int wave_units = gridDim.x * wpc;
+    unsigned wave = 0u;
+    for (int unit = unit0;; unit += wave_units, ++wave) {
+        const int row = unit >> 1, half = unit & 1;
+        const int j = j_lo + row;
+        double uw = 0.0;
+        const unsigned long long t = (row < sh.max_rows && j < Bg) ? draw_target(sa.seed, round, sh.call, j, Bg, T, &uw) : hi;
+        if (t >= hi) {                                       // beyond this rank's run of draws (or the caller's rows)
+            if (unit == 0 && lane == 0) *sh.count_out = 0;   // (unit 0 dead: the rank owns no draw)
+            break;
         }
-        if (node >= 0 && lane == 16) copy_meta_row(rv, ga, row, node);
+        unsigned long long leaf, total;
+        const long long node = warp_descend(tv, vtop, t - lo, false, 0.0, &leaf, &total, ctrl);
+        const int k = half * C + lane;
+        long long f = -1;
+        if (node >= 0 && lane < C) f = rv.fidx[node * twoC + k];
+        bool moving = false;
+        if (node >= 0 && lane < C) {
+            if (f < 0 || f >= rv.N * rv.fpr) atomicOr(ctrl, APEXB200_ST_BAD_INDEX);
+            else { moving = true; tma_issue_frame(rv.frames + f * rv.F, stage, my_bars, (unsigned)rv.F, nch); }
+        }
+        if (lane < C && sa.fsel_out) sa.fsel_out[(long long)row * twoC + k] = (int32_t)f;
+        if (half == 0) {
+            if (lane == 0) {
+                sa.idx_out[row] = (int32_t)node;
+                if (sh.pos_out) sh.pos_out[row] = j;
+                if (sa.u_out) sa.u_out[row] = uw;
+            }
+            if (node >= 0 && lane == 16) copy_meta_row(rv, ga, row, node);
+        }
+        if (unit == 0) {                                     // row count, computed in the shadow of the frame loads
+            const int j_hi = first_draw_at_or_above(hi, sa.seed, round, sh.call, Bg, T);
+            int cnt = j_hi - j_lo;
+            // only a caller that passed fewer rows than the global batch can lose draws
+            if (cnt > sh.max_rows) { cnt = sh.max_rows; if (lane == 0) atomicOr(ctrl, APEXB200_ST_QUOTA); }
+            if (lane == 0) *sh.count_out = cnt;
+        }
+        tma_drain_frames(moving, moving ? item_dst(rv, ga, row, k) : nullptr, stage, my_bars, (unsigned)rv.F, nch,
+                         wave & 1u);
     }
-    if (unit == 0) {                                         // row count, computed in the shadow of the frame loads
-        const int j_hi = first_draw_at_or_above(hi, sa.seed, round, sh.call, Bg, T);
-        int cnt = j_hi - j_lo;
-        if (cnt > sh.max_rows) { cnt = sh.max_rows; if (lane == 0) atomicOr(ctrl, APEXB200_ST_QUOTA); }
-        if (lane == 0) *sh.count_out = cnt;
-    }
-    tma_drain_frames(moving, moving ? item_dst(rv, ga, row, k) : nullptr, stage, my_bars, (unsigned)rv.F, nch);
+}
+
+__global__ void __launch_bounds__(512)
+sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, ShardArgs sh, PeerView pv,
+                             int32_t *ctrl) {
+    sample_gather_sharded_body<false>(tv, rv, sa, ga, sh, pv, ctrl, nullptr, 0u);
+}
+
+// Same kernel for the host-facing sharded step: also waits for the arrival word of the step's Q rows.
+__global__ void __launch_bounds__(512)
+sample_gather_sharded_polled_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, ShardArgs sh, PeerView pv,
+                                    int32_t *ctrl, const unsigned *ready, unsigned ready_value) {
+    sample_gather_sharded_body<true>(tv, rv, sa, ga, sh, pv, ctrl, ready, ready_value);
 }
 
 static int ensure_smem(const void *fn, size_t smem, int device) {
-    static size_t configured[4][64] = {};
+    static size_t configured[5][64] = {};
     const int which = (fn == (const void *)gather_tma_kernel) ? 0 : (fn == (const void *)sample_gather_kernel) ? 1
-                    : (fn == (const void *)sample_gather_polled_kernel) ? 3 : 2;
+                    : (fn == (const void *)sample_gather_polled_kernel) ? 3
+                    : (fn == (const void *)sample_gather_sharded_polled_kernel) ? 4 : 2;
     if (smem > 48 * 1024 && device >= 0 && device < 64 && smem > configured[which][device]) {
         APEX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[which][device] = smem;
@@ -543,14 +604,23 @@ int run_sample_gather(apexb200_replay *h, const double *u, uint64_t seed, int32_
     return launch_step("sample_gather_kernel", sample_gather_kernel, dim3((unsigned)((units + wpc - 1) / wpc)),
                        dim3(wpc * 32), smem, st, h->tree, rv, sa, ga, h->status);
 }
-}  // namespace apexb200
 
-extern "C" {
+// Rows one wave of the sharded kernel covers: the rank's fair share of the global batch plus ~15 % head-room,
+// as whole rounds of the (kNumSMs - 1)-CTA grid.  A rank that owns more draws runs further waves in the
+// same launch; max_rows only bounds what the caller's output arrays can hold.
+int sharded_wave_rows(const apexb200_replay *h, int global_count, int max_rows) {
+    const int world = h->peers.world > 0 ? h->peers.world : 1;
+    long long share = ((long long)global_count + world - 1) / world;
+    share += (share + 7) / 8 + 2;
+    if (share > max_rows) share = max_rows;
+    return (int)share;
+}
 
-int apexb200_sample_gather_sharded(apexb200_replay_t h, uint64_t seed, int32_t global_count, int32_t max_rows,
-                                   int32_t *idx_out, int32_t *fsel_out, int32_t *pos_out, double *u_out,
-                                   int32_t *count_out, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R,
-                                   float *Gamma, float *q_t, float *q_tpn, void *stream) {
+int run_sample_gather_sharded(apexb200_replay *h, uint64_t seed, int32_t global_count, int32_t max_rows,
+                              int32_t *idx_out, int32_t *fsel_out, int32_t *pos_out, double *u_out,
+                              int32_t *count_out, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R, float *Gamma,
+                              float *q_t, float *q_tpn, const unsigned *ready, unsigned ready_value,
+                              cudaStream_t stream) {
     APEX_REQUIRE(h && global_count > 0 && max_rows > 0, APEXB200_EINVAL, "sample_gather_sharded: bad argument");
     APEX_REQUIRE(idx_out && count_out && S_t && S_tpn, APEXB200_EINVAL, "sample_gather_sharded: null output");
     APEX_REQUIRE((((uintptr_t)S_t | (uintptr_t)S_tpn) & 15) == 0, APEXB200_EINVAL,
@@ -559,20 +629,40 @@ int apexb200_sample_gather_sharded(apexb200_replay_t h, uint64_t seed, int32_t g
     const size_t per_unit = (size_t)rv.C * rv.F + 8 * kMaxChunks * 8;       // one half row: C frames + their mbarriers
     APEX_REQUIRE(rv.C <= 8 && per_unit <= kStageBudget, APEXB200_ERANGE,
                  "sample_gather_sharded: half a record (%d frames of %d bytes) does not fit one CTA's staging", rv.C, rv.F);
-    const int units = 2 * max_rows;
-    int wpc = (int)(kStageBudget / per_unit);
+    const int units = 2 * sharded_wave_rows(h, global_count, max_rows);
+    // one resident wave over kNumSMs - 1 CTAs (one SM stays free, as in sample_gather); half rows are dealt
+    // round-robin, so the live ones spread evenly whatever the wave size; further rows = further waves
+    const int ctas = units < kNumSMs - 1 ? units : kNumSMs - 1;
+    int wpc = (units + ctas - 1) / ctas;
+    const int fit = (int)(kStageBudget / per_unit);
+    if (wpc > fit) wpc = fit;
     if (wpc > 16) wpc = 16;
-    const int spread = (units + kNumSMs - 2) / (kNumSMs - 1);             // leave one SM free, as in sample_gather
-    if (spread < wpc) wpc = spread;
-    const int ctas = (units + wpc - 1) / wpc;
     const size_t smem = (size_t)wpc * per_unit;
-    int rc = ensure_smem((const void *)sample_gather_sharded_kernel, smem, h->cfg.device);
-    if (rc) return rc;
     SampleArgs sa{nullptr, (unsigned long long)seed, 0ull, idx_out, fsel_out, nullptr, nullptr, u_out};
     GatherArgs ga{idx_out, fsel_out, nullptr, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, max_rows};
     ShardArgs sh{(unsigned long long)seed, h->draw_calls++, global_count, max_rows, pos_out, count_out};
+    if (ready) {
+        int rc = ensure_smem((const void *)sample_gather_sharded_polled_kernel, smem, h->cfg.device);
+        if (rc) return rc;
+        return launch_step("sample_gather_sharded_polled_kernel", sample_gather_sharded_polled_kernel, dim3((unsigned)ctas),
+                           dim3(wpc * 32), smem, stream, h->tree, rv, sa, ga, sh, h->peers, h->status, ready, ready_value);
+    }
+    int rc = ensure_smem((const void *)sample_gather_sharded_kernel, smem, h->cfg.device);
+    if (rc) return rc;
     return launch_step("sample_gather_sharded_kernel", sample_gather_sharded_kernel, dim3((unsigned)ctas), dim3(wpc * 32),
-                       smem, (cudaStream_t)stream, h->tree, rv, sa, ga, sh, h->peers, h->status);
+                       smem, stream, h->tree, rv, sa, ga, sh, h->peers, h->status);
+}
+}  // namespace apexb200
+
+extern "C" {
+
+int apexb200_sample_gather_sharded(apexb200_replay_t h, uint64_t seed, int32_t global_count, int32_t max_rows,
+                                   int32_t *idx_out, int32_t *fsel_out, int32_t *pos_out, double *u_out,
+                                   int32_t *count_out, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R,
+                                   float *Gamma, float *q_t, float *q_tpn, void *stream) {
+    return apexb200::run_sample_gather_sharded(h, seed, global_count, max_rows, idx_out, fsel_out, pos_out, u_out,
+                                               count_out, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, nullptr, 0u,
+                                               (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -393,6 +393,35 @@ int apexb200_peer_connect(apexb200_replay_t h, int32_t rank, int32_t world, cons
     return APEXB200_OK;
 }
 
+int apexb200_peer_connect_local(apexb200_replay_t h, int32_t rank, int32_t world, const apexb200_replay_t *shards_host) {
+    APEX_REQUIRE(h && shards_host, APEXB200_EINVAL, "peer_connect_local: null argument");
+    APEX_REQUIRE(world >= 1 && world <= kMaxShards && rank >= 0 && rank < world, APEXB200_ERANGE,
+                 "peer_connect_local: rank %d / world %d outside [1, %d]", rank, world, kMaxShards);
+    APEX_REQUIRE(shards_host[rank] == h, APEXB200_EINVAL, "peer_connect_local: shards[rank] must be the handle itself");
+    APEX_CUDA(cudaSetDevice(h->cfg.device));
+    for (void *&m : h->opened) if (m) { cudaIpcCloseMemHandle(m); m = nullptr; }
+    PeerView pv;
+    memset(&pv, 0, sizeof(pv));
+    pv.world = world;
+    pv.rank = rank;
+    for (int g = 0; g < world; ++g) {
+        const apexb200_replay *peer = shards_host[g];
+        APEX_REQUIRE(peer, APEXB200_EINVAL, "peer_connect_local: null shard %d", g);
+        if (peer->cfg.device != h->cfg.device) {             // another GPU of this process: direct peer access
+            int can = 0;
+            APEX_CUDA(cudaDeviceCanAccessPeer(&can, h->cfg.device, peer->cfg.device));
+            APEX_REQUIRE(can, APEXB200_EINVAL, "peer_connect_local: device %d cannot access device %d", h->cfg.device,
+                         peer->cfg.device);
+            cudaError_t e = cudaDeviceEnablePeerAccess(peer->cfg.device, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceEnablePeerAccess");
+        }
+        pv.xbuf[g] = peer->xbuf;
+    }
+    h->peers = pv;
+    return APEXB200_OK;
+}
+
 }  // extern "C"
 
 namespace apexb200 {

@@ -90,87 +90,99 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
     __shared__ unsigned long long delta_part[32];
     pdl_prologue();
     if (idx != nullptr) bump_epoch(status);
-    const int b = threadIdx.x;
     const int live = live_rows(a);
-    // multi-GPU push (see the tail of this kernel): the shard total before this update, read by
-    // warp 0 while the batch rows are being fetched
+    // multi-GPU push (see below): the shard total before this update, read by warp 0 while the batch
+    // rows are being fetched
     unsigned long long total_before = 0ull, cur_round = 0ull, peer_word = 0ull;
     if (push && threadIdx.x < 32) {
         const int top = tv.n_levels - 1;
         total_before = threadIdx.x < tv.size[top] ? tv.lvl[top][threadIdx.x] : 0ull;
         // the peers' words of the current round (normally consumed by the preceding sample already):
-        // fetched now so that the push at the tail does not wait for this read
+        // fetched now so that the push does not wait for this read
         cur_round = read_round(status);
         if (threadIdx.x < pv.world && cur_round > 0ull)
             peer_word = *(volatile unsigned long long *)(pv.xbuf[pv.rank] +
                                                          (size_t)((int)(cur_round & 1ull) * kMaxShards + threadIdx.x));
     }
-    float l = 0.0f;
-    long long i = -1;
-    bool in_order = true, last_of_run = true;
-    unsigned long long old = 0ull;
-    if (b < live) {
-        if (idx != nullptr) {
-            i = idx[b];
-            const long long nxt = (b + 1 < live) ? (long long)idx[b + 1] : (1ll << 40);
-            in_order = i <= nxt;
-            last_of_run = i != nxt;
-            if (i < 0 || i >= tv.size[0]) { atomicOr(status, APEXB200_ST_BAD_INDEX); i = -1; }
-            else old = tv.lvl[0][i];
-        }
-        td_one(a, b, &l);
-    }
-    const int sorted = __syncthreads_and(in_order);
-    bool winner = (i >= 0) && last_of_run;
-    if (!sorted) {
-        if (i >= 0) atomicMax(stamp + i, (uint32_t)b + 1u);
-        __syncthreads();
-        winner = false;
-        if (i >= 0 && __ldcg(stamp + i) == (uint32_t)b + 1u) { winner = true; stamp[i] = 0u; }
-    }
-    unsigned long long d = 0ull;
-    if (winner) {
-        unsigned long long nl = leaf_from_prio(a.prio[b]);
-        tv.lvl[0][i] = nl;
-        d = nl - old;
-    }
-    if (push) {
-        // Fused collective (multi-GPU): publish this shard's new total to every peer from the
-        // kernel that produced it — the next step's sharded sample on each rank waits for these
-        // words instead of an all-gather.  new total = total before + sum of this batch's leaf
-        // deltas (exact in u64 arithmetic; this CTA is the only writer of the tree while it runs).
-        // It is sent BEFORE the ancestor updates and the loss reduction below, so that the NVLink
-        // flight overlaps them; peers only route draws with it, this shard's own tree is complete
-        // when the kernel ends.
-        unsigned long long ds = d;
-        #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) ds += __shfl_xor_sync(0xffffffffu, ds, o);
-        if ((threadIdx.x & 31) == 0) delta_part[threadIdx.x >> 5] = ds;
-        __syncthreads();
-        if (threadIdx.x < 32) {
-            const int lane = threadIdx.x;
-            unsigned long long v = total_before;
-            #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            const int nw = (blockDim.x + 31) >> 5;
-            for (int k = 0; k < nw; ++k) v += delta_part[k];
-            const unsigned long long cur = cur_round;
-            if (lane < pv.world) {
-                if (cur > 0ull && (peer_word & 15ull) != (cur & 15ull))
-                    peer_wait_round(pv, cur, lane, status);             // not there at kernel start: wait now
-                peer_push_round(pv, cur + 1ull, lane, v);
+    // One row per thread; a batch with more live rows than threads (a sharded batch whose rank owns far more
+    // than its fair share of the draws) takes further passes, `passes` is uniform over the CTA.  Each pass is
+    // complete in itself (vote, leaf writes, ancestor updates), passes run in batch order, so "last row wins"
+    // holds across them as well.
+    const int passes = live > (int)blockDim.x ? (live + (int)blockDim.x - 1) / (int)blockDim.x : 1;
+    float l_acc = 0.0f;
+    unsigned long long d_acc = 0ull;
+    for (int pass = 0; pass < passes; ++pass) {
+        const int b = pass * (int)blockDim.x + (int)threadIdx.x;
+        float l = 0.0f;
+        long long i = -1;
+        bool in_order = true, last_of_run = true;
+        unsigned long long old = 0ull;
+        if (b < live) {
+            if (idx != nullptr) {
+                i = idx[b];
+                const long long nxt = (b + 1 < live) ? (long long)idx[b + 1] : (1ll << 40);
+                in_order = i <= nxt;
+                last_of_run = i != nxt;
+                if (i < 0 || i >= tv.size[0]) { atomicOr(status, APEXB200_ST_BAD_INDEX); i = -1; }
+                else old = tv.lvl[0][i];
             }
-            __syncwarp();
-            if (lane == 0) *(volatile unsigned long long *)(status + 6) = cur + 1ull;
+            td_one(a, b, &l);
         }
+        l_acc += l;
+        const int sorted = __syncthreads_and(in_order);
+        bool winner = (i >= 0) && last_of_run;
+        if (!sorted) {
+            if (i >= 0) atomicMax(stamp + i, (uint32_t)b + 1u);
+            __syncthreads();
+            winner = false;
+            if (i >= 0 && __ldcg(stamp + i) == (uint32_t)b + 1u) { winner = true; stamp[i] = 0u; }
+        }
+        unsigned long long d = 0ull;
+        if (winner) {
+            unsigned long long nl = leaf_from_prio(a.prio[b]);
+            tv.lvl[0][i] = nl;
+            d = nl - old;
+        }
+        d_acc += d;
+        if (push && pass == passes - 1) {
+            // Fused collective (multi-GPU): publish this shard's new total to every peer from the
+            // kernel that produced it — the next step's sharded sample on each rank waits for these
+            // words instead of an all-gather.  new total = total before + sum of this batch's leaf
+            // deltas (exact in u64 arithmetic; this CTA is the only writer of the tree while it runs).
+            // It is sent BEFORE the (last pass's) ancestor updates and the loss reduction below, so that
+            // the NVLink flight overlaps them; peers only route draws with it, this shard's own tree is
+            // complete when the kernel ends.
+            unsigned long long ds = d_acc;
+            #pragma unroll
+            for (int o = 16; o > 0; o >>= 1) ds += __shfl_xor_sync(0xffffffffu, ds, o);
+            if ((threadIdx.x & 31) == 0) delta_part[threadIdx.x >> 5] = ds;
+            __syncthreads();
+            if (threadIdx.x < 32) {
+                const int lane = threadIdx.x;
+                unsigned long long v = total_before;
+                #pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                const int nw = (blockDim.x + 31) >> 5;
+                for (int k = 0; k < nw; ++k) v += delta_part[k];
+                const unsigned long long cur = cur_round;
+                if (lane < pv.world) {
+                    if (cur > 0ull && (peer_word & 15ull) != (cur & 15ull))
+                        peer_wait_round(pv, cur, lane, status);             // not there at kernel start: wait now
+                    peer_push_round(pv, cur + 1ull, lane, v);
+                }
+                __syncwarp();
+                if (lane == 0) *(volatile unsigned long long *)(status + 6) = cur + 1ull;
+            }
+        }
+        if (!sorted) {
+            if (d != 0ull) propagate_delta(tv, i, d);
+        } else if (idx != nullptr) {
+            // Sorted record indices (stratified draws): one atomic per distinct ancestor per warp
+            warp_propagate_adjacent(tv, i, d);
+        }
+        if (pass + 1 < passes) __syncthreads();                // the next pass reads leaves this one wrote
     }
-    if (!sorted) {
-        if (d != 0ull) propagate_delta(tv, i, d);
-    } else if (idx != nullptr) {
-        // Sorted record indices (stratified draws): one atomic per distinct ancestor per warp
-        warp_propagate_adjacent(tv, i, d);
-    }
-    float s = block_sum_fixed(l, warp_part);
+    float s = block_sum_fixed(l_acc, warp_part);
     if (threadIdx.x == 0) *a.loss_mean = s / mean_div(a);
 }
 
@@ -373,7 +385,9 @@ td_bwd_kernel(const float *__restrict__ delta, const int32_t *__restrict__ A, co
     int b = (int)(e / nA), k = (int)(e - (long long)b * nA);
     const int live = count_dev ? min(B, *count_dev) : B;
     float g = 0.0f;
-    if (b < live && k == A[b]) {
+    int act = b < live ? A[b] : -1;
+    if (b < live) act = act < 0 ? 0 : (act >= nA ? nA - 1 : act);      // same clamp as the forward (td_one)
+    if (b < live && k == act) {
         float d = delta[b];
         if (loss_kind == APEXB200_LOSS_HUBER) d = fminf(fmaxf(d, -kappa), kappa);
         g = -d * (*grad_out) / (divisor > 0.0f ? divisor : (float)B);   // d(mean loss)/dQ(S_t)[b, A_b]
@@ -468,9 +482,19 @@ static int td_launch(apexb200_replay *h, const int32_t *idx, const TdArgs &a, vo
                                    h ? h->status : (int32_t *)nullptr, h ? h->peers : pv_none,
                                    (h && idx && h->push_on_update) ? 1 : 0);
     }
-    if (a.B <= 1024) {
+    // Sharded batches: the arrays hold up to a.B rows (the whole global batch, so that no draw is ever
+    // dropped) but the live count is on the device and is normally the rank's fair share, divisor / world.
+    // The single-CTA kernel is sized for that share and takes extra passes when the rank owns more.
+    int small_threads = a.B <= 1024 ? ((a.B + 31) / 32) * 32 : 0;
+    if (a.count_dev && h && a.divisor > 0.0f) {
+        const int world = h->peers.world > 0 ? h->peers.world : 1;
+        long long share = ((long long)a.divisor + world - 1) / world;
+        share += (share + 7) / 8 + 2;
+        if (share < a.B && share <= 1024) small_threads = (int)((share + 31) / 32) * 32;
+    }
+    if (small_threads > 0) {
         PeerView pv_none{};
-        return launch_step("td_small_kernel", td_small_kernel, dim3(1), dim3(((a.B + 31) / 32) * 32), 0, st, a,
+        return launch_step("td_small_kernel", td_small_kernel, dim3(1), dim3(small_threads), 0, st, a,
                            h ? h->tree : tv_none, idx, h ? h->stamp : (uint32_t *)nullptr,
                            h ? h->status : (int32_t *)nullptr, h ? h->peers : pv_none,
                            (h && idx && h->push_on_update) ? 1 : 0);

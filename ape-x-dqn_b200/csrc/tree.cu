@@ -388,6 +388,11 @@ int apexb200_shard_exchange(apexb200_replay_t h, uint64_t *totals_out, void *str
                        h->peers, h->status, (unsigned long long *)totals_out);
 }
 
+int apexb200_shard_push(apexb200_replay_t h, void *stream) {
+    APEX_REQUIRE(h, APEXB200_EINVAL, "shard_push: null handle");
+    return run_peer_push(h, (cudaStream_t)stream);
+}
+
 int apexb200_peer_push_on_update(apexb200_replay_t h, int32_t enabled) {
     APEX_REQUIRE(h, APEXB200_EINVAL, "peer_push_on_update: null handle");
     h->push_on_update = enabled ? 1 : 0;

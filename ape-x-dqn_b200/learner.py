@@ -163,6 +163,9 @@ class Learner(object):
         """Capture one fast-tier learner step — K3+K4, the three forwards, backward, RMSprop, K5+K2 — in a
         CUDA graph.  Returns nothing; step_graphed() replays it.  The sampling kernel draws
         fresh stratified numbers on every replay (device-side epoch), the target-network sync stays outside.
+        Capturing is not free of side effects: the three warm-up passes before the capture are REAL learner
+        steps (weights, priorities and num_q_updates advance, the target network is synchronised when one of
+        them falls on q_target_sync_freq), exactly as three step_fast() calls would be.
         Losses returned by earlier compute_loss_and_priorities calls must have been released: a live
         autograd graph pins gradient-accumulation nodes to the stream they were created on."""
         dev = self._to_device()
@@ -180,6 +183,7 @@ class Learner(object):
                 loss.backward()
                 self.optimizer.step()
                 self.num_q_updates += 1
+                self._maybe_sync_target()
                 del loss
             side.synchronize()
             self._graph = torch.cuda.CUDAGraph()
@@ -273,7 +277,16 @@ class ShardedLearner(Learner):
     the networks; per step it takes its share of the global stratified batch (fused K8+K3+K4 over
     peer memory), runs the unchanged model on it, all-reduces the flat gradient (NCCL) and applies
     the identical RMSprop step; K5+K2 write the new priorities into the local shard and push the
-    shard's new total to the peers.  loss_mean is divided by the global batch on every rank."""
+    shard's new total to the peers.  loss_mean is divided by the global batch on every rank.
+
+    The rank's share is data dependent (proportional to its shard's priority mass) and is delivered in
+    full whatever the skew: the sample outputs hold the whole global batch, and the model runs on exactly
+    the rows the rank owns (one 4-byte device->host read of the row count per step; no stale rows ever
+    enter the network, so the reference model's batch-coupled duelling mean, duelling_network.py:27,
+    couples only live rows).  That coupling is per rank: a sharded step cannot reproduce the mean over the
+    GLOBAL batch that a single process would subtract; with a per-row mean
+    (qnet.DuellingQNet(batch_coupled_mean=False)) the all-reduced gradient equals the single-process
+    gradient exactly, which is what tests/multi_gpu_check.py asserts."""
 
     def __init__(self, env_conf, learner_params, shared_state, shared_replay_memory, group=None, quota=None):
         super().__init__(env_conf, learner_params, shared_state, shared_replay_memory)
@@ -285,9 +298,10 @@ class ShardedLearner(Learner):
         self.sampler = ShardedSampler(shared_replay_memory, group=group, rank=self.rank, world_size=self.world)
         B = int(self.params["replay_sample_size"])
         self.global_batch = B * self.world
-        # rows this rank may own in one step: its fair share plus slack for uneven shard totals
-        # (a multiple of 147, the CTAs the fused kernel spreads a B=512 share over: 588 rows there)
-        self.max_rows = int(quota) if quota else (-(-int(B * 1.14) // 147) * 147 if B >= 256 else int(B * 1.5) + 8)
+        # rows the sample outputs hold: the whole global batch (one rank may own every draw).  `quota` caps it
+        # for callers that want bounded buffers; a rank that then owns more raises ST_QUOTA in check_status().
+        self.max_rows = int(quota) if quota else self.global_batch
+        self.last_rows = 0
         self._ready = False
 
     def setup(self):
@@ -321,10 +335,14 @@ class ShardedLearner(Learner):
         if not self._ready:
             self.setup()
         batch, _pos, cnt = self.sampler.sample_fused(self.global_batch, self.max_rows)
-        shape = (self.max_rows,) + tuple(self.state_shape)
-        S_t, S_tpn = batch.S_t.view(shape).float(), batch.S_tpn.view(shape).float()
-        loss, _delta, _prio, _ = self._loss_from_tensors(S_t, S_tpn, batch.A, batch.R, batch.Gamma, replay=self.replay_memory,
-                                                         idx=batch.idx, count_dev=cnt, mean_divisor=float(self.global_batch))
+        n = int(cnt.item())                                   # this step's live rows (synchronises on the sample)
+        self.last_rows = n
+        rows = max(n, 1)                                      # a rank that owns no draw still takes part in the collectives
+        shape = (rows,) + tuple(self.state_shape)
+        S_t, S_tpn = batch.S_t[:rows].view(shape).float(), batch.S_tpn[:rows].view(shape).float()
+        loss, _delta, _prio, _ = self._loss_from_tensors(S_t, S_tpn, batch.A[:rows], batch.R[:rows], batch.Gamma[:rows],
+                                                         replay=self.replay_memory, idx=batch.idx[:rows], count_dev=cnt,
+                                                         mean_divisor=float(self.global_batch))
         self.grads.zero()
         loss.backward()
         self.grads.all_reduce(self.group)

@@ -1,11 +1,20 @@
-"""Multi-GPU replay: one shard per rank, quotas from an all-gather of shard totals.
+"""Multi-GPU replay: one shard per rank, every rank samples its share of one global batch.
 
-No counterpart in the reference (single process).  Design from SURVEY §8(e): every
-rank owns a replay shard; per step the ranks all-gather their tree totals (8 bytes
-each, NCCL over NVLink), derive the same global integer targets from the same
-uniform draws, and each rank descends its own tree for the targets that fall into
-its prefix interval.  With exact u64 totals this returns precisely the records a
-single tree over the concatenated shards would return.
+No counterpart in the reference (single process).  Design from SURVEY §8(e): every rank owns a
+replay shard; the only coupling is the global normaliser, the sum of the shard totals.  With exact
+u64 totals, identical global draws on every rank and each rank descending its own tree for the
+targets that fall into its prefix interval, the union of the ranks' rows is precisely what a single
+tree over the concatenated shards would return.
+
+Default path (peer memory, no NCCL on the step): the shard totals travel as 8-byte words written
+straight into the peers' exchange buffers over NVLink — by `exchange()` (one launch) or, with
+`push_on_update()`, by the TD/priority-update kernel itself — and `sample_fused()` is ONE kernel
+that waits for the words, finds the rank's run of the in-kernel stratified draws, searches and
+gathers.  A rank receives every draw it owns whatever the split of priority mass (outputs are sized
+for the whole global batch; the kernel runs extra waves for an over-sized share).
+
+Alternative path for caller-supplied (non-stratified) draws: `gather_totals()` (NCCL all-gather of
+the totals) + `route()` (apexb200_shard_targets) + `sample()`.
 """
 from __future__ import annotations
 
@@ -68,20 +77,41 @@ class ShardedSampler:
         from . import _C
         _C.call("apexb200_peer_push_on_update", self.mem._h, 1 if enabled else 0)
 
+    def connect_local(self, samplers):
+        """Single-process variant of connect_peers: `samplers` are the ShardedSamplers of ALL shards, in rank
+        order, living in this process (one GPU or several with peer access).  No IPC, no collective."""
+        import ctypes as C
+        from . import _C
+        for s_ in samplers:
+            s_.mem._ensure()
+        arr = (C.c_void_p * len(samplers))(*[s_.mem._h.value for s_ in samplers])
+        _C.call("apexb200_peer_connect_local", self.mem._h, int(self.rank), len(samplers), arr)
+        self.connected = True
+
+    def push(self):
+        """Publish this shard's total as a new exchange round without waiting for the peers' (the publishing
+        half of exchange(); for shards driven in lock step from one process)."""
+        from . import _C
+        _C.call("apexb200_shard_push", self.mem._h, _C.stream_ptr())
+
     def exchange(self, totals_out=None):
         """One-launch all-gather of the shard totals over peer memory (collective: every rank
         calls it once per step, before sample_fused)."""
         from . import _C
         _C.call("apexb200_shard_exchange", self.mem._h, _C.ptr(totals_out), _C.stream_ptr())
 
-    def sample_fused(self, global_count, max_rows, with_q=False, u_out=None):
+    def sample_fused(self, global_count, max_rows=None, with_q=False, u_out=None):
         """Fused routing + search + gather of this rank's share of `global_count` stratified draws
         generated in the kernel (identical on every rank).  Returns (Batch over max_rows rows,
-        pos [max_rows] global draw index per row, count [1] rows owned)."""
+        pos [max_rows] global draw index per row, count [1] rows owned).  max_rows defaults to
+        global_count — the outputs can then hold the whole batch and no draw is ever dropped, however
+        uneven the shards' priority mass; only the live rows are written (and touch HBM)."""
         import torch
         from . import _C
         from .replay import Batch
         mem = self.mem
+        if max_rows is None:
+            max_rows = int(global_count)
         o = mem._outputs(int(max_rows), with_q)
         if "pos" not in o:
             o["pos"] = torch.empty(int(max_rows), dtype=torch.int32, device=mem.device)

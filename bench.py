@@ -159,13 +159,12 @@ def run_ours(args):
 
     gen = torch.Generator(device=dev).manual_seed(99 + rank)
     P = 4                                                         # pool of Q-value inputs, cycled
-    rows = B if world == 1 else (max(147 * ((B * 9 // 8 + 146) // 147), 147) if not args.nccl_exchange else Bg)
+    rows = B if world == 1 else Bg                               # sharded outputs hold the whole global batch
     qpool = [[torch.randn(rows, nA, device=dev, generator=gen) for _ in range(3)] for _ in range(P)]
     td_out = tuple(torch.empty(rows, device=dev) for _ in range(3)) + (torch.empty(1, device=dev),)
     sampler = apex_b200.ShardedSampler(mem, rank=rank, world_size=world) if world > 1 else None
     peer_path = world > 1 and not args.nccl_exchange
-    # per-rank quota of the global batch: 147 CTAs x 4 rows (588 rows for B=512 => 15 % head-room)
-    max_rows = max(147 * ((B * 9 // 8 + 146) // 147), 147) if peer_path else Bg
+    max_rows = Bg                                                 # no quota: a rank receives every draw it owns
     if peer_path:
         sampler.connect_peers()
         sampler.push_on_update(not args.no_push)                  # K5+K2 publishes the new total to the peers itself

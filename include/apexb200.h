@@ -65,7 +65,7 @@ extern "C" {
 #define APEXB200_ST_BAD_TARGET   4      /* target >= total in sample_targets */
 #define APEXB200_ST_BAD_ACTION   8      /* action outside [0, num_actions) */
 #define APEXB200_ST_PEER_TIMEOUT 16     /* shard_exchange: a peer never delivered its total */
-#define APEXB200_ST_QUOTA        32     /* sharded sample: this shard owns more draws than max_rows */
+#define APEXB200_ST_QUOTA        32     /* sharded sample: the caller's output arrays (max_rows < global_count) were too small */
 
 #define APEXB200_MAX_SHARDS       16
 #define APEXB200_IPC_HANDLE_BYTES 64
@@ -330,11 +330,21 @@ int apexb200_shard_targets(const uint64_t *totals, int32_t G, int32_t rank, cons
  * (NVLink peer access).  world <= APEXB200_MAX_SHARDS. */
 int apexb200_peer_export(apexb200_replay_t h, void *ipc_handle_host);
 int apexb200_peer_connect(apexb200_replay_t h, int32_t rank, int32_t world, const void *ipc_handles_host);
+/* The same for shards that live in ONE process (one handle per shard, on one GPU or on several GPUs
+ * with direct peer access): shards_host [world] are the handles of all shards in rank order,
+ * shards_host[rank] == h.  No IPC handles are involved.  Kernels of different shards must not be
+ * made to wait for one another on one GPU: issue apexb200_shard_push (not shard_exchange) for every
+ * shard before the sharded samples, and keep push-on-update steps in lock step (all samples, then
+ * all updates), so that every word a kernel polls for has already been written. */
+int apexb200_peer_connect_local(apexb200_replay_t h, int32_t rank, int32_t world, const apexb200_replay_t *shards_host);
 /* One launch replacing tree_total + all-gather: every rank writes {total, round} into
  * every peer's buffer and waits for all entries of the round.  Collective: every rank
  * must call it the same number of times.  The totals are kept in the handle for
  * apexb200_sample_gather_sharded and copied to totals_out (device u64 [world], nullable). */
 int apexb200_shard_exchange(apexb200_replay_t h, uint64_t *totals_out, void *stream);
+/* The publishing half of shard_exchange alone: start a new exchange round and write this shard's total
+ * into every peer's buffer without waiting for theirs (what td_fwd_update does with push-on-update). */
+int apexb200_shard_push(apexb200_replay_t h, void *stream);
 /* Fused compute + collective: with this enabled every apexb200_td_fwd_update on the handle
  * also publishes the shard's new total to all peers from the kernel that produced it (as a
  * new exchange round), so the steady-state step is sample_gather_sharded -> model ->
@@ -352,10 +362,15 @@ int apexb200_peer_push_on_update(apexb200_replay_t h, int32_t enabled);
  * interval; each warp finds the run by a 32-ary search on the draw function, takes local
  * row r = j - j_first, descends the local tree with (target - prefix) and gathers the
  * record into row r of the outputs ([max_rows, ...]).  count_out [1] = rows owned (rows
- * beyond it are stale), pos_out [max_rows] = global draw index j of each row.  A shard
- * that owns more than max_rows draws keeps the first max_rows and sets
- * APEXB200_ST_QUOTA.  Needs frames_per_state <= 8 and half a record (C frames) fitting in shared
- * memory. */
+ * beyond it are stale), pos_out [max_rows] = global draw index j of each row.
+ * Every draw the rank owns is delivered whatever the split of priority mass between the shards
+ * (replay.py:52-57: B requested, B returned): the launch covers the rank's fair share of the batch
+ * (global_count / world, plus head-room) in one wave of CTAs and a rank that owns more runs further
+ * waves inside the same launch.  max_rows is only the number of rows the output arrays hold: pass
+ * max_rows >= global_count (one rank can own the whole batch) and nothing is ever dropped; a smaller
+ * max_rows is a caller-side limit — a rank that owns more draws than that keeps the first max_rows
+ * and sets APEXB200_ST_QUOTA.  Needs frames_per_state <= 8 and half a record (C frames) fitting in
+ * shared memory. */
 int apexb200_sample_gather_sharded(apexb200_replay_t h, uint64_t seed, int32_t global_count, int32_t max_rows,
                                    int32_t *idx_out, int32_t *fsel_out, int32_t *pos_out, double *u_out,
                                    int32_t *count_out, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R,

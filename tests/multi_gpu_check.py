@@ -3,10 +3,12 @@
 
     torchrun --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 tests/multi_gpu_check.py
 
-Every rank owns a shard; the sharded sampler (NCCL all-gather of shard totals + K8 routing +
-local K3/K4/K5/K2) must return, over all ranks together, exactly the records a single tree
-over the concatenated shards returns for the same draws, byte-exact batches, and a loss whose
-sum over ranks equals the single-batch mean.
+Every rank owns a shard; both sharded paths — NCCL all-gather of shard totals + K8 routing + local
+K3/K4/K5/K2, and the default peer-memory exchange + fused sharded kernel (+ push from the TD/update
+kernel) — must return, over all ranks together, exactly the records a single tree over the
+concatenated shards returns for the same draws, byte-exact batches, and a loss whose sum over ranks
+equals the single-batch mean.  The shards are deliberately uneven (rank 0 carries 8x the priority
+mass): every draw a rank owns must arrive, however large its share.
 """
 import os
 import sys
@@ -36,7 +38,9 @@ def shard_data(rank, n, C, F, lanes):
         A = rng.integers(0, 4, m).astype(np.int32)
         R = rng.standard_normal(m).astype(np.float32)
         G = np.full(m, 0.97, np.float32)
-        prio = (np.abs(rng.standard_normal(m)) * (1 + rank) + 1e-3).astype(np.float32)
+        # uneven shards: rank 0 carries 32^0.6 = 8x the priority mass of a unit-scale shard, so it owns far
+        # more than its fair share of every global batch (several waves of the fused sharded kernel)
+        prio = (np.abs(rng.standard_normal(m)) * (32.0 if rank == 0 else 1 + rank) + 1e-3).astype(np.float32)
         ring.insert(lane, frames, rel, A, R, G, prio=prio)
         ops.append((lane, frames, rel, A, R, G, prio))
     return ring, ops
@@ -61,7 +65,7 @@ def sharded_learner_check(rank, world, dev):
         mem.insert(lane, torch.randint(0, 256, (m, 7056), dtype=torch.uint8, device=dev, generator=g), rel,
                    torch.randint(0, nA, (m,), dtype=torch.int32, device=dev, generator=g),
                    torch.randn(m, device=dev, generator=g), torch.full((m,), 0.97, device=dev),
-                   prio=torch.rand(m, device=dev, generator=g) * (1 + rank) + 0.01)
+                   prio=torch.rand(m, device=dev, generator=g) * (32.0 if rank == 0 else 1 + rank) + 0.01)   # rank 0: 8x the mass
     torch.manual_seed(1000 + rank)                                   # replicas start different: setup() must equalise them
     lp = {"remove_old_xp_freq": 100, "q_target_sync_freq": 2500, "min_replay_mem_size": 10, "replay_sample_size": B,
           "load_saved_state": False}
@@ -180,8 +184,7 @@ def main():
             rings[r][0].leaves[:] = new_leaves[r].cpu().numpy().view(np.uint64)
     # ---- peer-memory exchange + fused routing/search/gather (no NCCL on the step path)
     sampler.connect_peers()
-    B = 256
-    max_rows = int(B * 1.5)
+    max_rows = Bg                        # the outputs hold the whole global batch: no draw can be dropped
     totals = torch.zeros(world, dtype=torch.int64, device=dev)
     for rnd in range(1, 6):
         sampler.exchange(totals)

@@ -669,7 +669,10 @@ def test_peer_exchange_and_fused_sharded_sample_world1(apex, N):
             np.testing.assert_array_equal(b.S_t.cpu().numpy()[:B], g["S_t"])
             np.testing.assert_array_equal(b.S_tpn.cpu().numpy()[:B], g["S_tpn"])
             np.testing.assert_array_equal(b.R.cpu().numpy()[:B], g["R"])
-        # quota overflow is reported, not silent
+        # default row capacity = the global batch: nothing can be dropped
+        b, pos, cnt = sampler.sample_fused(B)
+        assert int(cnt.item()) == B and b.S_t.shape[0] == B
+        # output arrays smaller than the batch are a caller-side limit: reported, not silent
         b, pos, cnt = sampler.sample_fused(B, B - 50)
         assert int(cnt.item()) == B - 50
         with pytest.raises(apex._C.ApexError, match="quota"):
@@ -677,6 +680,129 @@ def test_peer_exchange_and_fused_sharded_sample_world1(apex, N):
         mem.update_priorities(dev(np.arange(5, dtype=np.int32)), dev(np.full(5, 2.0 * rnd, np.float32)))
         ring.set_priorities(np.arange(5), np.full(5, 2.0 * rnd, np.float32))
         ring.leaves[:5] = u64(mem.buffer(apex._C.BUF_LEAVES))[:5]
+    mem.check_status()
+
+
+@pytest.mark.parametrize("skew", [1.0, 8.0, 200.0])
+def test_sharded_group_on_one_gpu_returns_every_draw_whatever_the_skew(apex, skew):
+    """§8(e) with four shards driven in lock step from this process (apexb200_peer_connect_local): the fused
+    sharded kernel + the push from the TD/update kernel.  Shard 0 carries `skew` times the priority mass of
+    shards 1 and 2 and shard 3 is empty, so shard 0 owns far more than its fair share of the global batch
+    (several waves inside one launch, several passes of the single-CTA TD kernel).  Over all shards the rows
+    must be exactly the records one tree over the concatenated leaves returns for the same draws (indices
+    bit-exact, batches byte-exact, no draw lost or duplicated), the loss parts must add up to the global mean,
+    and every tree level must equal a rebuild after the updates."""
+    rng = np.random.default_rng(int(skew) + 77)
+    G_, n, C_, F, lanes, nA = 4, 4096, 2, 256, 2, 4
+    Bg = 1024
+    W = C_ - 1 + 3
+    mems, rings, samplers = [], [], []
+    for g in range(G_):
+        mem = make_mem(apex, n, C=C_, F=F, layout="stream", lanes=lanes, n=3)
+        mem.seed = 1234                                                        # identical draws on every shard
+        ring = ro.RingOracle(n, C_, F, lanes=lanes, fpr=1, lookback=W, alpha=0.6)
+        for lane in range(lanes):
+            m = n // lanes - W
+            args = (lane, rng.integers(0, 256, (m, F), dtype=np.uint8),
+                    apex.stream_offsets(C_, np.full(m, 3), np.minimum(np.arange(m), 300)),
+                    rng.integers(0, nA, m).astype(np.int32), rng.standard_normal(m).astype(np.float32),
+                    np.where(rng.random(m) < 0.05, 0, 0.97).astype(np.float32))
+            scale = (skew ** (1 / 0.6) if g == 0 else 1.0) if g != 3 else 0.0
+            prio = ((np.abs(rng.standard_normal(m)) + 1e-2) * scale).astype(np.float32)
+            mem.insert(*args, prio=prio)
+            ring.insert(*args, prio=prio)
+        ring.leaves[:] = u64(mem.buffer(apex._C.BUF_LEAVES))
+        mems.append(mem)
+        rings.append(ring)
+        samplers.append(apex.ShardedSampler(mem, rank=g, world_size=G_))
+    for s_ in samplers:
+        s_.connect_local(samplers)
+        s_.push_on_update(True)
+    for s_ in samplers:
+        s_.push()                                                              # round 1, nobody waits
+    rnd = 1
+    for step in range(3):
+        concat = np.concatenate([r.leaves for r in rings])
+        seen = np.zeros(Bg, np.int64)
+        u_glob = np.zeros(Bg)
+        got_idx = np.full(Bg, -1, np.int64)
+        outs = []
+        for g in range(G_):                                                    # all samples first ...
+            u_out = torch.full((Bg,), -1.0, dtype=torch.float64, device="cuda")
+            b, pos, cnt = samplers[g].sample_fused(Bg, u_out=u_out)
+            c = int(cnt.item())
+            pos_h = pos.cpu().numpy()[:c]
+            seen[pos_h] += 1
+            u_glob[pos_h] = u_out.cpu().numpy()[:c]
+            got_idx[pos_h] = g * n + b.idx.cpu().numpy()[:c]
+            assert (np.diff(pos_h) == 1).all() or c <= 1                       # a rank owns one contiguous run of draws
+            outs.append((b, pos_h, c, {k: getattr(b, k)[:c].clone() for k in ("idx", "S_t", "S_tpn", "A", "R", "Gamma")}))
+        assert (seen == 1).all(), "every global draw must be owned by exactly one shard"
+        np.testing.assert_array_equal(u_glob, ro.kernel_stratified_uniforms(1234, rnd, step, Bg))
+        whole = ro.tree_sample(concat, u_glob)
+        np.testing.assert_array_equal(got_idx, whole)
+        assert outs[3][2] == 0                                                 # the empty shard owns nothing
+        if skew >= 8:
+            assert outs[0][2] > Bg // 2                                        # far beyond one wave of the fair share
+        qrng = np.random.default_rng(100 + step)
+        qg = [qrng.standard_normal((Bg, nA)).astype(np.float32) for _ in range(3)]
+        loss_sum, A_g, R_g, G_g = 0.0, np.zeros(Bg, np.int32), np.zeros(Bg, np.float32), np.zeros(Bg, np.float32)
+        for g in range(G_):                                                    # ... then all updates (they push round + 1)
+            b, pos_h, c, rows = outs[g]
+            want = rings[g].gather(rows["idx"].cpu().numpy())
+            for k, wk in (("S_t", "S_t"), ("S_tpn", "S_tpn"), ("A", "A"), ("R", "R"), ("Gamma", "G")):
+                np.testing.assert_array_equal(rows[k].cpu().numpy(), want[wk])
+            A_g[pos_h], R_g[pos_h], G_g[pos_h] = want["A"], want["R"], want["G"]
+            q = [dev(np.concatenate([x[pos_h], np.zeros((Bg - c, nA), np.float32)])) for x in qg]
+            cnt = torch.tensor([c], dtype=torch.int32, device="cuda")
+            delta, prio, loss, mean = mems[g].td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma, count_dev=cnt,
+                                                        mean_divisor=float(Bg))
+            loss_sum += float(mean.item())
+            if c:
+                o = to.td_forward(qg[0][pos_h], qg[1][pos_h], qg[2][pos_h], want["A"], want["R"], want["G"], alpha=0.6)
+                np.testing.assert_allclose(prio.cpu().numpy()[:c], o["prio"], rtol=RTOL, atol=1e-7)
+                np.testing.assert_allclose(delta.cpu().numpy()[:c], o["delta"], rtol=RTOL, atol=1e-6)
+            rings[g].set_leaves(rows["idx"].cpu().numpy(), ro.priority_to_leaf(prio.cpu().numpy()[:c]))
+            for gl, w in zip(read_levels(apex, mems[g]), ro.build_levels(rings[g].leaves)):
+                np.testing.assert_array_equal(gl, w)
+        o = to.td_forward(qg[0], qg[1], qg[2], A_g, R_g, G_g, alpha=0.6)
+        np.testing.assert_allclose(loss_sum, o["loss_mean"], rtol=1e-5)
+        rnd += 1
+    for m_ in mems:
+        m_.check_status()                                                      # no quota / timeout / index bit anywhere
+
+
+@pytest.mark.parametrize("sorted_idx", [True, False])
+def test_td_update_with_more_live_rows_than_threads(apex, sorted_idx):
+    """Sharded call shape of K5+K2: arrays sized for a whole global batch, the live count on the device and
+    several times the rank's fair share -> the single-CTA kernel takes several passes (duplicates across
+    pass boundaries included); rows beyond the live count are ignored."""
+    rng = np.random.default_rng(5 + sorted_idx)
+    N, nA, rows, live, Bg = 1 << 15, 4, 3000, 2477, 256
+    mem = make_mem(apex, N)
+    leaves = rng.integers(1, 1 << 26, N, dtype=np.uint64)
+    load_leaves(apex, mem, leaves)
+    idx = rng.choice(rng.integers(0, N, 600), rows).astype(np.int32)               # ~4 rows per record: runs cross the
+    idx[310:330] = idx[330]                                                        # pass boundaries (320 threads per pass)
+    if sorted_idx:
+        idx[:live] = np.sort(idx[:live])
+    q = [rng.standard_normal((rows, nA)).astype(np.float32) for _ in range(3)]
+    A = rng.integers(0, nA, rows).astype(np.int32)
+    R, G = rng.standard_normal(rows).astype(np.float32), np.full(rows, 0.97, np.float32)
+    cnt = torch.tensor([live], dtype=torch.int32, device="cuda")
+    out = tuple(torch.full((k,), -7.0, device="cuda") for k in (rows, rows, rows, 1))
+    delta, prio, loss, mean = mem.td_update(dev(idx), dev(q[0]), dev(q[1]), dev(q[2]), dev(A), dev(R), dev(G), out=out,
+                                            count_dev=cnt, mean_divisor=float(Bg))
+    o = to.td_forward(q[0][:live], q[1][:live], q[2][:live], A[:live], R[:live], G[:live], alpha=0.6)
+    np.testing.assert_allclose(prio.cpu().numpy()[:live], o["prio"], rtol=RTOL, atol=1e-7)
+    np.testing.assert_allclose(delta.cpu().numpy()[:live], o["delta"], rtol=RTOL, atol=1e-6)
+    np.testing.assert_allclose(mean.item(), float(np.sum(o["loss"].astype(np.float64)) / Bg), rtol=RTOL)
+    assert (prio.cpu().numpy()[live:] == -7.0).all()                               # dead rows untouched
+    new = ro.priority_to_leaf(prio.cpu().numpy()[:live])
+    for i, v in zip(idx[:live].tolist(), new.tolist()):
+        leaves[i] = v
+    for g, w in zip(read_levels(apex, mem), ro.build_levels(leaves)):
+        np.testing.assert_array_equal(g, w)
     mem.check_status()
 
 
@@ -824,6 +950,27 @@ def test_insert_lanes_equals_per_lane_inserts(apex, E, lane_cap, T, rounds):
     b.check_status()
 
 
+@pytest.mark.parametrize("lane_cap,lanes", [(40, 1), (44, 8), (1032, 1), (96, 3), (33, 2)])
+def test_insert_across_ring_wrap_keeps_every_tree_level_exact(apex, lane_cap, lanes):
+    """Inserts whose slots wrap around the ring inside one warp of K6 (lane capacity not a multiple of 32):
+    after every insert each inner level of the sum tree must equal a rebuild from the leaves."""
+    rng = np.random.default_rng(lane_cap * 131 + lanes)
+    C_, F, n = 1, 16, 1
+    mem = make_mem(apex, lane_cap * lanes, C=C_, F=F, layout="stream", lanes=lanes, n=n)
+    look = C_ - 1 + n
+    sizes = [5, 7, 13, 29, 31, 32, lane_cap - look, 3, 17, 11, 23, 19, 9, 30, 6, 27]
+    for r, m in enumerate(sizes * 3):
+        m = min(m, lane_cap - look)
+        lane = r % lanes
+        mem.insert(lane, rng.integers(0, 256, (m, F), dtype=np.uint8), apex.stream_offsets(C_, np.full(m, n), np.arange(m)),
+                   rng.integers(0, 4, m).astype(np.int32), rng.standard_normal(m).astype(np.float32),
+                   np.full(m, 0.99, np.float32), prio=(np.abs(rng.standard_normal(m)) * 10 + 1e-3).astype(np.float32))
+        levels = read_levels(apex, mem)
+        for l, (got, want) in enumerate(zip(levels, ro.build_levels(levels[0]))):
+            np.testing.assert_array_equal(got, want, err_msg="level %d after insert %d (%d records)" % (l, r, m))
+    mem.check_status()
+
+
 def _ring_actor(name, slots, T, F, nA, chunks, seed):
     import sys
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -915,7 +1062,8 @@ def test_full_size_properties_2m(apex):
     g = torch.Generator(device="cuda").manual_seed(1234)
     lane_cap = N // 32
     chunk = 8192
-    rel = dev(apex.stream_offsets(C_, np.full(chunk, 3), np.minimum(np.arange(chunk) + 100, 1000)))
+    rel_host = apex.stream_offsets(C_, np.full(chunk, 3), np.minimum(np.arange(chunk) + 100, 1000)).astype(np.int64)
+    rel = dev(rel_host.astype(np.int32))
     for lane in range(32):
         for c in range(lane_cap // chunk):
             frames = torch.randint(0, 256, (chunk, F), dtype=torch.uint8, device="cuda", generator=g)
@@ -928,6 +1076,7 @@ def test_full_size_properties_2m(apex):
             prio = torch.randn(chunk, device="cuda", generator=g).abs() + 1e-3
             mem.insert(lane, frames, rel, A, R, G, prio=prio)
     assert mem.size() == N
+    store = mem.buffer(apex._C.BUF_FRAMES).view(-1, F)
     rng = np.random.default_rng(4321)
     leaves = u64(mem.buffer(apex._C.BUF_LEAVES))
     for step in range(20):
@@ -942,6 +1091,16 @@ def test_full_size_properties_2m(apex):
         got = sum(tags[:, :, k] << np.uint64(8 * k) for k in range(8))
         np.testing.assert_array_equal(got, fsel[:, C_:].astype(np.uint64))         # each gathered frame names its slot
         np.testing.assert_array_equal(fsel[:, -1], idx)                            # newest S_tpn frame = the record's own
+        # the frame slots of every sampled record, recomputed on the host from the insert's offsets ...
+        p = idx % lane_cap
+        want_f = (idx // lane_cap * lane_cap)[:, None] + (p[:, None] + rel_host[p % chunk]) % lane_cap
+        np.testing.assert_array_equal(fsel, want_f)
+        # ... and every byte of both gathered states against the frame store itself (2 x B x C x 7056 bytes)
+        sel = b.fsel.long()
+        assert torch.equal(b.S_t.view(B * C_, F), store.index_select(0, sel[:, :C_].reshape(-1)))
+        assert torch.equal(b.S_tpn.view(B * C_, F), store.index_select(0, sel[:, C_:].reshape(-1)))
+        for name, which in (("A", apex._C.BUF_ACTION), ("R", apex._C.BUF_REWARD), ("Gamma", apex._C.BUF_GAMMA)):
+            assert torch.equal(getattr(b, name), mem.buffer(which).index_select(0, b.idx.long()))
         q = [torch.randn(B, nA, device="cuda", generator=g) for _ in range(3)]
         _, prio, _, _ = mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma)
         new = ro.priority_to_leaf(prio.cpu().numpy())
@@ -1030,7 +1189,8 @@ def test_max_capacity_16m_records(apex):
     mem._ensure()
     g = torch.Generator(device="cuda").manual_seed(7)
     lane_cap, chunk = N // lanes, 16384
-    rel = dev(apex.stream_offsets(C_, np.full(chunk, 3), np.full(chunk, 100)))
+    rel_host = apex.stream_offsets(C_, np.full(chunk, 3), np.full(chunk, 100)).astype(np.int64)
+    rel = dev(rel_host.astype(np.int32))
     block = torch.randint(0, 256, (chunk, F), dtype=torch.uint8, device="cuda", generator=g)
     shifts = torch.arange(0, 64, 8, device="cuda")
     for lane in range(lanes):
@@ -1042,6 +1202,7 @@ def test_max_capacity_16m_records(apex):
                        torch.zeros(chunk, device="cuda"), torch.full((chunk,), 0.97, device="cuda"),
                        prio=torch.rand(chunk, device="cuda", generator=g) + 1e-3)
     assert mem.size() == N
+    store = mem.buffer(apex._C.BUF_FRAMES).view(-1, F)
     for step in range(4):
         u_out = torch.empty(B, dtype=torch.float64, device="cuda")
         b = mem.sample_tensors(B, u_out=u_out)
@@ -1052,6 +1213,12 @@ def test_max_capacity_16m_records(apex):
         got = sum(tags[:, :, k] << np.uint64(8 * k) for k in range(8))
         np.testing.assert_array_equal(got, fsel[:, C_:])
         np.testing.assert_array_equal(fsel[:, -1], idx.astype(np.uint64))
+        p = idx.astype(np.int64) % lane_cap                                  # frame slots recomputed on the host
+        want_f = (idx.astype(np.int64) // lane_cap * lane_cap)[:, None] + (p[:, None] + rel_host[p % chunk]) % lane_cap
+        np.testing.assert_array_equal(fsel.astype(np.int64), want_f)
+        sel = b.fsel.long()                                                  # every gathered byte against the store
+        assert torch.equal(b.S_t.view(B * C_, F), store.index_select(0, sel[:, :C_].reshape(-1)))
+        assert torch.equal(b.S_tpn.view(B * C_, F), store.index_select(0, sel[:, C_:].reshape(-1)))
         q = [torch.randn(B, nA, device="cuda", generator=g) for _ in range(3)]
         mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma)
     leaves = mem.buffer(apex._C.BUF_LEAVES)

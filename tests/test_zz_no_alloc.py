@@ -4,8 +4,9 @@ static buffer inside the library instead of a caller-provided workspace.
 It is meant for callers that cannot allocate device memory themselves (bindings without
 the CUDA runtime, processes whose framework already owns all of HBM, loops that must not
 hit cudaMalloc's device-wide synchronisation).  The test calls it through the C ABI and
-compares every output with apexb200_td_fwd on the same inputs, on two calls in a row: the
-second call is smaller than the first, so stale partial sums and the used ticket left in
+compares every output with apexb200_td_fwd on the same inputs and, directly, with the CPU
+oracle of learner.py:43-52 (oracle/td_oracle.py), on several calls in a row: each later
+call is smaller than the first, so stale partial sums and the used ticket left in
 the shared scratch by the first call would show up if the entry point did not handle them.
 This file sorts last on purpose: with `pytest -x` every other test has run before it.
 """
@@ -13,6 +14,8 @@ import numpy as np
 import pytest
 
 torch = pytest.importorskip("torch")
+
+from oracle import td_oracle as to               # noqa: E402
 
 pytestmark = pytest.mark.gpu
 
@@ -47,6 +50,13 @@ def test_noalloc_matches_workspace_entry_point_on_consecutive_calls():
             torch.testing.assert_close(g, w, rtol=RTOL, atol=1e-7, msg=lambda m: "%s B=%d: %s" % (name, B, m))
         if B > 1024:                                   # same kernel on both sides: identical bits
             assert all(torch.equal(g, w) for g, w in zip(got, want))
+        # and against the oracle itself, not only against the sibling entry point
+        o = to.td_forward(*(x.cpu().numpy() for x in q), A.cpu().numpy(), R.cpu().numpy(), G.cpu().numpy(), alpha=0.6,
+                          loss_kind=kind, kappa=1.0)
+        np.testing.assert_allclose(got[0].cpu().numpy(), o["delta"], rtol=RTOL, atol=1e-6)
+        np.testing.assert_allclose(got[1].cpu().numpy(), o["prio"], rtol=RTOL, atol=1e-7)
+        np.testing.assert_allclose(got[2].cpu().numpy(), o["loss"], rtol=RTOL, atol=1e-7)
+        np.testing.assert_allclose(got[3].item(), o["loss_mean"], rtol=RTOL)
     # the documented limit is enforced with a clear error, before anything is launched
     B = _C.TD_NOALLOC_MAX_B + 1
     z = torch.zeros(B, 4, device="cuda")
