@@ -14,6 +14,7 @@ LIB_PATH = os.environ.get("APEXB200_LIB", os.path.join(_HERE, "libapexb200.so"))
 
 OK, EINVAL, ECUDA, ENOMEM, ERANGE = 0, -1, -2, -3, -4
 LOSS_HALF_SQ, LOSS_HUBER = 0, 1
+FMT_U8, FMT_F32 = 0, 1
 ST_EMPTY_TREE, ST_BAD_INDEX, ST_BAD_TARGET, ST_BAD_ACTION, ST_PEER_TIMEOUT, ST_QUOTA = 1, 2, 4, 8, 16, 32
 IPC_HANDLE_BYTES = 64
 FRAC_BITS = 24
@@ -66,7 +67,7 @@ SIGNATURES = {
     "apexb200_sample_targets": [_P, _P, _P, _I32, _P, _P, _P, _P],
     "apexb200_gather": [_P, _P, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "apexb200_set_gather_variant": [_I32],
-    "apexb200_sample_gather": [_P, _P, C.c_uint64, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "apexb200_sample_gather": [_P, _P, C.c_uint64, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P],
     "apexb200_set_pdl": [_I32],
     "apexb200_set_td_cluster": [_I32],
     "apexb200_td_workspace_bytes": [_I32, C.POINTER(_I64)],
@@ -77,6 +78,7 @@ SIGNATURES = {
     "apexb200_td_fwd_update": [_P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _F, _I32, _F, _P, _P, _P, _P, _P, _P, _I64,
                                _P, _F, _P],
     "apexb200_host_step": [_P, _I32, _P, _P, _I32, _I32, _F, _I32, _F, _P, _P, _P, _P, _P, _P, _P, _P],
+    "apexb200_host_step_sharded": [_P, _I32, C.c_uint64, _I32, _I32, _P, _I32, _F, _I32, _F, _P, _P, _P, _P, _P, _P, _P, _P],
     "apexb200_nstep": [_P, _P, _I32, _I32, _I32, _F, _P, _P, _P, _P],
     "apexb200_initial_priority": [_P, _P, _P, _P, _P, _I32, _I32, _P, _P],
     "apexb200_shard_targets": [_P, _I32, _I32, _P, _I32, _P, _P, _P, _P],
@@ -86,7 +88,7 @@ SIGNATURES = {
     "apexb200_shard_exchange": [_P, _P, _P],
     "apexb200_shard_push": [_P, _P],
     "apexb200_peer_push_on_update": [_P, _I32],
-    "apexb200_sample_gather_sharded": [_P, C.c_uint64, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "apexb200_sample_gather_sharded": [_P, C.c_uint64, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P],
     "apexb200_params_create": [_I32, _P, _I32, C.c_uint64, C.POINTER(_P)],
     "apexb200_params_destroy": [_P],
     "apexb200_params_flat": [_P, C.POINTER(_P), C.POINTER(C.c_uint64)],

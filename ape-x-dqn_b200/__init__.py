@@ -11,13 +11,13 @@ from .actor import ExperienceBuffer, Actor, Transition        # noqa: F401
 from .learner import Learner, ShardedLearner, FlatGradients, td_loss   # noqa: F401
 from . import ops                                             # noqa: F401
 from .sharded import ShardedSampler                           # noqa: F401
-from .pipeline import HostStepPipeline                        # noqa: F401
+from .pipeline import HostStepPipeline, ShardedHostStepPipeline                        # noqa: F401
 from .ingest import VectorActorIngest, ActorStagingRing, RingIngest   # noqa: F401
 from .weights import (WeightPublisher, WeightSubscriber, DeviceWeightSubscriber, BatchedActorPolicy,   # noqa: F401
                       actor_policy, actor_epsilons, param_layout)
 from .vector_actor import VectorActor                         # noqa: F401
 
 __all__ = ["ReplayMemory", "Learner", "Actor", "ExperienceBuffer", "N_Step_Transition", "Transition", "Batch",
-           "KeyIndex", "stream_offsets", "td_loss", "ops", "ShardedSampler", "HostStepPipeline", "VectorActorIngest", "ActorStagingRing", "RingIngest",
+           "KeyIndex", "stream_offsets", "td_loss", "ops", "ShardedSampler", "HostStepPipeline", "ShardedHostStepPipeline", "VectorActorIngest", "ActorStagingRing", "RingIngest",
            "WeightPublisher", "WeightSubscriber", "DeviceWeightSubscriber", "BatchedActorPolicy", "actor_policy",
            "actor_epsilons", "param_layout", "VectorActor", "ShardedLearner", "FlatGradients"]

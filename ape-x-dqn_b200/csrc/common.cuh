@@ -361,11 +361,12 @@ bool sample_gather_is_fused(const apexb200_replay *h);
 int run_sample_gather(apexb200_replay *h, const double *u, uint64_t seed, int32_t count, int32_t *idx_out,
                       int32_t *fsel_out, uint64_t *leaf_out, uint64_t *total_out, double *u_out, uint8_t *S_t,
                       uint8_t *S_tpn, int32_t *A, float *R, float *Gamma, float *q_t, float *q_tpn,
-                      const unsigned *ready, unsigned ready_value, cudaStream_t stream);
+                      const unsigned *ready, unsigned ready_value, cudaStream_t stream,
+                      int out_format = APEXB200_FMT_U8);
 int sharded_wave_rows(const apexb200_replay *h, int global_count, int max_rows);
 int run_sample_gather_sharded(apexb200_replay *h, uint64_t seed, int32_t global_count, int32_t max_rows,
                               int32_t *idx_out, int32_t *fsel_out, int32_t *pos_out, double *u_out,
                               int32_t *count_out, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R, float *Gamma,
                               float *q_t, float *q_tpn, const unsigned *ready, unsigned ready_value,
-                              cudaStream_t stream);
+                              cudaStream_t stream, int out_format = APEXB200_FMT_U8);
 }  // namespace apexb200

@@ -19,10 +19,11 @@ __device__ __forceinline__ uint4 ld_stream(const uint4 *p) {
 
 struct GatherArgs {
     const int32_t *idx, *fsel, *count_dev;
-    uint8_t *S_t, *S_tpn;
+    uint8_t *S_t, *S_tpn;            // [rows, C, F] uint8, or (elem_bytes = 4) float32 in the same shape
     int32_t *A;
     float *R, *G, *q_t, *q_tpn;
     int count;
+    int elem_bytes;                  // bytes per output element: 1 (uint8 as stored) or 4 (float32, learner.py:37-38)
 };
 
 struct SampleArgs {
@@ -38,7 +39,7 @@ struct SampleArgs {
 __device__ __forceinline__ uint8_t *item_dst(const RingView &rv, const GatherArgs &ga, long long b, int k) {
     uint8_t *base = k < rv.C ? ga.S_t : ga.S_tpn;
     int kk = k < rv.C ? k : k - rv.C;
-    return base + (b * rv.C + kk) * (long long)rv.F;
+    return base + (b * rv.C + kk) * (long long)rv.F * ga.elem_bytes;
 }
 
 __device__ __forceinline__ bool resolve_item(const RingView &rv, const GatherArgs &ga, long long it, int count,
@@ -163,6 +164,37 @@ __device__ __forceinline__ void tma_drain_frames(bool moving, uint8_t *dst, uint
     asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 
+// float32 outputs (the dtype the learner's network consumes, learner.py:37-38): the bulk-copy engine cannot
+// convert, so a frame that has landed in shared memory is widened by the whole warp — 4 bytes in, one 16-byte
+// vector of 4 floats out per lane and iteration — and written with ordinary vector stores.  Frames are taken in
+// lane order; frame c's mbarrier is polled by all lanes.  `dst` is the owning lane's output pointer.
+// Must be called by all 32 lanes.
+__device__ __forceinline__ void f32_drain_frames(bool moving, uint8_t *dst, const uint8_t *warp_stage,
+                                                 unsigned long long *warp_bars, int C, unsigned bytes, int nch,
+                                                 unsigned parity) {
+    const int lane = threadIdx.x & 31;
+    const unsigned mask = __ballot_sync(0xffffffffu, moving);
+    for (int c = 0; c < C; ++c) {
+        if (!((mask >> c) & 1u)) continue;
+        for (int ch = 0; ch < nch; ++ch) {
+            const unsigned bar_s = (unsigned)__cvta_generic_to_shared(warp_bars + c * kMaxChunks + ch);
+            unsigned done = 0u;
+            while (!done)
+                asm volatile("{\n .reg .pred p;\n mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+                             " selp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(bar_s), "r"(parity) : "memory");
+        }
+        float4 *out = (float4 *)__shfl_sync(0xffffffffu, (unsigned long long)dst, c);
+        const uchar4 *in = (const uchar4 *)(warp_stage + (size_t)c * bytes);
+        const int nv = (int)(bytes >> 2);
+        #pragma unroll 4
+        for (int v = lane; v < nv; v += 32) {
+            const uchar4 x = in[v];
+            __stcs(out + v, make_float4((float)x.x, (float)x.y, (float)x.z, (float)x.w));
+        }
+    }
+    __syncwarp();
+}
+
 // ---- variant 0: one warp per frame, 16-byte vectors, all loads of a frame in flight
 // before the first store.  Kept as the non-TMA comparison point.
 template <int UNROLL>
@@ -238,7 +270,7 @@ gather_tma_kernel(RingView rv, GatherArgs ga, int per_cta, int32_t *status) {
 // index and metadata outputs.  Half draws as the unit of work balance the frames over the
 // SMs: a B=512, C=4 batch is 1024 units = 147 CTAs of 7 warps (28 frames, 193 KB of
 // staging each), one CTA per SM, every frame of the batch in flight at once.
-template <bool kPolled>
+template <bool kPolled, bool kF32>
 __device__ __forceinline__ void sample_gather_body(const TreeView &tv, const RingView &rv, const SampleArgs &sa,
                                                    const GatherArgs &ga, int32_t *ctrl, const unsigned *ready,
                                                    unsigned ready_value) {
@@ -300,19 +332,29 @@ __device__ __forceinline__ void sample_gather_body(const TreeView &tv, const Rin
         }
         if (node >= 0 && lane == 16) copy_meta_row(rv, ga, w, node);
     }
-    tma_drain_frames(moving, moving ? item_dst(rv, ga, w, k) : nullptr, stage, my_bars, (unsigned)rv.F, nch);
+    if (kF32)
+        f32_drain_frames(moving, moving ? item_dst(rv, ga, w, k) : nullptr, stage - (size_t)lane * rv.F,
+                         my_bars - lane * kMaxChunks, C, (unsigned)rv.F, nch, 0u);
+    else
+        tma_drain_frames(moving, moving ? item_dst(rv, ga, w, k) : nullptr, stage, my_bars, (unsigned)rv.F, nch);
 }
 
 __global__ void __launch_bounds__(512)
 sample_gather_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int32_t *ctrl) {
-    sample_gather_body<false>(tv, rv, sa, ga, ctrl, nullptr, 0u);
+    sample_gather_body<false, false>(tv, rv, sa, ga, ctrl, nullptr, 0u);
+}
+
+// The same search + gather writing float32 batches (the network's input dtype) instead of uint8.
+__global__ void __launch_bounds__(512)
+sample_gather_f32_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int32_t *ctrl) {
+    sample_gather_body<false, true>(tv, rv, sa, ga, ctrl, nullptr, 0u);
 }
 
 // Same kernel for the host-facing step: waits in-kernel for the arrival word of its draws.
 __global__ void __launch_bounds__(512)
 sample_gather_polled_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int32_t *ctrl,
                             const unsigned *ready, unsigned ready_value) {
-    sample_gather_body<true>(tv, rv, sa, ga, ctrl, ready, ready_value);
+    sample_gather_body<true, false>(tv, rv, sa, ga, ctrl, ready, ready_value);
 }
 
 // ---- fused K8 + K3 + K4 for one rank of a sharded replay (after shard_exchange_kernel).
@@ -378,7 +420,7 @@ __device__ __forceinline__ int first_draw_at_or_above(unsigned long long bound, 
 // + wave_rows, + 2 wave_rows, ... until it passes the end of the rank's run of draws.  Targets are
 // non-decreasing in the draw index, so the first dead row of a warp ends its loop.  The staging buffer
 // and mbarriers of a lane are reused from wave to wave (phase parity = wave & 1).
-template <bool kPolled>
+template <bool kPolled, bool kF32>
 __device__ __forceinline__ void sample_gather_sharded_body(const TreeView &tv, const RingView &rv, const SampleArgs &sa,
                                                            const GatherArgs &ga, const ShardArgs &sh, const PeerView &pv,
                                                            int32_t *ctrl, const unsigned *ready, unsigned ready_value) {
@@ -466,29 +508,42 @@ __device__ __forceinline__ void sample_gather_sharded_body(const TreeView &tv, c
             if (cnt > sh.max_rows) { cnt = sh.max_rows; if (lane == 0) atomicOr(ctrl, APEXB200_ST_QUOTA); }
             if (lane == 0) *sh.count_out = cnt;
         }
-        tma_drain_frames(moving, moving ? item_dst(rv, ga, row, k) : nullptr, stage, my_bars, (unsigned)rv.F, nch,
-                         wave & 1u);
+        if (kF32)
+            f32_drain_frames(moving, moving ? item_dst(rv, ga, row, k) : nullptr, stage - (size_t)lane * rv.F,
+                             my_bars - lane * kMaxChunks, C, (unsigned)rv.F, nch, wave & 1u);
+        else
+            tma_drain_frames(moving, moving ? item_dst(rv, ga, row, k) : nullptr, stage, my_bars, (unsigned)rv.F, nch,
+                             wave & 1u);
     }
 }
 
 __global__ void __launch_bounds__(512)
 sample_gather_sharded_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, ShardArgs sh, PeerView pv,
                              int32_t *ctrl) {
-    sample_gather_sharded_body<false>(tv, rv, sa, ga, sh, pv, ctrl, nullptr, 0u);
+    sample_gather_sharded_body<false, false>(tv, rv, sa, ga, sh, pv, ctrl, nullptr, 0u);
+}
+
+__global__ void __launch_bounds__(512)
+sample_gather_sharded_f32_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, ShardArgs sh, PeerView pv,
+                                 int32_t *ctrl) {
+    sample_gather_sharded_body<false, true>(tv, rv, sa, ga, sh, pv, ctrl, nullptr, 0u);
 }
 
 // Same kernel for the host-facing sharded step: also waits for the arrival word of the step's Q rows.
 __global__ void __launch_bounds__(512)
 sample_gather_sharded_polled_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, ShardArgs sh, PeerView pv,
                                     int32_t *ctrl, const unsigned *ready, unsigned ready_value) {
-    sample_gather_sharded_body<true>(tv, rv, sa, ga, sh, pv, ctrl, ready, ready_value);
+    sample_gather_sharded_body<true, false>(tv, rv, sa, ga, sh, pv, ctrl, ready, ready_value);
 }
 
 static int ensure_smem(const void *fn, size_t smem, int device) {
-    static size_t configured[5][64] = {};
-    const int which = (fn == (const void *)gather_tma_kernel) ? 0 : (fn == (const void *)sample_gather_kernel) ? 1
-                    : (fn == (const void *)sample_gather_polled_kernel) ? 3
-                    : (fn == (const void *)sample_gather_sharded_polled_kernel) ? 4 : 2;
+    constexpr int kKernels = 8;
+    static const void *known[kKernels] = {};
+    static size_t configured[kKernels][64] = {};
+    int which = 0;
+    while (which < kKernels && known[which] != nullptr && known[which] != fn) ++which;
+    APEX_REQUIRE(which < kKernels, APEXB200_ECUDA, "ensure_smem: kernel table full");
+    known[which] = fn;
     if (smem > 48 * 1024 && device >= 0 && device < 64 && smem > configured[which][device]) {
         APEX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[which][device] = smem;
@@ -517,7 +572,7 @@ int apexb200_gather(apexb200_replay_t h, const int32_t *idx, const int32_t *fsel
     APEX_REQUIRE((((uintptr_t)S_t | (uintptr_t)S_tpn) & 15) == 0, APEXB200_EINVAL,
                  "gather: output batches must be 16-byte aligned");
     const RingView &rv = h->ring;
-    GatherArgs ga{idx, fsel, count_dev, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, count};
+    GatherArgs ga{idx, fsel, count_dev, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, count, 1};
     cudaStream_t st = (cudaStream_t)stream;
     const long long items = (long long)count * 2 * rv.C;
     const long long meta_warps = (count + 31) / 32;
@@ -539,11 +594,14 @@ int apexb200_gather(apexb200_replay_t h, const int32_t *idx, const int32_t *fsel
 }
 
 int apexb200_sample_gather(apexb200_replay_t h, const double *u, uint64_t seed, int32_t count, int32_t *idx_out,
-                           int32_t *fsel_out, uint64_t *leaf_out, uint64_t *total_out, double *u_out, uint8_t *S_t,
-                           uint8_t *S_tpn, int32_t *A, float *R, float *Gamma, float *q_t, float *q_tpn,
-                           void *stream) {
-    return apexb200::run_sample_gather(h, u, seed, count, idx_out, fsel_out, leaf_out, total_out, u_out, S_t, S_tpn, A, R,
-                                       Gamma, q_t, q_tpn, nullptr, 0u, (cudaStream_t)stream);
+                           int32_t *fsel_out, uint64_t *leaf_out, uint64_t *total_out, double *u_out, void *S_t,
+                           void *S_tpn, int32_t *A, float *R, float *Gamma, float *q_t, float *q_tpn,
+                           int32_t out_format, void *stream) {
+    APEX_REQUIRE(out_format == APEXB200_FMT_U8 || out_format == APEXB200_FMT_F32, APEXB200_EINVAL,
+                 "sample_gather: unknown output format %d", out_format);
+    return apexb200::run_sample_gather(h, u, seed, count, idx_out, fsel_out, leaf_out, total_out, u_out, (uint8_t *)S_t,
+                                       (uint8_t *)S_tpn, A, R, Gamma, q_t, q_tpn, nullptr, 0u, (cudaStream_t)stream,
+                                       out_format);
 }
 
 }  // extern "C"
@@ -558,7 +616,7 @@ bool sample_gather_is_fused(const apexb200_replay *h) {
 int run_sample_gather(apexb200_replay *h, const double *u, uint64_t seed, int32_t count, int32_t *idx_out,
                       int32_t *fsel_out, uint64_t *leaf_out, uint64_t *total_out, double *u_out, uint8_t *S_t,
                       uint8_t *S_tpn, int32_t *A, float *R, float *Gamma, float *q_t, float *q_tpn,
-                      const unsigned *ready, unsigned ready_value, cudaStream_t stream) {
+                      const unsigned *ready, unsigned ready_value, cudaStream_t stream, int out_format) {
     APEX_REQUIRE(h && count >= 0, APEXB200_EINVAL, "sample_gather: bad argument");
     if (count == 0) return APEXB200_OK;
     APEX_REQUIRE(idx_out && S_t && S_tpn, APEXB200_EINVAL, "sample_gather: null idx_out/S_t/S_tpn");
@@ -567,8 +625,11 @@ int run_sample_gather(apexb200_replay *h, const double *u, uint64_t seed, int32_
     const RingView &rv = h->ring;
     const size_t per_unit = (size_t)rv.C * rv.F + 8 * kMaxChunks * 8;       // one half draw: C frames + their mbarriers
     cudaStream_t st = stream;
+    const bool f32 = out_format == APEXB200_FMT_F32;
     if (rv.C > 8 || per_unit > kStageBudget) {
         APEX_REQUIRE(!ready, APEXB200_ERANGE, "sample_gather: the polled variant needs the fused kernel");
+        APEX_REQUIRE(!f32, APEXB200_ERANGE, "sample_gather: float32 output needs the fused kernel (half a record of "
+                     "%d frames x %d bytes does not fit one CTA's staging)", rv.C, rv.F);
         // staging for half a record does not fit one CTA: run the two kernels back to back
         int rc = u ? apexb200_sample(h, u, count, idx_out, leaf_out, total_out, fsel_out, stream)
                    : apexb200_sample_stratified(h, seed, count, idx_out, leaf_out, total_out, fsel_out, u_out, stream);
@@ -592,7 +653,14 @@ int run_sample_gather(apexb200_replay *h, const double *u, uint64_t seed, int32_
     if (rc) return rc;
     SampleArgs sa{u, (unsigned long long)seed, u ? 0ull : h->draw_calls++, idx_out, fsel_out, (unsigned long long *)leaf_out,
                   (unsigned long long *)total_out, u_out};
-    GatherArgs ga{idx_out, fsel_out, nullptr, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, count};
+    GatherArgs ga{idx_out, fsel_out, nullptr, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, count, f32 ? 4 : 1};
+    if (f32) {
+        APEX_REQUIRE(!ready, APEXB200_ERANGE, "sample_gather: the polled variant writes uint8 batches");
+        rc = ensure_smem((const void *)sample_gather_f32_kernel, smem, h->cfg.device);
+        if (rc) return rc;
+        return launch_step("sample_gather_f32_kernel", sample_gather_f32_kernel, dim3((unsigned)((units + wpc - 1) / wpc)),
+                           dim3(wpc * 32), smem, st, h->tree, rv, sa, ga, h->status);
+    }
     if (ready) {
         APEX_REQUIRE(u, APEXB200_EINVAL, "sample_gather: the polled variant takes caller draws");
         rc = ensure_smem((const void *)sample_gather_polled_kernel, smem, h->cfg.device);
@@ -620,8 +688,9 @@ int run_sample_gather_sharded(apexb200_replay *h, uint64_t seed, int32_t global_
                               int32_t *idx_out, int32_t *fsel_out, int32_t *pos_out, double *u_out,
                               int32_t *count_out, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R, float *Gamma,
                               float *q_t, float *q_tpn, const unsigned *ready, unsigned ready_value,
-                              cudaStream_t stream) {
+                              cudaStream_t stream, int out_format) {
     APEX_REQUIRE(h && global_count > 0 && max_rows > 0, APEXB200_EINVAL, "sample_gather_sharded: bad argument");
+    const bool f32 = out_format == APEXB200_FMT_F32;
     APEX_REQUIRE(idx_out && count_out && S_t && S_tpn, APEXB200_EINVAL, "sample_gather_sharded: null output");
     APEX_REQUIRE((((uintptr_t)S_t | (uintptr_t)S_tpn) & 15) == 0, APEXB200_EINVAL,
                  "sample_gather_sharded: output batches must be 16-byte aligned");
@@ -639,8 +708,15 @@ int run_sample_gather_sharded(apexb200_replay *h, uint64_t seed, int32_t global_
     if (wpc > 16) wpc = 16;
     const size_t smem = (size_t)wpc * per_unit;
     SampleArgs sa{nullptr, (unsigned long long)seed, 0ull, idx_out, fsel_out, nullptr, nullptr, u_out};
-    GatherArgs ga{idx_out, fsel_out, nullptr, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, max_rows};
+    GatherArgs ga{idx_out, fsel_out, nullptr, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, max_rows, f32 ? 4 : 1};
     ShardArgs sh{(unsigned long long)seed, h->draw_calls++, global_count, max_rows, pos_out, count_out};
+    if (f32) {
+        APEX_REQUIRE(!ready, APEXB200_ERANGE, "sample_gather_sharded: the polled variant writes uint8 batches");
+        int rc = ensure_smem((const void *)sample_gather_sharded_f32_kernel, smem, h->cfg.device);
+        if (rc) return rc;
+        return launch_step("sample_gather_sharded_f32_kernel", sample_gather_sharded_f32_kernel, dim3((unsigned)ctas),
+                           dim3(wpc * 32), smem, stream, h->tree, rv, sa, ga, sh, h->peers, h->status);
+    }
     if (ready) {
         int rc = ensure_smem((const void *)sample_gather_sharded_polled_kernel, smem, h->cfg.device);
         if (rc) return rc;
@@ -658,11 +734,13 @@ extern "C" {
 
 int apexb200_sample_gather_sharded(apexb200_replay_t h, uint64_t seed, int32_t global_count, int32_t max_rows,
                                    int32_t *idx_out, int32_t *fsel_out, int32_t *pos_out, double *u_out,
-                                   int32_t *count_out, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R,
-                                   float *Gamma, float *q_t, float *q_tpn, void *stream) {
+                                   int32_t *count_out, void *S_t, void *S_tpn, int32_t *A, float *R,
+                                   float *Gamma, float *q_t, float *q_tpn, int32_t out_format, void *stream) {
+    APEX_REQUIRE(out_format == APEXB200_FMT_U8 || out_format == APEXB200_FMT_F32, APEXB200_EINVAL,
+                 "sample_gather_sharded: unknown output format %d", out_format);
     return apexb200::run_sample_gather_sharded(h, seed, global_count, max_rows, idx_out, fsel_out, pos_out, u_out,
-                                               count_out, S_t, S_tpn, A, R, Gamma, q_t, q_tpn, nullptr, 0u,
-                                               (cudaStream_t)stream);
+                                               count_out, (uint8_t *)S_t, (uint8_t *)S_tpn, A, R, Gamma, q_t, q_tpn,
+                                               nullptr, 0u, (cudaStream_t)stream, out_format);
 }
 
 }  // extern "C"

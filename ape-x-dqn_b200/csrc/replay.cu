@@ -519,6 +519,61 @@ int apexb200_host_step(apexb200_replay_t h, int32_t slot, const double *u_host, 
     return APEXB200_OK;
 }
 
+int apexb200_host_step_sharded(apexb200_replay_t h, int32_t slot, uint64_t seed, int32_t global_count, int32_t max_rows,
+                               const float *q_host, int32_t num_actions, float eps, int32_t loss_kind, float kappa,
+                               uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R, float *Gamma, float *result_host,
+                               void *done_event, void *stream) {
+    APEX_REQUIRE(h && q_host && result_host && S_t && S_tpn && A && R && Gamma, APEXB200_EINVAL,
+                 "host_step_sharded: null argument");
+    APEX_REQUIRE(slot >= 0 && slot < APEXB200_HOST_STEP_SLOTS, APEXB200_EINVAL,
+                 "host_step_sharded: slot must be in [0, %d)", APEXB200_HOST_STEP_SLOTS);
+    APEX_REQUIRE(global_count > 0 && max_rows > 0 && num_actions >= 1 && num_actions <= APEXB200_MAX_ACTIONS,
+                 APEXB200_ERANGE, "host_step_sharded: global_count=%d / max_rows=%d / num_actions=%d out of range",
+                 global_count, max_rows, num_actions);
+    APEX_REQUIRE(sample_gather_is_fused(h), APEXB200_ERANGE,
+                 "host_step_sharded: half a record does not fit one CTA's staging (no fused sharded kernel)");
+    {
+        const int world = h->peers.world > 0 ? h->peers.world : 1;
+        long long share = ((long long)global_count + world - 1) / world;
+        share += (share + 7) / 8 + 2;
+        APEX_REQUIRE(max_rows <= 1024 || share <= 1024, APEXB200_ERANGE,
+                     "host_step_sharded: the single-CTA TD kernel needs max_rows <= 1024 or a fair share <= 1024 rows");
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t M = (size_t)max_rows;
+    const size_t in_bytes = (size_t)3 * M * num_actions * 4;
+    const size_t out_words = 5 * M + 4;
+    int prc = host_step_prepare(h, in_bytes, out_words * 4);
+    if (prc) return prc;
+    float *d_q = (float *)h->hs_in[slot];
+    float *d_res = h->hs_out[slot];
+    // copy-in stream: the staging of this slot is free once the kernels of its previous use are done
+    APEX_CUDA(cudaStreamWaitEvent(h->hs_copy_in, h->hs_ev_k[slot], 0));
+    APEX_CUDA(cudaMemcpyAsync(d_q, q_host, in_bytes, cudaMemcpyHostToDevice, h->hs_copy_in));
+    unsigned *ready = (unsigned *)(h->status + 48 + slot);
+    const unsigned tick = ++h->hs_seq[slot];
+    h->hs_seq_host[slot] = tick;
+    APEX_CUDA(cudaMemcpyAsync(ready, h->hs_seq_host + slot, sizeof(unsigned), cudaMemcpyHostToDevice, h->hs_copy_in));
+    // compute stream: this slot's previous results have left the device
+    APEX_CUDA(cudaStreamWaitEvent(st, h->hs_ev_out[slot], 0));
+    float *d_delta = d_res, *d_prio = d_res + M, *d_loss = d_res + 2 * M, *d_mean = d_res + 5 * M;
+    int32_t *d_idx = (int32_t *)(d_res + 3 * M), *d_pos = (int32_t *)(d_res + 4 * M), *d_count = (int32_t *)(d_res + 5 * M + 1);
+    int rc = run_sample_gather_sharded(h, seed, global_count, max_rows, d_idx, nullptr, d_pos, nullptr, d_count, S_t, S_tpn,
+                                       A, R, Gamma, nullptr, nullptr, ready, tick, st);
+    if (rc) return rc;
+    const size_t qs = M * num_actions;
+    rc = apexb200_td_fwd_update(h, d_idx, d_q, d_q + qs, d_q + 2 * qs, A, R, Gamma, max_rows, num_actions, eps, loss_kind,
+                                kappa, nullptr, d_delta, d_prio, d_loss, d_mean, nullptr, 0, d_count, (float)global_count,
+                                stream);
+    if (rc) return rc;
+    APEX_CUDA(cudaEventRecord(h->hs_ev_k[slot], st));
+    APEX_CUDA(cudaStreamWaitEvent(h->hs_copy_out, h->hs_ev_k[slot], 0));
+    APEX_CUDA(cudaMemcpyAsync(result_host, d_res, out_words * 4, cudaMemcpyDeviceToHost, h->hs_copy_out));
+    APEX_CUDA(cudaEventRecord(h->hs_ev_out[slot], h->hs_copy_out));
+    if (done_event) APEX_CUDA(cudaEventRecord((cudaEvent_t)done_event, h->hs_copy_out));
+    return APEXB200_OK;
+}
+
 int apexb200_host_register(void *address_host, uint64_t bytes) {
     APEX_REQUIRE(address_host && bytes > 0, APEXB200_EINVAL, "host_register: null or empty range");
     cudaError_t e = cudaHostRegister(address_host, bytes, cudaHostRegisterDefault);

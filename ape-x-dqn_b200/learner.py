@@ -93,6 +93,9 @@ class Learner(object):
         self.loss_kind = _C.LOSS_HUBER if self.params.get("loss", "half_sq") == "huber" else _C.LOSS_HALF_SQ
         self.kappa = float(self.params.get("huber_kappa", 1.0))
         self.alpha = float(self.params.get("priority_exponent", getattr(shared_replay_memory, "alpha", 0.6)))
+        # learner.py:37-38 hands the model float32 states.  "f32" (default): the gather kernel writes the float32
+        # batch itself; "u8": uint8 gather followed by two .float() passes (the round-1 path, kept for comparison).
+        self.batch_f32 = self.params.get("batch_format", "f32") != "u8"
         self.device = None
 
     # ------------------------------------------------------------------ helpers
@@ -108,6 +111,17 @@ class Learner(object):
 
     def _fast(self):
         return isinstance(self.replay_memory, ReplayMemory)
+
+    def _f32(self):
+        """Float32 batches straight from the gather when the fused kernel can stage half a record (C <= 8)."""
+        m = self.replay_memory
+        return bool(self.batch_f32 and m.C <= 8 and m.C * m.F + 256 <= 226 * 1024)
+
+    @staticmethod
+    def _states(b, shape):
+        if b.S_t.dtype == torch.float32:
+            return b.S_t.view(shape), b.S_tpn.view(shape)
+        return b.S_t.view(shape).float(), b.S_tpn.view(shape).float()
 
     def _loss_from_tensors(self, S_t, S_tpn, A, R, Gamma, replay=None, idx=None, count_dev=None, mean_divisor=0.0):
         with torch.no_grad():                                                  # learner.py:43-45
@@ -146,9 +160,9 @@ class Learner(object):
         """One learner step with the batch resident in HBM: K3 -> K4 -> model -> K5+K2 -> optimiser."""
         self._to_device()
         B = int(self.params["replay_sample_size"])
-        b = self.replay_memory.sample_tensors(B, u=u)
+        b = self.replay_memory.sample_tensors(B, u=u, f32=self._f32())
         shape = (B,) + tuple(self.state_shape)
-        S_t, S_tpn = b.S_t.view(shape).float(), b.S_tpn.view(shape).float()
+        S_t, S_tpn = self._states(b, shape)
         loss, delta, prio, _ = self._loss_from_tensors(S_t, S_tpn, b.A, b.R, b.Gamma, replay=self.replay_memory, idx=b.idx)
         self.update_Q(loss)
         return loss.detach()              # no autograd graph leaves this call (capture_step needs them all gone)
@@ -196,9 +210,9 @@ class Learner(object):
 
     def _step_body(self):
         B = int(self.params["replay_sample_size"])
-        b = self.replay_memory.sample_tensors(B)
+        b = self.replay_memory.sample_tensors(B, f32=self._f32())
         shape = (B,) + tuple(self.state_shape)
-        S_t, S_tpn = b.S_t.view(shape).float(), b.S_tpn.view(shape).float()
+        S_t, S_tpn = self._states(b, shape)
         loss, _delta, _prio, _ = self._loss_from_tensors(S_t, S_tpn, b.A, b.R, b.Gamma, replay=self.replay_memory, idx=b.idx)
         return loss
 
@@ -334,12 +348,13 @@ class ShardedLearner(Learner):
     def step_sharded(self):
         if not self._ready:
             self.setup()
-        batch, _pos, cnt = self.sampler.sample_fused(self.global_batch, self.max_rows)
+        batch, _pos, cnt = self.sampler.sample_fused(self.global_batch, self.max_rows, f32=self._f32())
         n = int(cnt.item())                                   # this step's live rows (synchronises on the sample)
         self.last_rows = n
         rows = max(n, 1)                                      # a rank that owns no draw still takes part in the collectives
         shape = (rows,) + tuple(self.state_shape)
-        S_t, S_tpn = batch.S_t[:rows].view(shape).float(), batch.S_tpn[:rows].view(shape).float()
+        S_t, S_tpn = (x[:rows].view(shape) if x.dtype == torch.float32 else x[:rows].view(shape).float()
+                      for x in (batch.S_t, batch.S_tpn))
         loss, _delta, _prio, _ = self._loss_from_tensors(S_t, S_tpn, batch.A[:rows], batch.R[:rows], batch.Gamma[:rows],
                                                          replay=self.replay_memory, idx=batch.idx[:rows], count_dev=cnt,
                                                          mean_divisor=float(self.global_batch))

@@ -106,3 +106,73 @@ class HostStepPipeline:
         s["busy"] = False
         mean, prio, idx = s["views"]
         return float(mean[0]), prio, idx
+
+
+class ShardedHostStepPipeline:
+    """HostStepPipeline for one rank of a sharded replay: Q rows arrive from pinned HOST memory, this rank's
+    share of the global batch is sampled + gathered (in-kernel stratified draws, identical on every rank), and
+    loss part / priorities / record indices / global draw positions / the row count are read back on the host.
+    One apexb200_host_step_sharded call per step.  `max_rows` (default: the whole global batch, so that no
+    draw can ever be dropped) is the number of rows the host supplies Q values for.  Collective discipline as
+    for ShardedSampler: every rank submits the same number of steps; peers connected, push-on-update enabled."""
+    DEPTH = 3
+
+    def __init__(self, sampler, global_count, num_actions, max_rows=None, loss_kind=_C.LOSS_HALF_SQ, kappa=1.0, depth=None):
+        mem = sampler.mem
+        mem._ensure()
+        if depth is not None:
+            if not 1 <= int(depth) <= _C.HOST_STEP_SLOTS:
+                raise ValueError("depth must be in [1, %d]" % _C.HOST_STEP_SLOTS)
+            self.DEPTH = int(depth)
+        self.mem, self.sampler = mem, sampler
+        self.Bg, self.nA = int(global_count), int(num_actions)
+        self.M = M = int(max_rows) if max_rows else self.Bg
+        nA = self.nA
+        self.in_bytes = 3 * M * nA * 4
+        self.out_words = 5 * M + 4
+        o = mem._outputs(M, False)
+        self._batch = o
+        self.slots = []
+        for k in range(self.DEPTH):
+            h_in = torch.empty(3 * M * nA, dtype=torch.float32).pin_memory()
+            h_out = torch.empty(self.out_words, dtype=torch.float32).pin_memory()
+            ev = torch.cuda.Event()
+            ev.record()
+            out = h_out.numpy()
+            self.slots.append(dict(
+                h_in=h_in, h_out=h_out, event=ev, busy=False, q_host=h_in.numpy().reshape(3, M, nA),
+                views=(out[5 * M:5 * M + 1], out[M:2 * M], out[3 * M:4 * M].view(np.int32), out[4 * M:5 * M].view(np.int32),
+                       out[5 * M + 1:5 * M + 2].view(np.int32)),
+                args=(mem._h, k, int(mem.seed), self.Bg, M, _C.ptr(h_in), nA, float(mem.eps), int(loss_kind), float(kappa),
+                      _C.ptr(o["S_t"]), _C.ptr(o["S_tpn"]), _C.ptr(o["A"]), _C.ptr(o["R"]), _C.ptr(o["Gamma"]),
+                      _C.ptr(h_out), _C.C.c_void_p(ev.cuda_event), _C.stream_ptr())))
+        self._host_step = _C.lib().apexb200_host_step_sharded
+        self._k = 0
+        torch.cuda.current_stream().synchronize()
+
+    def submit(self, q, rows=None):
+        """q: float32 [3, rows, nA] host array — Q(S_t), Q(S_tpn), Q_target(S_tpn) for the first `rows` rows this
+        rank will own (rows defaults to max_rows).  Returns a ticket for result()."""
+        s = self.slots[self._k % self.DEPTH]
+        if s["busy"]:
+            s["event"].synchronize()
+        if rows is None:
+            s["q_host"][:] = q
+        else:
+            s["q_host"][:, :rows] = q
+        rc = self._host_step(*s["args"])
+        if rc:
+            _C.check(rc)
+        s["busy"] = True
+        self._k += 1
+        return self._k - 1
+
+    def result(self, ticket):
+        """Blocks until step `ticket` has finished; returns (loss part, priorities[n], record indices[n],
+        global draw positions[n], n) as host views, n = rows this rank owned in that step."""
+        s = self.slots[ticket % self.DEPTH]
+        s["event"].synchronize()
+        s["busy"] = False
+        mean, prio, idx, pos, cnt = s["views"]
+        n = int(cnt[0])
+        return float(mean[0]), prio[:n], idx[:n], pos[:n], n

@@ -294,16 +294,17 @@ class ReplayMemory(object):
         _C.call("apexb200_replay_insert_lanes", self._h, lanes, E, T, _C.ptr(frames), _C.ptr(rel), _C.ptr(A), _C.ptr(R),
                 _C.ptr(Gamma), _C.ptr(prio), _C.ptr(q_t), _C.ptr(q_tpn), self._stream())
 
-    def _outputs(self, B, with_q):
+    def _outputs(self, B, with_q, f32=False):
         import torch
-        key = (B, with_q)
+        key = (B, with_q) if not f32 else (B, with_q, "f32")
         out = self._out_cache.get(key)
         if out is None:
             d = self.device
+            sdt = torch.float32 if f32 else torch.uint8
             out = dict(idx=torch.empty(B, dtype=torch.int32, device=d),
                        fsel=torch.empty((B, 2 * self.C), dtype=torch.int32, device=d),
-                       S_t=torch.empty((B, self.C, self.F), dtype=torch.uint8, device=d),
-                       S_tpn=torch.empty((B, self.C, self.F), dtype=torch.uint8, device=d),
+                       S_t=torch.empty((B, self.C, self.F), dtype=sdt, device=d),
+                       S_tpn=torch.empty((B, self.C, self.F), dtype=sdt, device=d),
                        A=torch.empty(B, dtype=torch.int32, device=d),
                        R=torch.empty(B, dtype=torch.float32, device=d),
                        Gamma=torch.empty(B, dtype=torch.float32, device=d),
@@ -356,21 +357,25 @@ class ReplayMemory(object):
                 _C.ptr(total_out), _C.ptr(fsel_out), _C.ptr(u_out), self._stream())
         return idx_out
 
-    def sample_tensors(self, batch_size, u=None, with_q=False, u_out=None, fused=True):
+    def sample_tensors(self, batch_size, u=None, with_q=False, u_out=None, fused=True, f32=False):
         """ReplayMemory.sample on the device: draw `batch_size` records and gather them into
         [B, C, F] uint8 batch tensors (K3 + K4, one fused launch unless fused=False).
 
         u: CUDA float64 uniforms in [0,1); None = stratified draws generated inside the kernel
-        (written to u_out if given).  The returned tensors are reused by the next call with the
-        same batch size.
+        (written to u_out if given).  f32=True: S_t / S_tpn come back as float32 [B, C, F] — the dtype
+        the network consumes (learner.py:37-38), every byte widened exactly by the gather kernel itself
+        (fused kernel only).  The returned tensors are reused by the next call with the same batch size.
         """
         self._ensure()
         B = int(batch_size)
-        o = self._outputs(B, with_q)
+        o = self._outputs(B, with_q, f32)
+        if f32 and not fused:
+            raise ValueError("float32 batches are written by the fused sample+gather kernel only")
         if fused:
             _C.call("apexb200_sample_gather", self._h, _C.ptr(u), self.seed, B, _C.ptr(o["idx"]), _C.ptr(o["fsel"]),
                     None, None, _C.ptr(u_out), _C.ptr(o["S_t"]), _C.ptr(o["S_tpn"]), _C.ptr(o["A"]), _C.ptr(o["R"]),
-                    _C.ptr(o["Gamma"]), _C.ptr(o.get("q_t")), _C.ptr(o.get("q_tpn")), self._stream())
+                    _C.ptr(o["Gamma"]), _C.ptr(o.get("q_t")), _C.ptr(o.get("q_tpn")),
+                    _C.FMT_F32 if f32 else _C.FMT_U8, self._stream())
             self._last_q = (o["q_t"], o["q_tpn"]) if with_q and o.get("q_t") is not None else None
             return Batch(o["idx"], o["S_t"], o["S_tpn"], o["A"], o["R"], o["Gamma"], o["fsel"])
         if u is None:

@@ -100,7 +100,7 @@ class ShardedSampler:
         from . import _C
         _C.call("apexb200_shard_exchange", self.mem._h, _C.ptr(totals_out), _C.stream_ptr())
 
-    def sample_fused(self, global_count, max_rows=None, with_q=False, u_out=None):
+    def sample_fused(self, global_count, max_rows=None, with_q=False, u_out=None, f32=False):
         """Fused routing + search + gather of this rank's share of `global_count` stratified draws
         generated in the kernel (identical on every rank).  Returns (Batch over max_rows rows,
         pos [max_rows] global draw index per row, count [1] rows owned).  max_rows defaults to
@@ -112,14 +112,14 @@ class ShardedSampler:
         mem = self.mem
         if max_rows is None:
             max_rows = int(global_count)
-        o = mem._outputs(int(max_rows), with_q)
+        o = mem._outputs(int(max_rows), with_q, f32)               # f32: float32 batches, as in sample_tensors
         if "pos" not in o:
             o["pos"] = torch.empty(int(max_rows), dtype=torch.int32, device=mem.device)
             o["count"] = torch.zeros(1, dtype=torch.int32, device=mem.device)
         _C.call("apexb200_sample_gather_sharded", mem._h, mem.seed, int(global_count), int(max_rows), _C.ptr(o["idx"]),
                 _C.ptr(o["fsel"]), _C.ptr(o["pos"]), _C.ptr(u_out), _C.ptr(o["count"]), _C.ptr(o["S_t"]),
                 _C.ptr(o["S_tpn"]), _C.ptr(o["A"]), _C.ptr(o["R"]), _C.ptr(o["Gamma"]), _C.ptr(o.get("q_t")),
-                _C.ptr(o.get("q_tpn")), _C.stream_ptr())
+                _C.ptr(o.get("q_tpn")), _C.FMT_F32 if f32 else _C.FMT_U8, _C.stream_ptr())
         return Batch(o["idx"], o["S_t"], o["S_tpn"], o["A"], o["R"], o["Gamma"], o["fsel"]), o["pos"], o["count"]
 
     def sample(self, u_global, out=None, with_q=False):

@@ -18,7 +18,21 @@ import sys
 import threading
 import time
 
-import numpy as np
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+if "reference" in sys.argv:
+    # The CPU arm uses every host core it can, also under torchrun (which exports OMP_NUM_THREADS=1 to its
+    # workers): the OpenMP / BLAS pools read these variables when numpy and torch are first imported.
+    for _v in ("OMP_NUM_THREADS", "MKL_NUM_THREADS", "OPENBLAS_NUM_THREADS"):
+        os.environ[_v] = str(host_threads())
+
+import numpy as np   # noqa: E402
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -27,7 +41,11 @@ if ROOT not in sys.path:
 F_BYTES = 7056          # 84 x 84 uint8
 ALPHA = 0.6
 GAMMA_N = 0.99 ** 3
-NCU_DRAM_BYTES_PER_LAUNCH = 26_050_000      # sample_gather_kernel, B=512, C=4 (profiles/r01_ncu_full_sample_gather.csv)
+NCU_DRAM_BYTES_PER_LAUNCH = 26_050_000      # sample_gather_kernel, B=512, C=4 (profiles/r01_ncu_full_sample_gather_final.csv)
+NCU_TRAFFIC_SOURCE = ("profiles/r01_ncu_full_sample_gather_final.csv (ncu --set full, B=512, C=4: "
+                      "dram__bytes_read.sum 25.8 MB + dram__bytes_write.sum 0.27 MB per launch)")
+METRIC = "prioritized sample+update transitions/s (2M cap, B=512)"
+DTYPE = "u8 frames / u64 fixed-point tree / f32 TD"
 
 
 def parse():
@@ -47,6 +65,9 @@ def parse():
     ap.add_argument("--no-graph", action="store_true", help="launch every step from Python instead of a CUDA graph")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the CPU-baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-learner-loop", action="store_true", help="skip the short learner-loop (configs[2]) extra key")
+    ap.add_argument("--min-ms", type=float, default=50.0,
+                    help="repeat the K-step block until at least this much time has been measured; the median block is reported")
     ap.add_argument("--nccl-exchange", action="store_true",
                     help="multi-GPU: all-gather the shard totals with NCCL + separate routing/search/gather kernels "
                          "instead of the peer-memory exchange + fused sharded kernel")
@@ -133,6 +154,35 @@ def fill_shard(torch, apex, mem, args, dev, seed):
     torch.cuda.synchronize()
 
 
+def config_dict(args, world):
+    """The workload description both arms print (a function of the command line and the rank count only)."""
+    N, B, C = args.capacity, args.batch, args.frames_per_state
+    fused = not args.unfused
+    peer_path = world > 1 and not args.nccl_exchange
+    graph = (not args.no_graph) and (world == 1 or peer_path)
+    return {"workload": "replay microbench: %d-record shard per GPU, batch %d per GPU, C=%d 84x84 uint8, "
+                        "n=3, alpha=%.1f; sample(K3)+gather(K4)+TD/loss(K5)+priority update(K2) per step" % (N, B, C, ALPHA),
+            "capacity_per_gpu": N, "batch_per_gpu": B, "frames_per_state": C, "lanes": args.lanes,
+            "launch": "cuda graph of 4 steps" if graph else "python loop",
+            "kernels_per_step": ("sample_gather_kernel + td_small_kernel" if fused else
+                                 "tree_sample_kernel + gather kernel (variant %d) + td_small_kernel" % args.gather_variant)
+            if world == 1 else ("sample_gather_sharded_kernel + td_small_kernel" if peer_path else
+                                "nccl all-gather + shard_targets + tree_sample + gather + td kernels"),
+            "pdl": not args.no_pdl,
+            "l2": "frame store %.1f GB >> 126 MB L2 (random gathers miss); the %.1f MB tree is L2-resident by design"
+                  % (N * F_BYTES / 1e9, N * 8 * 33 / 32 / 1e6),
+            "parallelism": ("1 shard per GPU; every rank's TD/update kernel pushes its new shard total into all peers' "
+                            "memory over NVLink, the next fused routing+search+gather kernel waits for them (no NCCL on "
+                            "the step path; outputs hold the whole global batch: a rank receives every draw it owns)"
+                            if peer_path else "1 shard per GPU, NCCL all-gather of shard totals")
+            if world > 1 else "single shard"}
+
+
+def block_stats(ms_list):
+    v = sorted(ms_list)
+    return v[len(v) // 2], v[0], v[-1]
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -196,8 +246,16 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def max_over_ranks(values):
+        if world == 1:
+            return [float(v) for v in values]
+        t = torch.tensor(list(values), device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(v) for v in t.tolist()]
+
     use_graph = (not args.no_graph) and (world == 1 or peer_path)   # the NCCL path stays a python loop
-    for k in range(max(args.warmup, 3)):
+    W = max(args.warmup, 3)
+    for k in range(W):
         step(k)
     torch.cuda.synchronize()
     graph = None
@@ -215,65 +273,95 @@ def run_ours(args):
             graph.replay()
         torch.cuda.synchronize()
 
+    # ---- parity round at the bench size, before anything is timed (the oracle is the checker here)
+    parity = parity_round(torch, dist, apex_b200, mem, sampler, args, dev, rank, world, peer_path)
+
+    # ---- device-timed region: blocks of EXACTLY K steps, each bracketed by barrier + synchronize on both sides and
+    # timed with CUDA events; the block is repeated until >= 50 ms of device time has been measured (a single
+    # block of the driver's K=20 is 0.3 ms); value = the MEDIAN block, max over ranks per block.
     K = args.steps
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e0.record()
-    if graph is not None:
-        for _ in range(K // P):
-            graph.replay()
-        for k in range(K % P):
-            step(k)
-    else:
-        for k in range(K):
-            step(k)
-    e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
-    if world > 1:
-        t = torch.tensor([ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+
+    def timed_block():
+        barrier()
+        e0.record()
+        if graph is not None:
+            for _ in range(K // P):
+                graph.replay()
+            for k in range(K % P):
+                step(k)
+        else:
+            for k in range(K):
+                step(k)
+        e1.record()
+        barrier()
+        return e0.elapsed_time(e1)
+
+    pilot = max_over_ranks([timed_block()])[0]
+    n_blocks = int(min(400, max(3, -(-args.min_ms // max(pilot, 1e-3)))))
+    blocks = max_over_ranks([timed_block() for _ in range(n_blocks)])
+    ms, ms_min, ms_max = block_stats(blocks)
     launches_per_step = (2 if fused else 3) if world == 1 else (2 if peer_path else 5 + (1 if Bg > 1024 else 0))
     value = K * Bg / (ms * 1e-3)
+    timing = {"blocks": n_blocks, "steps_per_block": K, "block_ms_median": round(ms, 5), "block_ms_min": round(ms_min, 5),
+              "block_ms_max": round(ms_max, 5), "device_ms_total": round(sum(blocks), 3),
+              "how": "each block = exactly K steps between barrier+synchronize, CUDA events, max over ranks; median block reported"}
 
-    # ---- roofline of the dominant kernel (fused K3+K4 sample_gather, or K4 alone with --unfused).
-    # (a) launch duration: CUDA events around a CUDA graph of R back-to-back launches of that kernel
-    #     (fresh draws every launch, 16 x 28.9 MB of distinct source frames per replay >> L2), / launches;
-    # (b) the same kernel timed in place with an event pair per launch in an eager pass of the full
-    #     step (reported for reference: an event pair adds ~4-5 us to a ~12 us kernel).
+    # ---- roofline of the dominant kernel (fused K3+K4, single-GPU or sharded form; K4 alone with --unfused).
+    # Launch duration: CUDA events around replays of a CUDA graph of R back-to-back launches of that kernel
+    # (fresh draws every launch, R x 28.9 MB of distinct source frames per replay >> L2), / launches.
     peak, peak_src = peaks()
     bytes_per_rec = 4 * C * F_BYTES + 32
     roofline = None
     multi = None
+
+    def graph_of(fn, reps_in=16, replays=25):
+        sd = torch.cuda.Stream()
+        sd.wait_stream(torch.cuda.current_stream())
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(sd):
+            with torch.cuda.graph(g, stream=sd):
+                for r in range(reps_in):
+                    fn(r)
+        torch.cuda.current_stream().wait_stream(sd)
+        for _ in range(3):
+            g.replay()
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(replays):
+            g.replay()
+        a1.record()
+        barrier()
+        return a0.elapsed_time(a1) * 1e3 / (reps_in * replays)
+
     if peer_path:
-        def graph_of(fn, reps_in=16):
-            sd = torch.cuda.Stream()
-            sd.wait_stream(torch.cuda.current_stream())
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.stream(sd):
-                with torch.cuda.graph(g, stream=sd):
-                    for _ in range(reps_in):
-                        fn()
-            torch.cuda.current_stream().wait_stream(sd)
-            for _ in range(3):
-                g.replay()
-            barrier()
-            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a0.record()
-            for _ in range(20):
-                g.replay()
-            a1.record()
-            barrier()
-            return a0.elapsed_time(a1) * 1e3 / (reps_in * 20)
         sampler.push_on_update(False)
-        multi = {"shard_exchange_us": round(graph_of(sampler.exchange), 3),
-                 "sample_gather_sharded_us": round(graph_of(lambda: sampler.sample_fused(Bg, max_rows)), 3)}
+        counts = []
+        for _ in range(8):
+            _b, _p, c_ = sampler.sample_fused(Bg, max_rows)
+            counts.append(int(c_.item()))
+        rows_owned = sum(counts) / len(counts)
+        x_us = graph_of(lambda r: sampler.exchange())
+        s_us = max_over_ranks([graph_of(lambda r: sampler.sample_fused(Bg, max_rows))])[0]
         sampler.push_on_update(not args.no_push)
+        sampler.exchange()
+        rows_all = max_over_ranks([rows_owned])[0]
+        ach = bytes_per_rec * rows_owned / (s_us * 1e-6) / 1e9
+        roofline = {"kernel": "sample_gather_sharded_kernel", "bound": "hbm", "achieved": round(ach, 1), "peak": peak,
+                    "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": None,
+                    "algorithmic_bytes_per_launch": int(bytes_per_rec * rows_owned), "rows_owned_mean_rank0": rows_owned,
+                    "rows_owned_max_over_ranks": rows_all, "launch_us_mean": round(s_us, 3),
+                    "launches_timed": 16 * 25, "peak_source": peak_src,
+                    "timing": "rank 0's rows x SURVEY 8(d) bytes / launch duration (max over ranks) from CUDA events around 25 "
+                              "replays of a CUDA graph of 16 back-to-back launches; traffic: ncu is single-GPU only, see the "
+                              "N=1 line for the DRAM byte count of the same gather",
+                    "share_of_step": round(s_us / (ms / K * 1e3), 3)}
+        multi = {"shard_exchange_us": round(x_us, 3), "sample_gather_sharded_us": round(s_us, 3)}
     if world == 1:
         o = mem._outputs(B, False)
 
-        def dominant():
+        def dominant(r=0):
             if fused:
                 mem.sample_tensors(B)
             else:
@@ -281,37 +369,28 @@ def run_ours(args):
         R_, reps = 16, 25
         dominant()
         torch.cuda.synchronize()
-        side = torch.cuda.Stream()
-        side.wait_stream(torch.cuda.current_stream())
-        gk = torch.cuda.CUDAGraph()
-        with torch.cuda.stream(side):
-            with torch.cuda.graph(gk, stream=side):
-                for _ in range(R_):
-                    if not fused:
-                        mem.sample_stratified(B, idx_out=o["idx"], fsel_out=o["fsel"])
-                    dominant()
-        torch.cuda.current_stream().wait_stream(side)
-        gs = None
-        if not fused:                                             # subtract the interleaved K3 launches
-            gs = torch.cuda.CUDAGraph()
-            with torch.cuda.stream(side):
-                with torch.cuda.graph(gs, stream=side):
-                    for _ in range(R_):
-                        mem.sample_stratified(B, idx_out=o["idx"], fsel_out=o["fsel"])
-            torch.cuda.current_stream().wait_stream(side)
 
-        def time_graph(g):
-            for _ in range(3):
-                g.replay()
-            torch.cuda.synchronize()
-            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a0.record()
-            for _ in range(reps):
-                g.replay()
-            a1.record()
-            torch.cuda.synchronize()
-            return a0.elapsed_time(a1) * 1e3 / (R_ * reps)
-        g_mean_us = time_graph(gk) - (time_graph(gs) if gs is not None else 0.0)
+        def with_k3(r):
+            if not fused:
+                mem.sample_stratified(B, idx_out=o["idx"], fsel_out=o["fsel"])
+            dominant()
+        g_mean_us = graph_of(with_k3, R_, reps)
+        if not fused:                                             # subtract the interleaved K3 launches
+            g_mean_us -= graph_of(lambda r: mem.sample_stratified(B, idx_out=o["idx"], fsel_out=o["fsel"]), R_, reps)
+        # the same launches with the OUTPUT batch rotating through R_ buffer sets (16 x 28.9 MB = 462 MB > L2):
+        # every launch's 28.9 MB of writes then has to evict a previous batch to HBM instead of overwriting an
+        # L2-resident one
+        rot_us = None
+        if fused:
+            key = (B, False)
+            sets = [dict(o)] + [{k: (v.clone() if v is not None else None) for k, v in o.items()} for _ in range(R_ - 1)]
+
+            def rotating(r):
+                mem._out_cache[key] = sets[r % R_]
+                mem.sample_tensors(B)
+            rot_us = graph_of(rotating, R_, reps)
+            mem._out_cache[key] = sets[0]
+            del sets
 
         n_r = min(K, 400)
         ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(n_r)]
@@ -336,88 +415,226 @@ def run_ours(args):
         t_us = sorted(e[1].elapsed_time(e[2]) * 1e3 for e in ev)
         del big
         ach = bytes_per_rec * B / (g_mean_us * 1e-6) / 1e9
+        traffic = NCU_DRAM_BYTES_PER_LAUNCH if (fused and B == 512 and C == 4) else None
         kname = "sample_gather_kernel" if fused else ("gather_tma_kernel" if args.gather_variant == 1 else "gather_vec_kernel")
         roofline = {"kernel": kname, "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
-                    "frac": round(ach / peak, 4),
-                    "traffic": NCU_DRAM_BYTES_PER_LAUNCH if (fused and B == 512 and C == 4) else None,
-                    "traffic_source": "profiles/r01_ncu_full_sample_gather.csv (ncu --set full, B=512, C=4: "
-                                      "dram__bytes_read.sum 25.8 MB + dram__bytes_write.sum 0.23 MB per launch)",
+                    "frac": round(ach / peak, 4), "traffic": traffic, "traffic_source": NCU_TRAFFIC_SOURCE,
+                    "dram_frac": round(traffic / (g_mean_us * 1e-6) / 1e9 / peak, 4) if traffic else None,
+                    "dram_frac_note": "traffic / launch duration / peak: the bytes DRAM itself moves per launch (the output batch "
+                                      "stays in L2 and S_t/S_tpn share one frame in eight); `frac` is the SURVEY 8(d) accounting "
+                                      "of algorithmic bytes",
                     "algorithmic_bytes_per_launch": bytes_per_rec * B,
                     "launch_us_mean": round(g_mean_us, 3), "launches_timed": R_ * reps, "peak_source": peak_src,
+                    "rotating_outputs": None if rot_us is None else {
+                        "launch_us_mean": round(rot_us, 3), "achieved": round(bytes_per_rec * B / (rot_us * 1e-6) / 1e9, 1),
+                        "frac": round(bytes_per_rec * B / (rot_us * 1e-6) / 1e9 / peak, 4),
+                        "note": "same launches, output batch rotating through %d buffer sets (%.0f MB > 126 MB L2): the "
+                                "writes reach HBM" % (R_, R_ * 2 * B * C * F_BYTES / 1e6)},
                     "timing": "cuda events around %d replays of a CUDA graph of %d back-to-back launches "
-                              "(includes one inter-launch gap per launch)" % (reps, R_),
+                              "(includes one inter-launch gap per launch); outputs reuse one L2-resident batch buffer"
+                              % (reps, R_),
                     "share_of_step": round(g_mean_us / (ms / K * 1e3), 3),
                     "in_step_event_pairs": {"launch_us_mean": round(sum(g_us) / len(g_us), 3),
                                             "launch_us_min": round(g_us[0], 3), "launches_timed": len(g_us),
                                             "td_small_kernel_us_mean": round(sum(t_us) / len(t_us), 3),
                                             "note": "event pair per launch inside an eager pass of the full step; "
                                                     "inflated by event overhead"},
-                    "note": "ncu: DRAM sees 25.5 MB read + 0.3 MB written per launch (batch stays in L2); the launch is "
-                            "bound by L2 slice throughput, see profiles/r01_kernel_experiments.md"}
+                    "note": "the launch is a chain of latencies (tree descent, frame-slot row, one HBM round trip and one L2 "
+                            "write per frame), not a saturated memory system; see profiles/"}
 
-    # ---- end to end through the host-facing API: draws and Q-values start in pinned HOST memory
-    # every step, loss / priorities / indices are read back on the host every step.
+    # ---- end to end through the host-facing C-ABI step: inputs start in pinned HOST memory every step, loss /
+    # priorities / indices (/ draw positions, row count) are read back on the host every step.  Blocks of K
+    # steps of wall-clock time, repeated until >= 50 ms, median block, max over ranks.
     e2e = None
-    if world == 1:
-        rng = np.random.default_rng(4321)
-        pipe = apex_b200.HostStepPipeline(mem, B, nA)
-        n_e = max(20, min(K, 2000))
-        q_host = rng.standard_normal((P, 3, B, nA)).astype(np.float32)
-        u_host = (np.arange(B) + rng.random((64, B))) / B         # host-side stratified draws
-        losses = 0.0
-        for k in range(8):
-            pipe.result(pipe.submit(u_host[k % 64], q_host[k % P]))
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        pending = collections.deque()
-        for k in range(n_e):
-            pending.append(pipe.submit(u_host[k % 64], q_host[k % P]))   # fills the pinned inputs, one C call
-            if len(pending) == pipe.DEPTH:
-                losses += pipe.result(pending.popleft())[0]       # host reads step k-2 while steps k-1, k are queued
-        while pending:
-            losses += pipe.result(pending.popleft())[0]
-        dt = time.perf_counter() - t0
-        e2e = {"value": round(n_e * B / dt, 1), "unit": "transitions/s", "h2d_bytes_per_step": pipe.in_bytes,
-               "d2h_bytes_per_step": pipe.out_words * 4, "steps": n_e, "ms_per_step": round(dt / n_e * 1e3, 4),
-               "api": "apex_b200.HostStepPipeline.submit(u_host, q_host)/result() -> C ABI apexb200_host_step: pinned H2D of "
-                      "draws+Q on a copy stream, fused sample+gather, TD+update, D2H of loss/priorities/indices on a copy "
-                      "stream, ordered by events; every step's results are read on the host, %d steps behind (%d buffer sets)"
-                      % (pipe.DEPTH - 1, pipe.DEPTH),
-               "mean_loss": round(losses / n_e, 6)}
+    if world == 1 or peer_path:
+        rng = np.random.default_rng(4321 + rank)
+        if world == 1:
+            pipe = apex_b200.HostStepPipeline(mem, B, nA)
+            q_host = rng.standard_normal((P, 3, B, nA)).astype(np.float32)
+            u_host = (np.arange(B) + rng.random((64, B))) / B     # host-side stratified draws
+
+            def submit(k):
+                return pipe.submit(u_host[k % 64], q_host[k % P])  # fills the pinned inputs, one C call
+        else:
+            pipe = apex_b200.ShardedHostStepPipeline(sampler, Bg, nA, max_rows=max_rows)
+            q_host = rng.standard_normal((P, 3, max_rows, nA)).astype(np.float32)
+
+            def submit(k):
+                return pipe.submit(q_host[k % P])
+        state = {"loss": 0.0, "rows": 0, "rows_max": 0}
+
+        def take(ticket):
+            r = pipe.result(ticket)
+            state["loss"] += r[0]
+            if world > 1:
+                state["rows"] += r[4]
+                state["rows_max"] = max(state["rows_max"], r[4])
+
+        def e2e_run(n_blocks):
+            """(n_blocks + 1) x K steps through the pipeline without draining it in between; a wall-clock stamp is
+            taken whenever another K results have been read on the host.  The first K steps are the ramp; the
+            differences between later stamps are steady-state blocks of exactly K steps."""
+            barrier()
+            pending, stamps, taken = collections.deque(), [], 0
+            for k in range((n_blocks + 1) * K):
+                pending.append(submit(k))
+                if len(pending) == pipe.DEPTH:
+                    take(pending.popleft())                       # host reads step k-2 while steps k-1, k are queued
+                    taken += 1
+                    if taken % K == 0:
+                        stamps.append(time.perf_counter())
+            while pending:
+                take(pending.popleft())
+                taken += 1
+                if taken % K == 0:
+                    stamps.append(time.perf_counter())
+            barrier()
+            return [(b - a) * 1e3 for a, b in zip(stamps, stamps[1:])]
+        pilot_e = max_over_ranks([block_stats(e2e_run(2))[0]])[0]
+        n_eb = int(min(2000, max(3, -(-args.min_ms // max(pilot_e, 1e-3)))))
+        state.update(loss=0.0, rows=0, rows_max=0)
+        eb = max_over_ranks(e2e_run(n_eb))
+        em, emin, emax = block_stats(eb)
+        n_taken = (n_eb + 1) * K
+        e2e = {"value": round(K * Bg / (em * 1e-3), 1), "unit": "transitions/s", "h2d_bytes_per_step": pipe.in_bytes,
+               "d2h_bytes_per_step": pipe.out_words * 4, "steps": K, "ms_per_step": round(em / K, 5),
+               "blocks": n_eb, "block_ms_median": round(em, 4), "block_ms_min": round(emin, 4), "block_ms_max": round(emax, 4),
+               "api": ("apex_b200.HostStepPipeline.submit(u_host, q_host)/result() -> C ABI apexb200_host_step: pinned H2D of "
+                       "draws+Q on a copy stream, fused sample+gather, TD+update, D2H of loss/priorities/indices on a copy "
+                       "stream, ordered by events" if world == 1 else
+                       "apex_b200.ShardedHostStepPipeline.submit(q_host)/result() -> C ABI apexb200_host_step_sharded on every rank: "
+                       "pinned H2D of Q rows for the whole global batch (%d rows: no quota), fused sharded routing+search+gather "
+                       "(draws generated in-kernel, identical on every rank), TD+update+total push, D2H of loss/priorities/"
+                       "indices/draw positions/row count" % max_rows) +
+                      "; every step's results are read on the host, %d steps behind (%d buffer sets); wall clock, bytes are "
+                      "per rank" % (pipe.DEPTH - 1, pipe.DEPTH),
+               "mean_loss": round(state["loss"] / n_taken, 6),
+               "how": "one continuous run of (blocks + 1) x K pipelined steps; wall-clock stamp every K results read on "
+                      "the host; first K steps (ramp) discarded; median block, max over ranks per block"}
+        if world > 1:
+            e2e["rows_owned_mean_rank0"] = round(state["rows"] / n_taken, 2)
+            e2e["rows_owned_max_rank0"] = state["rows_max"]
     clk = clocks.stop()
     mem.check_status()
+
+    learner_loop = None
+    if rank == 0 and world == 1 and fused and not args.no_learner_loop:
+        learner_loop = learner_loop_short(torch, apex_b200, mem, args, dev)
 
     cpu, cpu_c = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu, cpu_c = cpu_baseline_from_device(torch, mem, args, dev)
 
     if rank == 0:
+        ref = lambda a, b: round(a / b, 2) if (a and b) else None           # noqa: E731
         line = {
-            "metric": "prioritized sample+update transitions/s (2M cap, B=512)", "value": round(value, 1),
-            "unit": "transitions/s", "n_gpus": world, "steps": K, "warmup": max(args.warmup, 3),
-            "ms_per_step": round(ms / K, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "u8 frames / u64 fixed-point tree / f32 TD", "data": "synthetic",
-            "config": {"workload": "replay microbench: %d-record shard per GPU, batch %d per GPU, C=%d 84x84 uint8, "
-                                   "n=3, alpha=%.1f; sample(K3)+gather(K4)+TD/loss(K5)+priority update(K2) per step"
-                                   % (N, B, C, ALPHA),
-                       "capacity_per_gpu": N, "batch_per_gpu": B, "frames_per_state": C, "lanes": args.lanes,
-                       "launch": "cuda graph of %d steps" % P if graph is not None else "python loop",
-                       "kernels_per_step": "sample_gather_kernel + td_small_kernel" if fused else
-                                           "tree_sample_kernel + gather kernel (variant %d) + td_small_kernel" % args.gather_variant,
-                       "pdl": not args.no_pdl,
-                       "l2": "frame store %.1f GB >> 126 MB L2 (random gathers miss); the %.1f MB tree is L2-resident by design"
-                             % (N * F_BYTES / 1e9, N * 8 * 33 / 32 / 1e6),
-                       "parallelism": ("1 shard per GPU; every rank's TD/update kernel pushes its new shard total into all peers' "
-                                       "memory over NVLink, the next fused routing+search+gather kernel waits for them "
-                                       "(no NCCL on the step path; quota %d rows per rank)" % max_rows
-                                       if peer_path else "1 shard per GPU, NCCL all-gather of shard totals")
-                       if world > 1 else "single shard"},
-            "gpu_launches": K * launches_per_step, "clocks": clk, "roofline": roofline, "multi_gpu_kernels": multi, "e2e": e2e, "cpu_baseline": cpu,
-            "cpu_baseline_c_openmp": cpu_c,
+            "metric": METRIC, "value": round(value, 1),
+            "unit": "transitions/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": round(ms / K, 6), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": DTYPE, "data": "synthetic", "config": config_dict(args, world),
+            "gpu_launches": K * launches_per_step, "timing": timing, "parity": parity, "clocks": clk, "roofline": roofline,
+            "multi_gpu_kernels": multi, "e2e": e2e, "cpu_baseline": cpu, "cpu_baseline_c_openmp": cpu_c,
+            "vs_cpu_c_openmp": None if not cpu_c else {"e2e_ratio": ref(e2e and e2e["value"], cpu_c["value"]),
+                                                      "value_ratio": ref(value, cpu_c["value"]),
+                                                      "note": "ours / the hand-written C+OpenMP port on this box's cores "
+                                                              "(a stricter baseline than the reference's numpy/torch path)"},
+            "learner_loop": learner_loop,
         }
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def parity_round(torch, dist, apex, mem, sampler, args, dev, rank, world, peer_path):
+    """One sample at the bench size checked against the oracle: record indices bit-exact against the cumulative
+    search over the (concatenated) leaves for the same draws, every gathered byte equal to the frame store."""
+    from apex_b200 import _C
+    from oracle import replay_oracle as ro
+    B, C, N = args.batch, args.frames_per_state, args.capacity
+    Bg = B * world
+    store = mem.buffer(_C.BUF_FRAMES).view(-1, F_BYTES)
+    fidx = mem.buffer(_C.BUF_FIDX).view(N, 2 * C)
+    leaves = mem.buffer(_C.BUF_LEAVES).clone()
+
+    def bytes_ok(b, n):
+        sel = b.fsel[:n].long()
+        ok = torch.equal(b.fsel[:n], fidx.index_select(0, b.idx[:n].long()))
+        ok &= torch.equal(b.S_t[:n].reshape(n * C, F_BYTES), store.index_select(0, sel[:, :C].reshape(-1)))
+        ok &= torch.equal(b.S_tpn[:n].reshape(n * C, F_BYTES), store.index_select(0, sel[:, C:].reshape(-1)))
+        for name, which in (("A", _C.BUF_ACTION), ("R", _C.BUF_REWARD), ("Gamma", _C.BUF_GAMMA)):
+            ok &= torch.equal(getattr(b, name)[:n], mem.buffer(which).index_select(0, b.idx[:n].long()))
+        return bool(ok)
+
+    if world == 1:
+        u_out = torch.empty(B, dtype=torch.float64, device=dev)
+        b = mem.sample_tensors(B, u_out=u_out)
+        want = ro.tree_sample(leaves.cpu().numpy().view(np.uint64), u_out.cpu().numpy())
+        return {"indices_bit_exact": bool((b.idx.cpu().numpy() == want).all()), "bytes_exact": bytes_ok(b, B), "world": 1,
+                "draws": B, "records": N, "checked_against": "oracle.replay_oracle.tree_sample (searchsorted(cumsum(leaves), "
+                "target, 'right')) on the device's leaves and the kernel's own draws; every gathered byte vs the frame store"}
+    if not peer_path:
+        return None
+    u_out = torch.zeros(Bg, dtype=torch.float64, device=dev)
+    b, pos, cnt = sampler.sample_fused(Bg, u_out=u_out)
+    n = int(cnt.item())
+    u_glob = torch.zeros(Bg, dtype=torch.float64, device=dev)
+    owner = torch.zeros(Bg, dtype=torch.int64, device=dev)
+    u_glob[pos[:n].long()] = u_out[:n]
+    owner[pos[:n].long()] = 1
+    dist.all_reduce(u_glob)
+    dist.all_reduce(owner)
+    every = [torch.empty_like(leaves) for _ in range(world)]
+    dist.all_gather(every, leaves)
+    whole = ro.tree_sample(torch.cat(every).cpu().numpy().view(np.uint64), u_glob.cpu().numpy())
+    mine = np.nonzero(whole // N == rank)[0]
+    idx_ok = bool((owner == 1).all().item()) and n == len(mine) and bool((pos.cpu().numpy()[:n] == mine).all()) and \
+        bool((b.idx.cpu().numpy()[:n] == whole[mine] % N).all())
+    flags = torch.tensor([1 if idx_ok else 0, 1 if bytes_ok(b, n) else 0], device=dev)
+    dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+    cmin, cmax = torch.tensor([n], device=dev), torch.tensor([n], device=dev)
+    dist.all_reduce(cmin, op=dist.ReduceOp.MIN)
+    dist.all_reduce(cmax, op=dist.ReduceOp.MAX)
+    return {"indices_bit_exact": bool(flags[0].item()), "bytes_exact": bool(flags[1].item()), "world": world, "draws": Bg,
+            "records": N * world, "rows_per_rank_min": int(cmin.item()), "rows_per_rank_max": int(cmax.item()),
+            "checked_against": "oracle.replay_oracle.tree_sample over the concatenated leaves of all shards for the global draw "
+                               "vector reassembled from every rank's rows (each draw owned exactly once); every gathered byte "
+                               "vs the rank's frame store; min over ranks"}
+
+
+def learner_loop_short(torch, apex, mem, args, dev):
+    """BASELINE configs[2] in short (<= ~2 s): the learner loop on the same shard, whole step replayed from one CUDA
+    graph — fused sample+gather writing the network's float32 input directly, three forwards, backward, RMSprop,
+    fused TD/priority update.  Reported as an extra key; not the metric's workload."""
+    try:
+        B, C, nA = args.batch, args.frames_per_state, args.actions
+        lp = {"remove_old_xp_freq": 100, "q_target_sync_freq": 2500, "min_replay_mem_size": 20000, "replay_sample_size": B,
+              "load_saved_state": False}
+        out = {}
+        for fmt in ("f32", "u8"):
+            lp["batch_format"] = fmt
+            L = apex.Learner({"state_shape": [C, 84, 84], "action_dim": nA}, dict(lp), {}, mem)
+            L.capture_step()
+            for _ in range(5):
+                L.step_graphed()
+            torch.cuda.synchronize()
+            n = 60
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(n):
+                loss = L.step_graphed()
+            e1.record()
+            torch.cuda.synchronize()
+            out[fmt] = (e0.elapsed_time(e1) / n, float(loss))
+            del L
+        mem.check_status()
+        ms = out["f32"][0]
+        return {"ms_per_step": round(ms, 4), "transitions_per_s": round(B / (ms * 1e-3), 1), "steps": 60,
+                "ms_per_step_u8_gather_plus_float_cast": round(out["u8"][0], 4), "final_loss": out["f32"][1],
+                "workload": "Ape-X learner loop (BASELINE configs[2]): 2M-record replay, batch %d, n=3 double-DQN, duelling net "
+                            "fp32 (PyTorch/cuDNN), RMSprop; one CUDA graph per step; f32 = gather writes the float32 "
+                            "[B,C,84,84] network input itself, u8 = uint8 gather + two .float() passes" % B}
+    except Exception as e:                                        # an extra key must never take the headline line down
+        return {"error": "%s: %s" % (type(e).__name__, e)}
 
 
 class NumpyReplay:
@@ -460,19 +677,21 @@ def time_cpu(obj, B, nA, seconds, max_steps, rng):
             return n, dt
 
 
-def cpu_baselines(leaves, frames, fidx, A, R, G, args, n_records):
+def cpu_baselines(leaves, frames, fidx, A, R, G, args, n_records, only_c=False):
     """-> (cpu_baseline dict [numpy/torch port], extra dict [C/OpenMP port])."""
     from oracle.c_oracle import CpuReplay
     C, B, nA = args.frames_per_state, args.batch, args.actions
     rng = np.random.default_rng(7)
-    ref = NumpyReplay(leaves.copy(), frames, fidx, A, R, G, C, ALPHA)
-    n, dt = time_cpu(ref, B, nA, args.cpu_seconds * 0.6, 5000, rng)
-    base = {"value": round(n * B / dt, 1), "unit": "transitions/s", "cores": ref.threads, "kind": "port",
-            "sample": "%d steps of B=%d on a %d-record host-resident shard (%.1f s): numpy/torch-CPU restatement of the "
-                      "reference algorithm (u64 cumsum + right-sided searchsorted per np.random.choice, index_select "
-                      "frame copies on %d torch threads, learner.py TD math in numpy, fancy-index write-back)"
-                      % (n, B, n_records, dt, ref.threads),
-            "ms_per_step": round(dt / n * 1e3, 4)}
+    base = None
+    if not only_c:
+        ref = NumpyReplay(leaves.copy(), frames, fidx, A, R, G, C, ALPHA)
+        n, dt = time_cpu(ref, B, nA, args.cpu_seconds * 0.6, 5000, rng)
+        base = {"value": round(n * B / dt, 1), "unit": "transitions/s", "cores": ref.threads, "kind": "port",
+                "sample": "%d steps of B=%d on a %d-record host-resident shard (%.1f s): numpy/torch-CPU restatement of the "
+                          "reference algorithm (u64 cumsum + right-sided searchsorted per np.random.choice, index_select "
+                          "frame copies on %d torch threads, learner.py TD math in numpy, fancy-index write-back)"
+                          % (n, B, n_records, dt, ref.threads),
+                "ms_per_step": round(dt / n * 1e3, 4)}
     cpu = CpuReplay(leaves.copy(), frames, fidx, A, R, G, C, F_BYTES, ALPHA)
     n2, dt2 = time_cpu(cpu, B, nA, args.cpu_seconds * 0.4, 5000, rng)
     extra = {"value": round(n2 * B / dt2, 1), "unit": "transitions/s", "cores": cpu.threads, "kind": "port (optimised)",
@@ -510,17 +729,23 @@ def cpu_baseline_from_device(torch, mem, args, dev):
 
 
 def run_reference(args):
-    """CPU arm: the reference's algorithm for the path (oracle port on the host cores); rank 0 only."""
+    """CPU arm: the reference's algorithm for the path (oracle port on the host cores); rank 0 only.
+    Same workload description as the GPU arm.  At N > 1 the one host stands in for all N shards: the
+    global batch of N x B draws is taken over N x capacity records (or as many as host RAM holds)."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
+    import torch
     from oracle import replay_oracle as ro
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
+    torch.set_num_threads(host_threads())
     N, C, B, nA = args.capacity, args.frames_per_state, args.batch, args.actions
+    Bg = B * world
     try:
         import psutil
         avail = psutil.virtual_memory().available
     except Exception:
         avail = 1 << 62
-    n_cpu = N
+    n_cpu = N * world
     while n_cpu * F_BYTES * 1.1 + (4 << 30) > avail and n_cpu > 1 << 16:
         n_cpu //= 2
     rng = np.random.default_rng(1234)
@@ -539,30 +764,43 @@ def run_reference(args):
     G = np.where(rng.random(n_cpu) < 0.01, 0, GAMMA_N).astype(np.float32)
     leaves = ro.priority_to_leaf(ro.pow_priority(np.abs(rng.standard_normal(n_cpu)) + 1e-3, ALPHA))
     ref = NumpyReplay(leaves.copy(), frames, fidx, A, R, G, C, ALPHA)
-    q = [[rng.standard_normal((B, nA)).astype(np.float32) for _ in range(3)] for _ in range(4)]
+    q = [[rng.standard_normal((Bg, nA)).astype(np.float32) for _ in range(3)] for _ in range(4)]
     W, K = max(args.warmup, 3), args.steps
     for k in range(W):
-        ref.step(ro.stratified_uniforms(B, rng), *q[k % 4])
-    us = [ro.stratified_uniforms(B, rng) for _ in range(min(K, 256))]
-    t0 = time.perf_counter()
-    for k in range(K):
-        ref.step(us[k % len(us)], *q[k % 4])
-    dt = time.perf_counter() - t0
-    value = round(K * B / dt, 1)
-    sample = ("each step = one full B=%d step on a %d-record host-resident shard; numpy/torch-CPU restatement of the reference "
-              "algorithm (u64 cumsum + right-sided searchsorted per np.random.choice, torch.index_select frame copies on %d "
-              "threads, learner.py TD math, fancy-index write-back); the literal reference is O(N^2) per update and cannot "
-              "run at this size (BASELINE.md §2)" % (B, n_cpu, ref.threads))
+        ref.step(ro.stratified_uniforms(Bg, rng), *q[k % 4])
+    us = [ro.stratified_uniforms(Bg, rng) for _ in range(min(K, 256))]
+
+    def block_of_k():
+        t0 = time.perf_counter()
+        for k in range(K):
+            ref.step(us[k % len(us)], *q[k % 4])
+        return (time.perf_counter() - t0) * 1e3
+    blocks = [block_of_k()]
+    while sum(blocks) < args.min_ms or len(blocks) < 3:
+        if sum(blocks) > 120e3:                                   # bounded: at most ~2 minutes of CPU blocks
+            break
+        blocks.append(block_of_k())
+    ms, ms_min, ms_max = block_stats(blocks)
+    value = round(K * Bg / (ms * 1e-3), 1)
+    sample = ("each step = one full step of %d draws (B=%d x %d shard(s)) over %d host-resident records (%s); numpy/torch-CPU "
+              "restatement of the reference algorithm (u64 cumsum + right-sided searchsorted per np.random.choice, "
+              "torch.index_select frame copies on %d threads, learner.py TD math, fancy-index write-back); %d block(s) of %d "
+              "steps, median block; the literal reference is O(N^2) per update and cannot run at this size (BASELINE.md §2)"
+              % (Bg, B, world, n_cpu, "all shards" if n_cpu == N * world else "as many as host RAM holds, of %d" % (N * world),
+                 ref.threads, len(blocks), K))
     args.cpu_seconds = min(args.cpu_seconds, 10.0)
-    _, extra = cpu_baselines(leaves, frames, fidx, A, R, G, args, n_cpu)
+    args_c = argparse.Namespace(**vars(args))
+    args_c.batch = Bg
+    _, extra = cpu_baselines(leaves, frames, fidx, A, R, G, args_c, n_cpu, only_c=True)
     print(json.dumps({
-        "impl": "reference", "metric": "prioritized sample+update transitions/s (2M cap, B=512)", "value": value,
-        "unit": "transitions/s", "n_gpus": args.gpus, "steps": K, "warmup": W, "ms_per_step": round(dt / K * 1e3, 5),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8 frames / u64 tree / f32 TD",
-        "data": "synthetic",
-        "config": {"workload": "replay microbench: %d-record shard, batch %d, C=%d 84x84 uint8 (CPU, host RAM)" % (n_cpu, B, C),
-                   "capacity_per_gpu": n_cpu, "batch_per_gpu": B, "frames_per_state": C},
-        "cpu_baseline": {"value": value, "unit": "transitions/s", "cores": ref.threads, "kind": "port", "sample": sample},
+        "impl": "reference", "metric": METRIC, "value": value,
+        "unit": "transitions/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": round(ms / K, 5),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": DTYPE,
+        "data": "synthetic", "config": config_dict(args, world),
+        "timing": {"blocks": len(blocks), "steps_per_block": K, "block_ms_median": round(ms, 3), "block_ms_min": round(ms_min, 3),
+                   "block_ms_max": round(ms_max, 3), "how": "wall clock around blocks of K steps, median block"},
+        "cpu_baseline": {"value": value, "unit": "transitions/s", "cores": ref.threads, "kind": "port", "sample": sample,
+                         "host_records": n_cpu, "draws_per_step": Bg},
         "cpu_baseline_c_openmp": extra,
         "e2e": {"value": value, "unit": "transitions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,

@@ -56,6 +56,9 @@ extern "C" {
 #define APEXB200_HOST_STEP_SLOTS 4           /* buffer sets of apexb200_host_step */
 #define APEXB200_TD_NOALLOC_MAX_B 262144    /* rows per call of apexb200_td_fwd_noalloc */
 
+#define APEXB200_FMT_U8  0              /* gathered batches as stored: uint8 [rows, C, F] */
+#define APEXB200_FMT_F32 1              /* gathered batches widened to float32 [rows, C, F] (learner.py:37-38) */
+
 #define APEXB200_LOSS_HALF_SQ 0         /* 1/2 delta^2, learner.py:48 */
 #define APEXB200_LOSS_HUBER   1         /* Huber(kappa) */
 
@@ -200,11 +203,14 @@ int apexb200_set_gather_variant(int32_t variant);
  * frames_per_state <= 8 and C frames fitting in shared memory (otherwise the two kernels
  * run back to back).  Outputs as in
  * apexb200_sample + apexb200_gather (fsel_out, leaf_out, total_out, u_out, A, R, Gamma,
- * q_t, q_tpn nullable). */
+ * q_t, q_tpn nullable).  out_format: APEXB200_FMT_U8 — S_t/S_tpn are uint8 [count, C, frame_bytes]
+ * as stored; APEXB200_FMT_F32 — float32 arrays of the same shape, every byte widened exactly
+ * (the torch.from_numpy(...).float() of learner.py:37-38 done by the gather itself: frames land in
+ * shared memory by bulk copy, the SM converts and writes 16-byte vectors; fused kernel only). */
 int apexb200_sample_gather(apexb200_replay_t h, const double *u, uint64_t seed, int32_t count,
                            int32_t *idx_out, int32_t *fsel_out, uint64_t *leaf_out, uint64_t *total_out,
-                           double *u_out, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R, float *Gamma,
-                           float *q_t, float *q_tpn, void *stream);
+                           double *u_out, void *S_t, void *S_tpn, int32_t *A, float *R, float *Gamma,
+                           float *q_t, float *q_tpn, int32_t out_format, void *stream);
 /* Programmatic dependent launch for the per-step kernels (default 1): each kernel is
  * scheduled while its predecessor on the stream drains and blocks on
  * griddepcontrol.wait before touching memory.  0 = plain stream-ordered launches. */
@@ -301,6 +307,23 @@ int apexb200_host_step(apexb200_replay_t h, int32_t slot, const double *u_host, 
                        uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R, float *Gamma,
                        float *result_host, void *done_event, void *stream);
 
+/* The same step for one rank of a sharded replay (learner.py:68 -> :70 -> :76 over N GPUs; the sampling side is
+ * apexb200_sample_gather_sharded, so the draws are generated on the device, identically on every rank, and no
+ * draws travel).  q_host [3, max_rows, num_actions] fp32, pinned: row r of each block belongs to the r-th row this
+ * rank owns; S_t/S_tpn/A/R/Gamma are device batch arrays of max_rows rows.  result_host [5*max_rows + 4] fp32,
+ * pinned, receives delta[max_rows] | priority | loss | record index (int32 bits) | global draw index (int32
+ * bits) | loss_mean (this rank's part: sum of its rows' losses / global_count) | rows owned (int32 bits) | 2 pad
+ * words; only the first `rows owned` entries of each array are meaningful.  max_rows is the caller's row
+ * capacity: with max_rows >= global_count no draw can be lost whatever the split of priority mass; with a smaller
+ * max_rows a rank that owns more keeps the first max_rows, sets APEXB200_ST_QUOTA and reports max_rows.  Needs
+ * the peers connected (apexb200_peer_connect[_local]) and push-on-update or an exchange per step; the TD side
+ * runs as the single-CTA kernel (max_rows <= 1024, or a fair share global_count/world of at most ~900 rows).
+ * Streams, slots, done_event and ordering as for apexb200_host_step. */
+int apexb200_host_step_sharded(apexb200_replay_t h, int32_t slot, uint64_t seed, int32_t global_count, int32_t max_rows,
+                               const float *q_host, int32_t num_actions, float eps, int32_t loss_kind, float kappa,
+                               uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R, float *Gamma,
+                               float *result_host, void *done_event, void *stream);
+
 /* ---- K7 n-step return: ExperienceBuffer.update_buffer (actor.py:29-43),
  * intended semantics, vectorised over E actors x T steps --------
  * R[e,t] = sum_{k<m} gamma^k r[e,t+k], Gamma = gamma^m, or 0 when a terminal lies
@@ -369,12 +392,12 @@ int apexb200_peer_push_on_update(apexb200_replay_t h, int32_t enabled);
  * waves inside the same launch.  max_rows is only the number of rows the output arrays hold: pass
  * max_rows >= global_count (one rank can own the whole batch) and nothing is ever dropped; a smaller
  * max_rows is a caller-side limit — a rank that owns more draws than that keeps the first max_rows
- * and sets APEXB200_ST_QUOTA.  Needs frames_per_state <= 8 and half a record (C frames) fitting in
- * shared memory. */
+ * and sets APEXB200_ST_QUOTA.  out_format as for apexb200_sample_gather.  Needs frames_per_state <= 8
+ * and half a record (C frames) fitting in shared memory. */
 int apexb200_sample_gather_sharded(apexb200_replay_t h, uint64_t seed, int32_t global_count, int32_t max_rows,
                                    int32_t *idx_out, int32_t *fsel_out, int32_t *pos_out, double *u_out,
-                                   int32_t *count_out, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R,
-                                   float *Gamma, float *q_t, float *q_tpn, void *stream);
+                                   int32_t *count_out, void *S_t, void *S_tpn, int32_t *A, float *R,
+                                   float *Gamma, float *q_t, float *q_tpn, int32_t out_format, void *stream);
 
 /* ---- K9 learner -> actor weight publication ----------------
  * Replaces shared_state["Q_state_dict"] = Q.state_dict() (learner.py:24, :74 — a 13.3 MB

@@ -329,6 +329,55 @@ def test_stream_insert_and_gather_byte_exact(apex, variant, C_, F):
         apex._C.call("apexb200_set_gather_variant", 0)
 
 
+@pytest.mark.parametrize("C_,F,B", [(4, 7056, 96), (1, 7056, 33), (3, 208, 700), (8, 64, 17)])
+def test_float32_batches_equal_widened_uint8_batches(apex, C_, F, B):
+    """apexb200_sample_gather with APEXB200_FMT_F32 (learner.py:37-38: the model is handed float32 states):
+    for the same draws the float32 batch equals the uint8 batch converted by .float(), element for element,
+    and the uint8 batch equals the oracle's gather byte for byte; same for the sharded kernel (group of one)."""
+    rng = np.random.default_rng(C_ * 1000 + B)
+    N, lanes = 4096, 2
+    mem = make_mem(apex, N, C=C_, F=F, layout="stream", lanes=lanes, n=3)
+    ring = ro.RingOracle(N, C_, F, lanes=lanes, fpr=1, lookback=C_ - 1 + 3, alpha=0.6)
+    for lane in range(lanes):
+        m = N // lanes - (C_ + 2)
+        args = (lane, rng.integers(0, 256, (m, F), dtype=np.uint8), apex.stream_offsets(C_, np.full(m, 3), np.arange(m) % 211),
+                rng.integers(0, 4, m).astype(np.int32), rng.standard_normal(m).astype(np.float32), np.full(m, 0.97, np.float32))
+        prio = (np.abs(rng.standard_normal(m)) + 1e-3).astype(np.float32)
+        mem.insert(*args, prio=prio)
+        ring.insert(*args, prio=prio)
+    ring.leaves[:] = u64(mem.buffer(apex._C.BUF_LEAVES))
+    u = rng.random(B)
+    want = ring.gather(ring.sample(u))
+    b8 = mem.sample_tensors(B, u=dev(u))
+    s8, n8, idx8 = b8.S_t.clone(), b8.S_tpn.clone(), b8.idx.clone()
+    np.testing.assert_array_equal(s8.cpu().numpy(), want["S_t"])
+    np.testing.assert_array_equal(n8.cpu().numpy(), want["S_tpn"])
+    bf = mem.sample_tensors(B, u=dev(u), f32=True)
+    assert bf.S_t.dtype == torch.float32 and bf.S_t.shape == (B, C_, F)
+    assert torch.equal(bf.idx, idx8)
+    assert torch.equal(bf.S_t, s8.float()) and torch.equal(bf.S_tpn, n8.float())
+    np.testing.assert_array_equal(bf.R.cpu().numpy(), want["R"])
+    # sharded kernel, group of one: same rows in float32 and uint8 for the same in-kernel draws
+    sampler = apex.ShardedSampler(mem, rank=0, world_size=1)
+    sampler.connect_peers()
+    sampler.exchange()
+    from apex_b200 import _C
+    o8, of = mem._outputs(B, False), mem._outputs(B, False, True)
+    for o, fmt in ((o8, _C.FMT_U8), (of, _C.FMT_F32)):
+        cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
+        u_out = torch.zeros(B, dtype=torch.float64, device="cuda")
+        _C.call("apexb200_sample_gather_sharded", mem._h, 77, B, B, _C.ptr(o["idx"]), _C.ptr(o["fsel"]), None, _C.ptr(u_out),
+                _C.ptr(cnt), _C.ptr(o["S_t"]), _C.ptr(o["S_tpn"]), _C.ptr(o["A"]), _C.ptr(o["R"]), _C.ptr(o["Gamma"]), None, None,
+                fmt, _C.stream_ptr())
+        assert int(cnt.item()) == B
+        w = ring.gather(ring.sample(u_out.cpu().numpy()))
+        got = o["S_t"].cpu().numpy()
+        np.testing.assert_array_equal(got, w["S_t"].astype(got.dtype))
+        got = o["S_tpn"].cpu().numpy()
+        np.testing.assert_array_equal(got, w["S_tpn"].astype(got.dtype))
+    mem.check_status()
+
+
 @pytest.mark.parametrize("seed", range(12))
 def test_random_configurations(apex, seed):
     """Ragged shapes: random frames-per-state (odd, 1, the fused kernels' limit 8 and beyond it), frame
