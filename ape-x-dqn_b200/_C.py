@@ -81,6 +81,12 @@ SIGNATURES = {
     "apexb200_host_step_sharded": [_P, _I32, C.c_uint64, _I32, _I32, _P, _I32, _F, _I32, _F, _P, _P, _P, _P, _P, _P, _P, _P],
     "apexb200_nstep": [_P, _P, _I32, _I32, _I32, _F, _P, _P, _P, _P],
     "apexb200_initial_priority": [_P, _P, _P, _P, _P, _I32, _I32, _P, _P],
+    "apexb200_ingest_create": [_P, _I32, _P, _I32, _F, _I32, _I32, C.POINTER(_P)],
+    "apexb200_ingest_destroy": [_P],
+    "apexb200_ingest_push": [_P, _P, _I32, _I32, _P, _P, _P, _P, _P, _P],
+    "apexb200_ingest_push_blobs": [_P, _P, _P, _I32, _I32, _I32, _I32, _I32, _I32, _P],
+    "apexb200_ingest_sync_heads": [_P, _P],
+    "apexb200_host_register_mapped": [_P, C.c_uint64, C.POINTER(_P)],
     "apexb200_shard_targets": [_P, _I32, _I32, _P, _I32, _P, _P, _P, _P],
     "apexb200_peer_export": [_P, _P],
     "apexb200_peer_connect": [_P, _I32, _I32, _P],
@@ -148,6 +154,13 @@ def stream_ptr(stream=None):
 def host_register(address, nbytes):
     """Page-lock [address, address + nbytes) for this process so that copies to and from it are asynchronous."""
     call("apexb200_host_register", C.c_void_p(address), int(nbytes))
+
+
+def host_register_mapped(address, nbytes):
+    """Page-lock [address, address + nbytes) and map it for kernels; returns the device-visible address."""
+    dp = C.c_void_p()
+    call("apexb200_host_register_mapped", C.c_void_p(address), int(nbytes), C.byref(dp))
+    return int(dp.value)
 
 
 def host_unregister(address):

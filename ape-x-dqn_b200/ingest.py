@@ -1,30 +1,33 @@
 """Device-side ingest for vectorised actors: frame streams in, n-step records out.
 
-Replaces, for E environments stepped in lock-step, the chain ExperienceBuffer.add /
-update_buffer / construct_nstep_transition (actor.py:29-70) -> Actor.compute_priorities
-(actor.py:127-143) -> queue -> ReplayMemory.add (main.py:21-25, replay.py:59-69) with
-K7 (apexb200_nstep) + K6 (apexb200_replay_insert); nothing is pickled and the frames are
-stored once.
+Replaces, for E environments, the chain ExperienceBuffer.add / update_buffer /
+construct_nstep_transition (actor.py:29-70) -> Actor.compute_priorities (actor.py:127-143) ->
+queue -> ReplayMemory.add (main.py:21-25, replay.py:59-69) with the apexb200_ingest_* entry points:
+nothing is pickled, the frames are stored once, and the n-step carry, the episode ages and the ring
+heads of every environment live on the device — a push is three kernel launches (frame copy, record
+build + insert, state roll) with no host arithmetic in between.
 
-One environment owns one lane of a stream-layout replay.  The frame observed at env step
-tau is stored at lane position tau together with the n-step record of step t = tau - n
-(its S_tpn ends at that frame): A_t, R = sum_{k<m} gamma^k r_{t+k}, Gamma = gamma^m or 0
-when a terminal lies inside the window, initial priority |R + Gamma max q_tau - q_t[A_t]|
-computed by the insert kernel.  Everything a record needs lies in the past of its frame,
-so a chunk of T env steps emits T records immediately; only the last n steps are carried
-to the next chunk.  The first n frames of a stream carry no record (priority 0).
+One environment owns one lane of a stream-layout replay.  The frame observed at env step tau is
+stored at lane position tau together with the n-step record of step t = tau - n (its S_tpn ends at
+that frame): A_t, R = sum_{k<m} gamma^k r_{t+k}, Gamma = gamma^m or 0 when a terminal lies inside
+the window, initial priority |R + Gamma max q_tau - q_t[A_t]| computed by the insert kernel.
+Everything a record needs lies in the past of its frame, so a chunk of T env steps emits T records
+immediately; only the last n steps are carried to the next chunk.  The first n frames of a stream
+carry no record (priority 0).
 """
 from __future__ import annotations
+
+import ctypes as C
 
 import numpy as np
 import torch
 
-from . import ops
+from . import _C
 from .replay import stream_offsets
 
 
 class VectorActorIngest:
-    def __init__(self, mem, num_envs, n_step=None, gamma=0.99, lanes=None):
+    def __init__(self, mem, num_envs, n_step=None, gamma=0.99, lanes=None, num_actions=None, max_chunk_steps=0):
         mem._ensure()
         self.lanes = list(range(num_envs)) if lanes is None else [int(x) for x in lanes]
         if mem.layout != "stream" or len(self.lanes) != num_envs or max(self.lanes) >= mem.lanes:
@@ -34,68 +37,69 @@ class VectorActorIngest:
         if mem.lookback < mem.C - 1 + self.n:
             raise ValueError("replay lookback %d < frames_per_state - 1 + n_step" % mem.lookback)
         self.gamma = float(gamma)
-        E, n, dev = self.E, self.n, mem.device
-        # carry of the last n steps per env (device) and episode ages (host)
-        self.c_act = torch.zeros((E, n), dtype=torch.int32, device=dev)
-        self.c_rew = torch.zeros((E, n), dtype=torch.float32, device=dev)
-        self.c_done = torch.ones((E, n), dtype=torch.uint8, device=dev)      # "terminal": no record before the stream starts
-        self.c_q = None                                                      # sized by the first chunk's q
-        self.seen = 0                                                        # frames pushed per env so far
-        self.age = np.zeros(E, np.int64)                                     # frames since episode start, at the next frame
+        self.max_chunk_steps = int(max_chunk_steps)
+        self._g = None
+        self.nA = None
+        if num_actions is not None:
+            self._create(int(num_actions))
 
-    def push(self, frames, actions, rewards, dones, q):
-        """One chunk of T env steps for all E envs.
+    def _create(self, num_actions):
+        g = C.c_void_p()
+        lanes = (C.c_int32 * self.E)(*self.lanes)
+        with torch.cuda.device(self.mem.device):
+            _C.call("apexb200_ingest_create", self.mem._h, self.E, lanes, self.n, self.gamma, int(num_actions),
+                    self.max_chunk_steps, C.byref(g))
+        self._g, self.nA = g, int(num_actions)
+
+    def __del__(self):
+        g, self._g = getattr(self, "_g", None), None
+        if g is not None:
+            try:
+                _C.lib().apexb200_ingest_destroy(g)
+            except Exception:
+                pass
+
+    close = __del__
+
+    def _field(self, x, dtype, np_dtype):
+        """Device tensor of the wanted dtype: CUDA tensors are used in place, host data goes through the replay's
+        pinned staging (asynchronous copy)."""
+        if isinstance(x, torch.Tensor) and x.is_cuda:
+            return x.to(dtype).contiguous()
+        a = x.numpy() if isinstance(x, torch.Tensor) else np.asarray(x)
+        return self.mem._dev(a, np_dtype)
+
+    def push(self, frames, actions, rewards, dones, q, envs=None):
+        """One chunk of T env steps for all E envs (or for the environments listed in `envs`).
 
         frames [E, T, F] uint8: observation s_tau seen at step tau; actions/rewards/dones [E, T]:
         what was done at s_tau and what came back (dones[e, tau] = episode ended by that step, so
         s_{tau+1} starts a new episode); q [E, T, A] = Q(s_tau).  Device tensors or host arrays.
         Returns the number of records (E * T) written.
         """
-        mem, E, n, dev = self.mem, self.E, self.n, self.mem.device
-        frames = torch.as_tensor(frames).to(dev)
-        actions = torch.as_tensor(actions).to(dev, torch.int32)
-        rewards = torch.as_tensor(rewards).to(dev, torch.float32)
-        dones_h = np.asarray(dones.cpu() if isinstance(dones, torch.Tensor) else dones).astype(bool)
-        dones_d = torch.as_tensor(dones_h.astype(np.uint8)).to(dev)
-        q = torch.as_tensor(q).to(dev, torch.float32)
-        T = frames.shape[1]
-        # steps tau-n .. tau-1 for every new frame tau: carry + this chunk
-        act = torch.cat([self.c_act, actions], 1)
-        rew = torch.cat([self.c_rew, rewards], 1).contiguous()
-        don = torch.cat([self.c_done, dones_d], 1).contiguous()
-        if self.c_q is None:
-            self.c_q = torch.zeros((E, n, q.shape[-1]), dtype=torch.float32, device=dev)
-        qq = torch.cat([self.c_q, q], 1)
-        R, G, _span = ops.nstep_returns(rew, don, n, self.gamma)             # K7 over [E, n + T]
-        A_rec, R_rec, G_rec = act[:, :T].contiguous(), R[:, :T].contiguous(), G[:, :T].contiguous()
-        q_t, q_tpn = qq[:, :T].contiguous(), qq[:, n:n + T].contiguous()
-        # episode ages on the host (tiny): age of frame tau and of step t = tau - n
-        age_tau = np.zeros((E, T), np.int64)
-        a = self.age.copy()
-        for t in range(T):
-            age_tau[:, t] = a
-            a = np.where(dones_h[:, t], 0, a + 1)
-        self.age = a
-        hist = getattr(self, "_age_hist", np.zeros((E, n), np.int64))
-        age_all = np.concatenate([hist, age_tau], 1)                         # ages of frames tau-n .. tau
-        self._age_hist = age_all[:, -n:]
-        age_t = age_all[:, :T]                                               # age of frame t = tau - n
-        prio_mask = torch.ones((E, T), dtype=torch.float32, device=dev)
-        warm = max(0, n - self.seen)                                         # first n frames of the stream: no record yet
-        if warm:
-            prio_mask[:, :min(warm, T)] = 0.0
-        C = mem.C
-        back = np.arange(C - 1, -1, -1, dtype=np.int64)[None, None, :]
-        s_tpn = -np.minimum(back, age_tau[:, :, None])
-        s_t = -(n + np.minimum(back, age_t[:, :, None]))
-        rel = torch.as_tensor(np.concatenate([s_t, s_tpn], 2).astype(np.int32)).to(dev)
-        prio = ops.initial_priority(q_t.reshape(E * T, -1), q_tpn.reshape(E * T, -1), A_rec.reshape(-1), R_rec.reshape(-1),
-                                    G_rec.reshape(-1)).view(E, T) * prio_mask
-        mem.insert_lanes(self.lanes, frames.reshape(E, T, -1), rel, A_rec, R_rec, G_rec, prio=prio.contiguous())   # K6, all lanes
-        self.c_act, self.c_rew, self.c_done, self.c_q = (act[:, -n:].contiguous(), rew[:, -n:].contiguous(),
-                                                         don[:, -n:].contiguous(), qq[:, -n:].contiguous())
-        self.seen += T
+        q = self._field(q, torch.float32, np.float32)
+        if self._g is None:
+            self._create(int(q.shape[-1]))
+        frames = self._field(frames, torch.uint8, np.uint8)
+        actions = self._field(actions, torch.int32, np.int32)
+        rewards = self._field(rewards, torch.float32, np.float32)
+        dones = self._field(dones, torch.uint8, np.uint8)
+        E, T = int(actions.shape[0]), int(actions.shape[1])
+        if envs is None:
+            if E != self.E:
+                raise ValueError("push: inputs for %d environments, ingest has %d" % (E, self.E))
+            ids = None
+        else:
+            ids = (C.c_int32 * E)(*[int(e) for e in envs])
+        _C.call("apexb200_ingest_push", self._g, ids, E, T, _C.ptr(frames), _C.ptr(actions), _C.ptr(rewards), _C.ptr(dones),
+                _C.ptr(q), _C.stream_ptr())
         return E * T
+
+    def sync_heads(self):
+        """After replaying a CUDA graph that contains push(): bring the host-side ring heads (size(), checkpoints,
+        plain insert calls) up to date with the device-side ones."""
+        if self._g is not None:
+            _C.call("apexb200_ingest_sync_heads", self._g, _C.stream_ptr())
 
 
 class ActorStagingRing:
@@ -111,7 +115,6 @@ class ActorStagingRing:
     """
 
     def __init__(self, name, slots, chunk_steps, frame_bytes, num_actions, create):
-        from . import _C
         self.slots, self.T, self.F, self.nA = int(slots), int(chunk_steps), int(frame_bytes), int(num_actions)
         T, F, nA = self.T, self.F, self.nA
         self.off_act = T * F
@@ -151,13 +154,17 @@ class ActorStagingRing:
 
     # ---- consumer side (process that owns the replay)
     def register_cuda(self):
-        """Page-lock the shared memory for this process so that H2D copies out of it are asynchronous."""
+        """Page-lock the shared memory for this process and map it for kernels: copies out of it are asynchronous
+        and the ingest's pack kernel can read the chunks in place (self.dev_base = device-visible address)."""
         if not self._registered:
-            from . import _C
             self._reg_base = self._data.ctypes.data - 256
-            _C.host_register(self._reg_base, 256 + self.slots * self.slot_bytes)
+            self.dev_base = _C.host_register_mapped(self._reg_base, 256 + self.slots * self.slot_bytes)
             self._registered = True
         return self._registered
+
+    def blob_address(self, k):
+        """Device-visible address of chunk slot k (register_cuda() first)."""
+        return self.dev_base + 256 + (k % self.slots) * self.slot_bytes
 
     def pop(self):
         """-> (frames, actions, rewards, dones, q) host views of the oldest unread chunk, or None.
@@ -172,41 +179,69 @@ class ActorStagingRing:
 
     def close(self, unlink=False):
         if self._registered:                              # before the mapping goes away: the range may be reused
-            from . import _C
             _C.host_unregister(self._reg_base)
             self._registered = False
         self.ctrl = self._data = None
         self.shm.close()
         if unlink:
-            from . import _C
             _C.unlink_shared_memory(self.shm)
 
 
 class RingIngest:
-    """Drains a set of ActorStagingRings (one per actor = one lane each) into a stream-layout replay."""
+    """Drains a set of ActorStagingRings (one per actor = one lane each) into a stream-layout replay.
+
+    Every poll() collects ALL rings that hold an unread chunk and moves them with one apexb200_ingest_push_blobs
+    call: a pack kernel reads the chunks in place from the page-locked, device-mapped shared memory (no per-ring
+    copy calls), then the three ingest launches build and insert the records of all those actors.  A ring slot is
+    handed back to its actor when a CUDA event recorded behind that work has completed — the host never waits
+    for the stream."""
 
     def __init__(self, mem, rings, n_step=None, gamma=0.99):
         self.mem, self.rings = mem, list(rings)
-        self.lane_ingest = [VectorActorIngest(mem, 1, n_step=n_step, gamma=gamma, lanes=[k]) for k in range(len(self.rings))]
+        r0 = self.rings[0]
+        if any((r.T, r.F, r.nA) != (r0.T, r0.F, r0.nA) for r in self.rings):
+            raise ValueError("RingIngest: all rings must carry chunks of the same shape")
+        self.ingest = VectorActorIngest(mem, len(self.rings), n_step=n_step, gamma=gamma, num_actions=r0.nA,
+                                        max_chunk_steps=r0.T)
         for r in self.rings:
             r.register_cuda()
+        self._taken = [int(r.ctrl[1]) for r in self.rings]                # chunks handed to the device per ring
+        self._inflight = []                                               # (event, [ring indices]) in stream order
+
+    def _reap(self, wait=False):
+        while self._inflight:
+            ev, ks = self._inflight[0]
+            if wait:
+                ev.synchronize()
+            elif not ev.query():
+                break
+            for k in ks:
+                self.rings[k].release()                                   # the actor may overwrite the slot now
+            self._inflight.pop(0)
 
     def poll(self):
-        """Move every chunk that is ready; returns the number of records inserted."""
-        n = 0
-        dev = self.mem.device
-        for ring, ing in zip(self.rings, self.lane_ingest):
-            while True:
-                chunk = ring.pop()
-                if chunk is None:
-                    break
-                f, a, r, d, q = chunk
-                tensors = [torch.from_numpy(x).to(dev, non_blocking=True) for x in (f, a, r, q)]
-                dones = d.copy()
-                torch.cuda.current_stream().synchronize()         # payload is on the device: the slot can be reused
-                ring.release()
-                n += ing.push(tensors[0][None], tensors[1][None], tensors[2][None], dones[None], tensors[3][None])
+        """Move every chunk that is ready; returns the number of records inserted (enqueued)."""
+        self._reap()
+        n, r0 = 0, self.rings[0]
+        while True:
+            ready = [k for k, r in enumerate(self.rings) if int(r.ctrl[0]) > self._taken[k]]
+            if not ready:
+                break
+            envs = (C.c_int32 * len(ready))(*ready)
+            blobs = (C.c_uint64 * len(ready))(*[self.rings[k].blob_address(self._taken[k]) for k in ready])
+            _C.call("apexb200_ingest_push_blobs", self.ingest._g, envs, blobs, len(ready), r0.T, r0.off_act, r0.off_rew,
+                    r0.off_done, r0.off_q, _C.stream_ptr())
+            ev = torch.cuda.Event()
+            ev.record()
+            self._inflight.append((ev, ready))
+            for k in ready:
+                self._taken[k] += 1
+            n += len(ready) * r0.T
         return n
+
+    def flush(self):
+        """Wait for everything handed to the device and release the slots."""
+        self._reap(wait=True)
 
 
 __all__ = ["VectorActorIngest", "ActorStagingRing", "RingIngest", "stream_offsets"]

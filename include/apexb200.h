@@ -335,6 +335,41 @@ int apexb200_initial_priority(const float *q_t, const float *q_tpn, const int32_
                               const float *R, const float *Gamma, int32_t count,
                               int32_t num_actions, float *abs_td, void *stream);
 
+/* ---- device-side ingest of actor step streams: replaces, for E environments that each own
+ * one lane of a frame-once ("stream") replay, ExperienceBuffer.add / update_buffer / construct_nstep_transition
+ * (actor.py:29-70), Actor.compute_priorities (actor.py:127-143), the queue pump (main.py:21-25) and
+ * ReplayMemory.add (replay.py:59-69).  The n-step carry (last n_step actions, rewards, dones, Q rows), the
+ * episode ages and the ring heads of every environment live on the device, so a push is a fixed sequence of
+ * launches (frame copy, record build + insert, state roll) with no host arithmetic between them.
+ * The frame seen at env step tau is stored with the record of step t = tau - n_step: A_t, R = sum_k gamma^k
+ * r_{t+k}, Gamma = gamma^n_step or 0 when the episode ended inside the window, initial priority
+ * |R + Gamma max_a Q(s_tau) - Q(s_t)[A_t]|; S_t / S_tpn are the C frames ending at t / tau, repeating the
+ * episode's first frame where the episode is younger.  The first n_step frames of a stream carry no record.
+ * create: lanes_host [num_envs] distinct lanes (heads are taken over from the handle); max_chunk_steps > 0
+ * also allocates device staging for push_blobs.  Allocates and synchronises; push / push_blobs only enqueue. */
+typedef struct apexb200_ingest *apexb200_ingest_t;
+int apexb200_ingest_create(apexb200_replay_t h, int32_t num_envs, const int32_t *lanes_host, int32_t n_step, float gamma,
+                           int32_t num_actions, int32_t max_chunk_steps, apexb200_ingest_t *out);
+int apexb200_ingest_destroy(apexb200_ingest_t g);
+/* One chunk of T env steps for n_envs environments (envs_host [n_envs] distinct environment numbers, NULL = the
+ * first n_envs environments in order).  Device inputs with a leading environment dimension: frames [n_envs, T,
+ * frame_bytes] u8 (s_tau), actions [n_envs, T] (taken at s_tau), rewards [n_envs, T], dones [n_envs, T] u8
+ * (1 = the episode ended with that step), q [n_envs, T, num_actions] = Q(s_tau).  T + lookback <= lane capacity. */
+int apexb200_ingest_push(apexb200_ingest_t g, const int32_t *envs_host, int32_t n_envs, int32_t T, const uint8_t *frames,
+                         const int32_t *actions, const float *rewards, const uint8_t *dones, const float *q, void *stream);
+/* The same for chunks that sit in page-locked, device-mapped HOST memory (apexb200_host_register_mapped), one blob
+ * per environment as actor processes write them: frames [T, frame_bytes] at offset 0, then actions i32 [T],
+ * rewards f32 [T], dones u8 [T], q f32 [T, num_actions] at the given byte offsets.  blobs_host [n_envs] are the
+ * DEVICE-visible addresses of the blobs.  One pack kernel reads all of them over PCIe into the ingest's staging,
+ * then the three launches of ingest_push follow: no per-environment copy calls.  The blobs may be reused once
+ * work enqueued on `stream` up to here has completed (record an event). */
+int apexb200_ingest_push_blobs(apexb200_ingest_t g, const int32_t *envs_host, const uint64_t *blobs_host, int32_t n_envs,
+                               int32_t T, int32_t off_actions, int32_t off_rewards, int32_t off_dones, int32_t off_q,
+                               void *stream);
+/* The handle's host-side ring heads follow every push call; after replaying a CUDA graph that contains pushes
+ * (the host was not involved) copy the device-side heads back with this (synchronises `stream`). */
+int apexb200_ingest_sync_heads(apexb200_ingest_t g, void *stream);
+
 /* ---- K8 shard routing (no reference counterpart: the reference is single
  * process; this is the multi-GPU split of ReplayMemory.sample) ----
  * totals [G] = all-gathered shard totals.  For each draw u_j the global target is
@@ -448,6 +483,9 @@ int apexb200_actor_policy(const float *value, const float *advantage_or_q, const
  * with CUDA so that copies to and from it are asynchronous; a stale registration of the same
  * virtual range is replaced.  Unregister before unmapping the memory. */
 int apexb200_host_register(void *address_host, uint64_t bytes);
+/* The same, and the range becomes readable by kernels: *device_pointer_host receives its device-visible address
+ * (what apexb200_ingest_push_blobs takes). */
+int apexb200_host_register_mapped(void *address_host, uint64_t bytes, void **device_pointer_host);
 int apexb200_host_unregister(void *address_host);
 
 /* ---- raw access for checkpoint / tests (learner.py:18-23 is load-only; the

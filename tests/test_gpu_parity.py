@@ -959,6 +959,74 @@ def test_vector_actor_ingest_matches_sliding_buffer(apex):
     mem.check_status()
 
 
+@pytest.mark.parametrize("E,lane_cap,nA,store_q", [(5, 64, 4, False), (2, 40, 6, True), (300, 32, 3, False)])
+def test_device_ingest_equals_ring_oracle_fed_with_nstep_oracle(apex, E, lane_cap, nA, store_q):
+    """apexb200_ingest_push (n-step assembly, episode ages, initial priority, ring insert, all state on the device)
+    against the oracles directly: nstep_oracle.nstep_intended over the whole step history gives R / Gamma of every
+    record, stream offsets + RingOracle.insert give frame slots, eviction and the dead zone.  Ragged chunks, chunks
+    shorter than n, pushes for a subset of the environments, several ring wrap-arounds; every tree level equals a
+    rebuild at the end."""
+    rng = np.random.default_rng(E * 7 + lane_cap)
+    n, C_, F, gamma, steps = 3, 3, 32, 0.99, 150
+    W = C_ - 1 + n
+    mem = apex.ReplayMemory(E * lane_cap, {"priority_exponent": 0.6, "layout": "stream", "lanes": E, "n_step": n,
+                                           "state_shape": (C_, 1, F), "num_actions": nA if store_q else 0})
+    lanes = [int(x) for x in rng.permutation(E)]
+    ing = apex.VectorActorIngest(mem, E, gamma=gamma, lanes=lanes)
+    ring = ro.RingOracle(E * lane_cap, C_, F, lanes=E, fpr=1, lookback=W, alpha=0.6, num_actions=nA if store_q else 0)
+    frames = rng.integers(0, 256, (E, steps, F), dtype=np.uint8)
+    acts = rng.integers(0, nA, (E, steps)).astype(np.int32)
+    rews = rng.standard_normal((E, steps)).astype(np.float32)
+    dones = rng.random((E, steps)) < 0.08
+    qs = rng.standard_normal((E, steps, nA)).astype(np.float32)
+    R_all, G_all, span = no.nstep_intended(rews, dones, n, gamma)
+    age = np.zeros((E, steps), np.int64)                                   # frames since the episode start, per frame
+    for t in range(1, steps):
+        age[:, t] = np.where(dones[:, t - 1], 0, age[:, t - 1] + 1)
+    back = np.arange(C_ - 1, -1, -1)
+    cuts = [0, 2, 3, 11, 12, 30, 31, 33, 60, 61, 90, 120, 150] if lane_cap >= 40 else list(range(0, 151, 25))
+    for a_, b_ in zip(cuts, cuts[1:]):
+        # every other chunk goes to a subset of the environments first, then to the rest (same steps, two calls)
+        groups = [list(range(E))] if (a_ // 3) % 2 else [list(range(0, E, 2)), list(range(1, E, 2))]
+        for envs in [g for g in groups if g]:
+            sl = np.array(envs)
+            ing.push(frames[sl, a_:b_], acts[sl, a_:b_], rews[sl, a_:b_], dones[sl, a_:b_], qs[sl, a_:b_],
+                     envs=None if len(envs) == E else envs)
+            for e in envs:
+                tau = np.arange(a_, b_)
+                t = tau - n
+                ok = t >= 0
+                tc = np.maximum(t, 0)
+                A = np.where(ok, acts[e, tc], 0).astype(np.int32)
+                R = np.where(ok, R_all[e, tc], 0).astype(np.float32)
+                G = np.where(ok, G_all[e, tc], 0).astype(np.float32)
+                assert (span[e, tc][ok] > 0).all()                         # the window of step t is complete at tau
+                rel = np.concatenate([-(n + np.minimum(back[None, :], np.where(ok, age[e, tc], 0)[:, None])),
+                                      -np.minimum(back[None, :], age[e, tau][:, None])], 1).astype(np.int32)
+                prio = np.abs(R + G * qs[e, tau].max(1) - qs[e, tc, A]) * ok
+                ring.insert(lanes[e], frames[e, a_:b_], rel, A, R, G, prio=prio.astype(np.float32),
+                            q_t=np.where(ok[:, None], qs[e, tc], 0) if store_q else None, q_tpn=qs[e, tau] if store_q else None)
+    assert mem.size() == ring.size()
+    written = np.zeros(E * lane_cap, bool)
+    for e in range(E):
+        written[lanes[e] * lane_cap + np.arange(min(steps, lane_cap))] = True
+    get = lambda w: mem.buffer(w).cpu().numpy()                            # noqa: E731
+    np.testing.assert_array_equal(get(apex._C.BUF_FRAMES).reshape(-1, F)[written], ring.frames[written])
+    np.testing.assert_array_equal(get(apex._C.BUF_FIDX).reshape(-1, 2 * C_)[written], ring.fidx[written])
+    np.testing.assert_array_equal(get(apex._C.BUF_ACTION)[written], ring.A[written])
+    np.testing.assert_allclose(get(apex._C.BUF_REWARD)[written], ring.R[written], rtol=RTOL, atol=1e-6)
+    np.testing.assert_allclose(get(apex._C.BUF_GAMMA)[written], ring.G[written], rtol=RTOL)
+    if store_q:
+        np.testing.assert_array_equal(get(apex._C.BUF_QT).reshape(-1, nA)[written], ring.q_t[written])
+        np.testing.assert_array_equal(get(apex._C.BUF_QTPN).reshape(-1, nA)[written], ring.q_tpn[written])
+    leaves = u64(mem.buffer(apex._C.BUF_LEAVES))
+    assert ((leaves == 0) == (ring.leaves == 0)).all()                     # same live / dead records
+    np.testing.assert_allclose(leaves / float(1 << 24), ring.leaves / float(1 << 24), rtol=2e-4, atol=2e-6)
+    for l, (got, want) in enumerate(zip(read_levels(apex, mem), ro.build_levels(leaves))):
+        np.testing.assert_array_equal(got, want, err_msg="tree level %d" % l)
+    mem.check_status()
+
+
 @pytest.mark.parametrize("E,lane_cap,T,rounds", [(3, 64, 10, 9), (70, 32, 5, 4), (1, 128, 40, 5)])
 def test_insert_lanes_equals_per_lane_inserts(apex, E, lane_cap, T, rounds):
     """apexb200_replay_insert_lanes (one launch pair for E lanes, 64 lanes per launch) == E single-lane inserts,
@@ -1058,9 +1126,11 @@ def test_ring_ingest_from_actor_processes(apex):
         while got < want and time.time() - t0 < 120:
             got += ingest.poll()
             time.sleep(0.002)
+        ingest.flush()                                                     # every slot handed back to its actor
         for p in procs:
             p.join(timeout=30)
         assert got == want and all(p.exitcode == 0 for p in procs)
+        assert all(int(r.ctrl[0]) == int(r.ctrl[1]) == chunks for r in rings)
         direct = [apex.VectorActorIngest(ref, 1, n_step=n, lanes=[e]) for e in range(E)]
         for e in range(E):
             rng = np.random.default_rng(900 + e)
@@ -1076,6 +1146,7 @@ def test_ring_ingest_from_actor_processes(apex):
         assert mem.total() == ref.total() and mem.size() == ref.size() == want
         mem.check_status()
     finally:
+        torch.cuda.synchronize()
         for r in rings:
             r.close(unlink=True)
 
