@@ -67,6 +67,8 @@ SIGNATURES = {
     "apexb200_sample_targets": [_P, _P, _P, _I32, _P, _P, _P, _P],
     "apexb200_gather": [_P, _P, _P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "apexb200_set_gather_variant": [_I32],
+    "apexb200_debug_timeline": [_P, _I32],
+    "apexb200_debug_td_timeline": [_P],
     "apexb200_sample_gather": [_P, _P, C.c_uint64, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P],
     "apexb200_set_pdl": [_I32],
     "apexb200_set_td_cluster": [_I32],

@@ -344,6 +344,112 @@ sample_gather_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int
     sample_gather_body<false, false>(tv, rv, sa, ga, ctrl, nullptr, 0u);
 }
 
+// ---- instrumented copy of the fused kernel (apexb200_set_gather_variant(3)): same work, plus per-warp timestamps
+// (SM clock, relative to the warp's first instruction; global timer at entry and exit) in a static debug array
+// read back with apexb200_debug_timeline.  Measurement aid only.
+constexpr int kDbgWords = 12;
+__device__ unsigned long long g_dbg_timeline[2048 * kDbgWords];
+
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+__global__ void __launch_bounds__(512)
+sample_gather_timed_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int32_t *ctrl) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    unsigned long long *bars = (unsigned long long *)smem;
+    const unsigned long long g0 = gtimer();
+    const long long c0 = clock64();
+    pdl_prologue();
+    const long long c1 = clock64();
+    const int lane = threadIdx.x & 31;
+    const int wl = threadIdx.x >> 5;
+    const int wpc = blockDim.x >> 5;
+    const int nch = frame_chunks(rv.F);
+    const int unit = blockIdx.x * wpc + wl;
+    const int w = unit >> 1, half = unit & 1;
+    const int count = ga.count;
+    const int C = rv.C, twoC = 2 * rv.C;
+    if (w >= count) return;
+    uint8_t *stage = smem + (size_t)wpc * 8 * kMaxChunks * 8 + (size_t)(wl * C + lane) * rv.F;
+    unsigned long long *my_bars = bars + (wl * 8 + lane) * kMaxChunks;
+    const TopValues vtop = top_level_value(tv);
+    double uw;
+    if (sa.u == nullptr) {
+        uw = strat_uniform(sa.seed, read_epoch(ctrl), sa.call, w, count);
+        if (sa.u_out && lane == 0 && half == 0) sa.u_out[w] = uw;
+    } else {
+        uw = sa.u[w];
+    }
+    unsigned long long leaf, total;
+    const long long node = warp_descend(tv, vtop, 0ull, true, uw, &leaf, &total, ctrl);
+    const long long c2 = clock64();
+    const int k = half * C + lane;
+    long long f = -1;
+    if (node >= 0 && lane < C) f = rv.fidx[node * twoC + k];
+    bool moving = false;
+    long long c3 = 0;
+    if (node >= 0 && lane < C) {
+        if (f < 0 || f >= rv.N * rv.fpr) atomicOr(ctrl, APEXB200_ST_BAD_INDEX);
+        else { moving = true; c3 = clock64(); tma_load_frame(rv.frames + f * rv.F, stage, my_bars, (unsigned)rv.F, nch); }
+    }
+    if (lane < C && sa.fsel_out) sa.fsel_out[(long long)w * twoC + k] = (int32_t)f;
+    if (half == 0) {
+        if (lane == 0) {
+            sa.idx_out[w] = (int32_t)node;
+            if (sa.leaf_out) sa.leaf_out[w] = node >= 0 ? leaf : 0ull;
+            if (sa.total_out && w == 0) *sa.total_out = total;
+        }
+        if (node >= 0 && lane == 16) copy_meta_row(rv, ga, w, node);
+    }
+    // drain with a landing timestamp per frame (frames up to 16 KB move as one chunk)
+    uint8_t *dst = moving ? item_dst(rv, ga, w, k) : nullptr;
+    long long c_land = 0;
+    {
+        const unsigned buf_s = (unsigned)__cvta_generic_to_shared(stage);
+        bool pending = moving;
+        while (__any_sync(0xffffffffu, pending)) {
+            if (pending) {
+                const unsigned bar_s = (unsigned)__cvta_generic_to_shared(my_bars);
+                unsigned done;
+                asm volatile("{\n .reg .pred p;\n mbarrier.test_wait.parity.shared::cta.b64 p, [%1], 0;\n"
+                             " selp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(bar_s) : "memory");
+                if (done) {
+                    c_land = clock64();
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                                 ::"l"(dst), "r"(buf_s), "r"((unsigned)rv.F) : "memory");
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    pending = false;
+                }
+            }
+        }
+    }
+    const long long c5 = clock64();
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    const long long c6 = clock64();
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");        // writes complete (measurement only)
+    const long long c7 = clock64();
+    long long lmin = moving ? c_land - c0 : (1ll << 60), lmax = moving ? c_land - c0 : 0, i3 = moving ? c3 - c0 : (1ll << 60);
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        lmin = min(lmin, __shfl_xor_sync(0xffffffffu, lmin, o));
+        lmax = max(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
+        i3 = min(i3, __shfl_xor_sync(0xffffffffu, i3, o));
+    }
+    if (lane == 0 && unit < 2048) {
+        unsigned long long *d = g_dbg_timeline + (size_t)unit * kDbgWords;
+        d[0] = g0; d[1] = (unsigned long long)(c1 - c0); d[2] = (unsigned long long)(c2 - c0); d[3] = (unsigned long long)i3;
+        d[4] = (unsigned long long)lmin; d[5] = (unsigned long long)lmax; d[6] = (unsigned long long)(c5 - c0);
+        d[7] = (unsigned long long)(c6 - c0); d[8] = (unsigned long long)(c7 - c0); d[9] = gtimer();
+        unsigned smid;
+        asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+        d[10] = smid; d[11] = (unsigned long long)blockIdx.x;
+    }
+}
+
 // The same search + gather writing float32 batches (the network's input dtype) instead of uint8.
 __global__ void __launch_bounds__(512)
 sample_gather_f32_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int32_t *ctrl) {
@@ -536,6 +642,8 @@ sample_gather_sharded_polled_kernel(TreeView tv, RingView rv, SampleArgs sa, Gat
     sample_gather_sharded_body<true, false>(tv, rv, sa, ga, sh, pv, ctrl, ready, ready_value);
 }
 
+static inline bool nch_is_one(int frame_bytes) { return frame_bytes <= 16384; }
+
 static int ensure_smem(const void *fn, size_t smem, int device) {
     constexpr int kKernels = 8;
     static const void *known[kKernels] = {};
@@ -558,8 +666,14 @@ using namespace apexb200;
 extern "C" {
 
 int apexb200_set_gather_variant(int32_t variant) {
-    APEX_REQUIRE(variant == 0 || variant == 1, APEXB200_EINVAL, "set_gather_variant: unknown variant %d", variant);
+    APEX_REQUIRE(variant == 0 || variant == 1 || variant == 3, APEXB200_EINVAL, "set_gather_variant: unknown variant %d", variant);
     g_gather_variant = variant;
+    return APEXB200_OK;
+}
+
+int apexb200_debug_timeline(uint64_t *out_host, int32_t units) {
+    APEX_REQUIRE(out_host && units > 0 && units <= 2048, APEXB200_EINVAL, "debug_timeline: bad argument");
+    APEX_CUDA(cudaMemcpyFromSymbol(out_host, g_dbg_timeline, (size_t)units * kDbgWords * 8));
     return APEXB200_OK;
 }
 
@@ -576,7 +690,7 @@ int apexb200_gather(apexb200_replay_t h, const int32_t *idx, const int32_t *fsel
     cudaStream_t st = (cudaStream_t)stream;
     const long long items = (long long)count * 2 * rv.C;
     const long long meta_warps = (count + 31) / 32;
-    if (g_gather_variant == 1 && kBarBytes + (size_t)rv.F <= kStageBudget) {
+    if (g_gather_variant >= 1 && kBarBytes + (size_t)rv.F <= kStageBudget) {
         long long per_cta = (long long)((kStageBudget - kBarBytes) / rv.F);
         if (per_cta > 32) per_cta = 32;
         const long long spread = (items + kNumSMs - 1) / kNumSMs;      // small batches: use every SM
@@ -668,6 +782,12 @@ int run_sample_gather(apexb200_replay *h, const double *u, uint64_t seed, int32_
         return launch_step("sample_gather_polled_kernel", sample_gather_polled_kernel,
                            dim3((unsigned)((units + wpc - 1) / wpc)), dim3(wpc * 32), smem, st, h->tree, rv, sa, ga,
                            h->status, ready, ready_value);
+    }
+    if (g_gather_variant == 3 && nch_is_one(rv.F)) {
+        rc = ensure_smem((const void *)sample_gather_timed_kernel, smem, h->cfg.device);
+        if (rc) return rc;
+        return launch_step("sample_gather_timed_kernel", sample_gather_timed_kernel, dim3((unsigned)((units + wpc - 1) / wpc)),
+                           dim3(wpc * 32), smem, st, h->tree, rv, sa, ga, h->status);
     }
     return launch_step("sample_gather_kernel", sample_gather_kernel, dim3((unsigned)((units + wpc - 1) / wpc)),
                        dim3(wpc * 32), smem, st, h->tree, rv, sa, ga, h->status);

@@ -83,12 +83,27 @@ __device__ __forceinline__ float block_sum_fixed(float v, float *warp_part) {
 // wins without any atomics; an unsorted batch falls back to the stamp protocol of K2.
 // The old leaf is fetched up front, in parallel with the Q rows, to keep the chain of
 // dependent memory round trips at two.
+// Measurement aid (builds with -DAPEX_TD_TIMELINE only): global-timer stamps of the last td_small_kernel launch
+// {entry, dependency wait done, thread 0 at the end}, read back with apexb200_debug_td_timeline.
+__device__ unsigned long long g_dbg_td[4];
+__device__ __forceinline__ unsigned long long td_gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
 __global__ void __launch_bounds__(1024)
 td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t *__restrict__ stamp,
                 int32_t *status, PeerView pv, int push) {
     __shared__ float warp_part[32];
     __shared__ unsigned long long delta_part[32];
+#ifdef APEX_TD_TIMELINE
+    if (threadIdx.x == 0) g_dbg_td[0] = td_gtimer();
+#endif
     pdl_prologue();
+#ifdef APEX_TD_TIMELINE
+    if (threadIdx.x == 0) g_dbg_td[1] = td_gtimer();
+#endif
     if (idx != nullptr) bump_epoch(status);
     const int live = live_rows(a);
     // multi-GPU push (see below): the shard total before this update, read by warp 0 while the batch
@@ -184,6 +199,9 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
     }
     float s = block_sum_fixed(l_acc, warp_part);
     if (threadIdx.x == 0) *a.loss_mean = s / mean_div(a);
+#ifdef APEX_TD_TIMELINE
+    if (threadIdx.x == 0) g_dbg_td[2] = td_gtimer();
+#endif
 }
 
 // ---- B <= 1024 as one thread-block cluster: ceil(B/128) CTAs of 128 rows on as many SMs
@@ -550,6 +568,12 @@ static int noalloc_scratch_of_current_device(void **out) {
 using namespace apexb200;
 
 extern "C" {
+
+int apexb200_debug_td_timeline(uint64_t *out_host) {
+    APEX_REQUIRE(out_host, APEXB200_EINVAL, "debug_td_timeline: null argument");
+    APEX_CUDA(cudaMemcpyFromSymbol(out_host, g_dbg_td, sizeof(unsigned long long) * 4));
+    return APEXB200_OK;
+}
 
 int apexb200_td_workspace_bytes(int32_t B, int64_t *bytes_host) {
     APEX_REQUIRE(bytes_host && B > 0, APEXB200_EINVAL, "td_workspace_bytes: bad argument");

@@ -194,8 +194,16 @@ int apexb200_sample_targets(apexb200_replay_t h, const uint64_t *targets, const 
 int apexb200_gather(apexb200_replay_t h, const int32_t *idx, const int32_t *fsel, int32_t count,
                     const int32_t *count_dev, uint8_t *S_t, uint8_t *S_tpn, int32_t *A, float *R,
                     float *Gamma, float *q_t, float *q_tpn, void *stream);
-/* 0 = per-warp 16-byte vector copy, 1 (default) = TMA bulk copy staged through shared memory. */
+/* 0 = per-warp 16-byte vector copy, 1 (default) = TMA bulk copy staged through shared memory.
+ * Measurement aid for the fused kernel only: 3 = the default kernel with per-warp timestamps, read back
+ * (synchronously) with apexb200_debug_timeline: out_host [units][12] u64 = global timer at entry, SM-clock
+ * offsets of {dependency wait done, search done, loads issued, first / last frame landed, stores issued,
+ * staging free, writes complete}, global timer at exit, SM id, CTA id (units = half draws, <= 2048). */
 int apexb200_set_gather_variant(int32_t variant);
+int apexb200_debug_timeline(uint64_t *out_host, int32_t units);
+/* out_host [4] u64: global-timer stamps {entry, dependency wait done, end of thread 0} of the last single-CTA
+ * TD/update launch; all zero unless the library was built with -DAPEX_TD_TIMELINE (tools/timeline.py). */
+int apexb200_debug_td_timeline(uint64_t *out_host);
 /* K3 + K4 in one launch: ReplayMemory.sample (replay.py:44-57) as a whole.  u [count]
  * as in apexb200_sample, or NULL for the in-kernel stratified draws of
  * apexb200_sample_stratified (seed, u_out).  One warp per half draw (S_t or S_tpn): the
