@@ -136,8 +136,10 @@ __device__ __forceinline__ unsigned long long read_epoch(const int32_t *ctrl) {
     return *(const volatile unsigned long long *)(ctrl + 4);
 }
 __device__ __forceinline__ void bump_epoch(int32_t *ctrl) {        // one thread of a tree-changing kernel
+    // a reduction without return value: the issuing warp does not wait for the round trip a volatile read-modify-
+    // write would cost it at the head of the kernel (writers of one handle are ordered by the stream)
     if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0)
-        *(volatile unsigned long long *)(ctrl + 4) += 1ull;
+        atomicAdd((unsigned long long *)(ctrl + 4), 1ull);
 }
 
 // The same for a full warp whose leaves are adjacent in index order (sorted batch rows, or the

@@ -35,7 +35,7 @@ __device__ __forceinline__ float mean_div(const TdArgs &a) { return a.divisor > 
 
 // learner.py:43-50 for one record.  Explicit _rn intrinsics keep the compiler from
 // contracting R + Gamma*q into an FMA, so delta/loss equal a plain fp32 evaluation.
-__device__ __forceinline__ float td_one(const TdArgs &a, int b, float *loss_out) {
+__device__ __forceinline__ float td_one(const TdArgs &a, int b, float *loss_out, float *prio_out = nullptr) {
     const float *row_t = a.q_on_t + (long long)b * a.nA;
     const float *row_n = a.q_on_tpn + (long long)b * a.nA;
     const float *row_g = a.q_tg_tpn + (long long)b * a.nA;
@@ -54,11 +54,67 @@ __device__ __forceinline__ float td_one(const TdArgs &a, int b, float *loss_out)
     if (a.loss_kind == APEXB200_LOSS_HALF_SQ) l = __fmul_rn(__fmul_rn(0.5f, d), d);   // learner.py:48
     else l = ad <= a.kappa ? __fmul_rn(__fmul_rn(0.5f, d), d) : __fmul_rn(a.kappa, __fsub_rn(ad, 0.5f * a.kappa));
     if (a.weights) l = __fmul_rn(l, a.weights[b]);                              // importance-sampling correction
+    const float pr = prio_pow(ad, a.alpha, a.eps);                              // learner.py:50 + replay.py:24
     a.delta[b] = d;
-    a.prio[b] = prio_pow(ad, a.alpha, a.eps);                                   // learner.py:50 + replay.py:24
+    a.prio[b] = pr;
     a.loss[b] = l;
     *loss_out = l;
+    if (prio_out) *prio_out = pr;
     return d;
+}
+
+// The inputs of one record fetched up front, before anything is used: a warp issues in order, so a dependent pair
+// (row of Q(S_tpn) -> the selected entry of Q_target(S_tpn); record index -> its leaf) otherwise costs two memory
+// round trips one after the other.  Rows of 4 actions (the Atari action set of parameters.json) are single 16-byte
+// loads.  td_row_finish performs the same operations on the same values as td_one: delta / loss / priority are
+// bit-identical.
+struct TdRow4 {
+    float4 qn, qg, qt;
+    int act;
+    float r, g, w;
+};
+__device__ __forceinline__ bool td_rows_are_vec4(const TdArgs &a) {
+    return a.nA == 4 && ((((uintptr_t)a.q_on_t | (uintptr_t)a.q_on_tpn | (uintptr_t)a.q_tg_tpn) & 15) == 0);
+}
+__device__ __forceinline__ TdRow4 td_row_load4(const TdArgs &a, int b) {
+    TdRow4 x;
+    x.qn = ((const float4 *)a.q_on_tpn)[b];
+    x.qg = ((const float4 *)a.q_tg_tpn)[b];
+    x.qt = ((const float4 *)a.q_on_t)[b];
+    x.act = a.A[b];
+    x.r = a.R[b];
+    x.g = a.G[b];
+    x.w = a.weights ? a.weights[b] : 1.0f;
+    return x;
+}
+__device__ __forceinline__ float td_row_finish4(const TdArgs &a, int b, const TdRow4 &x, float *loss_out) {
+    const float qn[4] = {x.qn.x, x.qn.y, x.qn.z, x.qn.w}, qg[4] = {x.qg.x, x.qg.y, x.qg.z, x.qg.w},
+                qt[4] = {x.qt.x, x.qt.y, x.qt.z, x.qt.w};
+    int arg = 0;
+    float best = qn[0];
+    #pragma unroll
+    for (int k = 1; k < 4; ++k)
+        if (qn[k] > best) { best = qn[k]; arg = k; }             // first maximum on ties (argmax, learner.py:45)
+    const int act = x.act < 0 ? 0 : (x.act > 3 ? 3 : x.act);
+    float g_sel = qg[0], t_sel = qt[0];
+    #pragma unroll
+    for (int k = 1; k < 4; ++k) {
+        if (k == arg) g_sel = qg[k];
+        if (k == act) t_sel = qt[k];
+    }
+    const float target = __fadd_rn(x.r, __fmul_rn(x.g, g_sel));                  // learner.py:44
+    const float d = __fsub_rn(target, t_sel);                                    // learner.py:47
+    const float ad = fabsf(d);
+    float l;
+    if (a.loss_kind == APEXB200_LOSS_HALF_SQ) l = __fmul_rn(__fmul_rn(0.5f, d), d);   // learner.py:48
+    else l = ad <= a.kappa ? __fmul_rn(__fmul_rn(0.5f, d), d) : __fmul_rn(a.kappa, __fsub_rn(ad, 0.5f * a.kappa));
+    if (a.weights) l = __fmul_rn(l, x.w);
+    const float pr = prio_pow(ad, a.alpha, a.eps);                               // learner.py:50 + replay.py:24
+    a.delta[b] = d;
+    a.prio[b] = pr;
+    a.loss[b] = l;
+    *loss_out = l;
+    return pr;
 }
 
 // Fixed-shape block sum: xor-shuffle tree inside each warp, then warp partials
@@ -85,7 +141,12 @@ __device__ __forceinline__ float block_sum_fixed(float v, float *warp_part) {
 // dependent memory round trips at two.
 // Measurement aid (builds with -DAPEX_TD_TIMELINE only): global-timer stamps of the last td_small_kernel launch
 // {entry, dependency wait done, thread 0 at the end}, read back with apexb200_debug_td_timeline.
-__device__ unsigned long long g_dbg_td[4];
+__device__ unsigned long long g_dbg_td[8];
+#ifdef APEX_TD_TIMELINE
+#define TD_STAMP(k) do { if (threadIdx.x == 0) g_dbg_td[k] = td_gtimer(); } while (0)
+#else
+#define TD_STAMP(k) do { } while (0)
+#endif
 __device__ __forceinline__ unsigned long long td_gtimer() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -124,6 +185,7 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
     // complete in itself (vote, leaf writes, ancestor updates), passes run in batch order, so "last row wins"
     // holds across them as well.
     const int passes = live > (int)blockDim.x ? (live + (int)blockDim.x - 1) / (int)blockDim.x : 1;
+    const bool vec4 = td_rows_are_vec4(a);
     float l_acc = 0.0f;
     unsigned long long d_acc = 0ull;
     for (int pass = 0; pass < passes; ++pass) {
@@ -132,18 +194,24 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
         long long i = -1;
         bool in_order = true, last_of_run = true;
         unsigned long long old = 0ull;
+        float pr = 0.0f;                                         // this row's |delta|^alpha, kept in a register
         if (b < live) {
+            long long nxt = 1ll << 40;
+            TdRow4 row;
+            if (vec4) row = td_row_load4(a, b);                   // all loads of the row in flight ...
             if (idx != nullptr) {
-                i = idx[b];
-                const long long nxt = (b + 1 < live) ? (long long)idx[b + 1] : (1ll << 40);
+                i = idx[b];                                       // ... together with the record index
+                if (b + 1 < live) nxt = (long long)idx[b + 1];
                 in_order = i <= nxt;
                 last_of_run = i != nxt;
                 if (i < 0 || i >= tv.size[0]) { atomicOr(status, APEXB200_ST_BAD_INDEX); i = -1; }
-                else old = tv.lvl[0][i];
+                else old = tv.lvl[0][i];                          // second (and last) dependent round trip
             }
-            td_one(a, b, &l);
+            if (vec4) pr = td_row_finish4(a, b, row, &l);
+            else td_one(a, b, &l, &pr);
         }
         l_acc += l;
+        TD_STAMP(3);
         const int sorted = __syncthreads_and(in_order);
         bool winner = (i >= 0) && last_of_run;
         if (!sorted) {
@@ -154,11 +222,12 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
         }
         unsigned long long d = 0ull;
         if (winner) {
-            unsigned long long nl = leaf_from_prio(a.prio[b]);
+            unsigned long long nl = leaf_from_prio(pr);
             tv.lvl[0][i] = nl;
             d = nl - old;
         }
         d_acc += d;
+        TD_STAMP(4);
         if (push && pass == passes - 1) {
             // Fused collective (multi-GPU): publish this shard's new total to every peer from the
             // kernel that produced it — the next step's sharded sample on each rank waits for these
@@ -195,12 +264,14 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
             // Sorted record indices (stratified draws): one atomic per distinct ancestor per warp
             warp_propagate_adjacent(tv, i, d);
         }
+        TD_STAMP(5);
         if (pass + 1 < passes) __syncthreads();                // the next pass reads leaves this one wrote
     }
     float s = block_sum_fixed(l_acc, warp_part);
     if (threadIdx.x == 0) *a.loss_mean = s / mean_div(a);
 #ifdef APEX_TD_TIMELINE
     if (threadIdx.x == 0) g_dbg_td[2] = td_gtimer();
+    if (threadIdx.x == blockDim.x - 1) g_dbg_td[6] = td_gtimer();
 #endif
 }
 
@@ -571,7 +642,7 @@ extern "C" {
 
 int apexb200_debug_td_timeline(uint64_t *out_host) {
     APEX_REQUIRE(out_host, APEXB200_EINVAL, "debug_td_timeline: null argument");
-    APEX_CUDA(cudaMemcpyFromSymbol(out_host, g_dbg_td, sizeof(unsigned long long) * 4));
+    APEX_CUDA(cudaMemcpyFromSymbol(out_host, g_dbg_td, sizeof(unsigned long long) * 8));
     return APEXB200_OK;
 }
 

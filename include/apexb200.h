@@ -201,8 +201,9 @@ int apexb200_gather(apexb200_replay_t h, const int32_t *idx, const int32_t *fsel
  * staging free, writes complete}, global timer at exit, SM id, CTA id (units = half draws, <= 2048). */
 int apexb200_set_gather_variant(int32_t variant);
 int apexb200_debug_timeline(uint64_t *out_host, int32_t units);
-/* out_host [4] u64: global-timer stamps {entry, dependency wait done, end of thread 0} of the last single-CTA
- * TD/update launch; all zero unless the library was built with -DAPEX_TD_TIMELINE (tools/timeline.py). */
+/* out_host [8] u64: global-timer stamps of the last single-CTA TD/update launch — [0] entry, [1] dependency wait
+ * done, [3] rows evaluated, [4] leaves written, [5] ancestor updates issued, [2] end of thread 0, [6] end of the
+ * last thread; all zero unless the library was built with -DAPEX_TD_TIMELINE (tools/timeline.py). */
 int apexb200_debug_td_timeline(uint64_t *out_host);
 /* K3 + K4 in one launch: ReplayMemory.sample (replay.py:44-57) as a whole.  u [count]
  * as in apexb200_sample, or NULL for the in-kernel stratified draws of

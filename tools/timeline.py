@@ -60,7 +60,7 @@ def main():
         buf = (C.c_uint64 * (units * 12))()
         apex_b200._C.call("apexb200_debug_timeline", buf, units)
         d = np.frombuffer(buf, dtype=np.uint64).reshape(units, 12).astype(np.int64)
-        td = (C.c_uint64 * 4)()
+        td = (C.c_uint64 * 8)()
         apex_b200._C.call("apexb200_debug_td_timeline", td)
         td = [int(x) for x in td]
         names = ["dependency wait done", "search done", "loads issued (first lane)", "first frame landed", "last frame landed",
@@ -74,6 +74,9 @@ def main():
         print("  global timer: entry spread %.2f us, first entry -> last exit %.2f us" %
               ((g0.max() - g0.min()) / 1e3, (g9.max() - g0.min()) / 1e3))
         if td[0] and mode.startswith("step"):
+            print("  TD kernel body (thread 0, us after its dependency wait): rows evaluated %.2f, leaves written %.2f, ancestor "
+                  "updates issued %.2f, loss reduced / end %.2f (last thread %.2f)" %
+                  tuple((td[k] - td[1]) / 1e3 for k in (3, 4, 5, 2, 6)))
             wait_done = g0 + (d[:, 1] / a.mhz * 1e3).astype(np.int64)      # absolute time the sample warps were released
             if mode.endswith("sample"):      # ... TD(8) -> sample(9): stamps of the TD kernel that precedes this sample
                 print("  TD kernel before this sample: entry -> wait done %.2f us, wait done -> thread 0 end %.2f us, "
