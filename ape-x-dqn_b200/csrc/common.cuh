@@ -224,7 +224,14 @@ __device__ __forceinline__ double strat_uniform(unsigned long long seed, unsigne
     z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
     z ^= z >> 31;
     const double v = (double)(z >> 11) * 0x1.0p-53;
-    return ((double)j + v) / (double)count;                 // u_j = (j + v_j) / B
+    // u_j = (j + v_j) / B.  For a power-of-two B the quotient is an exact scaling by 2^-k: one multiply gives the
+    // same bits as the fp64 division, which is a long dependent instruction sequence in front of the tree search
+    // (0.3 us of every sampling launch, tools/timeline.py)
+    if ((count & (count - 1)) == 0) {
+        const int k = 31 - __clz(count);
+        return ((double)j + v) * __longlong_as_double((long long)(1023 - k) << 52);
+    }
+    return ((double)j + v) / (double)count;
 }
 
 // K3 core.  One warp per draw.  At each level the warp loads the 32 children of the
@@ -268,9 +275,12 @@ __device__ __forceinline__ unsigned long long warp_inclusive_scan(unsigned long 
     return incl;
 }
 
+// `stamps` (measurement aid, normally null and compiled away): clock64() when the search of the top level(s) is
+// done and after every further level.
 __device__ __forceinline__ long long warp_descend(const TreeView &tv, const TopValues &vtop, unsigned long long t,
                                                   bool from_u, double u, unsigned long long *leaf,
-                                                  unsigned long long *total, int32_t *status) {
+                                                  unsigned long long *total, int32_t *status,
+                                                  long long *stamps = nullptr) {
     const int lane = threadIdx.x & 31;
     const int top = tv.n_levels - 1;
     const bool merged = top_is_merged(tv);
@@ -315,6 +325,8 @@ __device__ __forceinline__ long long warp_descend(const TreeView &tv, const TopV
         t -= excl;
         node = c;
     }
+    int n_stamp = 0;
+    if (stamps) stamps[n_stamp++] = clock64();
     for (int l = first; l >= 0; --l) {
         const unsigned long long v = tv.lvl[l][node * kFanout + lane];      // padded levels: in bounds
         const unsigned long long incl = warp_inclusive_scan(v, lane);
@@ -324,6 +336,7 @@ __device__ __forceinline__ long long warp_descend(const TreeView &tv, const TopV
         if (l == 0) lf = __shfl_sync(0xffffffffu, v, c);
         t -= excl;
         node = node * kFanout + c;
+        if (stamps && n_stamp < 6) stamps[n_stamp++] = clock64();
     }
     *leaf = lf;
     return node;

@@ -142,7 +142,8 @@ __device__ __forceinline__ void tma_issue_frame(const uint8_t *src, uint8_t *sta
 // stores of early frames overlap the loads of late ones (a blocking wait would hold the
 // whole warp until its slowest frame arrived).  Must be called by all 32 lanes.
 __device__ __forceinline__ void tma_drain_frames(bool moving, uint8_t *dst, uint8_t *stage, unsigned long long *bars,
-                                                 unsigned bytes, int nch, unsigned parity = 0u) {
+                                                 unsigned bytes, int nch, unsigned parity = 0u,
+                                                 long long *landed = nullptr) {
     const unsigned buf_s = (unsigned)__cvta_generic_to_shared(stage);
     const unsigned chunk = bytes / nch;
     int next = moving ? 0 : nch;                     // next chunk this lane has to store
@@ -153,6 +154,7 @@ __device__ __forceinline__ void tma_drain_frames(bool moving, uint8_t *dst, uint
             asm volatile("{\n .reg .pred p;\n mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
                          " selp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(bar_s), "r"(parity) : "memory");
             if (done) {
+                if (landed) *landed = clock64();             // measurement aid (null and compiled away otherwise)
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
                              ::"l"(dst + next * chunk), "r"(buf_s + next * chunk), "r"(chunk) : "memory");
@@ -161,7 +163,39 @@ __device__ __forceinline__ void tma_drain_frames(bool moving, uint8_t *dst, uint
             }
         }
     }
-    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    if (landed == nullptr) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+// Blocking wait for every chunk of this lane's frame (phase `parity`).
+__device__ __forceinline__ void tma_wait_frame(unsigned long long *bars, int nch, unsigned parity) {
+    for (int c = 0; c < nch; ++c) {
+        const unsigned bar_s = (unsigned)__cvta_generic_to_shared(bars + c);
+        unsigned done = 0u;
+        while (!done)
+            asm volatile("{\n .reg .pred p;\n mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+                         " selp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(bar_s), "r"(parity) : "memory");
+    }
+}
+
+// The frame slot a record's frame-slot row holds in the common case, computed without touching memory: record
+// `node` of a frame-once ("stream") ring looks back over fixed offsets (S_tpn = the C frames ending at its own,
+// S_t = the C frames ending n steps earlier, n = lookback - (C - 1)) unless it lies within C - 1 + n steps of an
+// episode start; a record that owns its frames (materialised layout) names them in order.  Always a valid slot of
+// the record's own lane; the row itself decides (see the fused kernels).
+__device__ __forceinline__ long long guess_frame_slot(const RingView &rv, long long node, int k) {
+    const unsigned lane_cap = (unsigned)rv.lane_cap;
+    const unsigned ring_lane = (unsigned)node / lane_cap, p = (unsigned)node - ring_lane * lane_cap;
+    const long long lane_frames = rv.lane_cap * rv.fpr;
+    int rel;
+    if (rv.fpr == 1) {
+        const int back = rv.C - 1 - (k < rv.C ? k : k - rv.C);
+        rel = k < rv.C ? -(rv.lookback - (rv.C - 1) + back) : -back;
+    } else {
+        rel = k - (2 * rv.C - 1);
+    }
+    long long f = (long long)p * rv.fpr + rv.fpr - 1 + rel;
+    if (f < 0) f += lane_frames;
+    return (long long)ring_lane * lane_frames + f;
 }
 
 // float32 outputs (the dtype the learner's network consumes, learner.py:37-38): the bulk-copy engine cannot
@@ -171,10 +205,11 @@ __device__ __forceinline__ void tma_drain_frames(bool moving, uint8_t *dst, uint
 // Must be called by all 32 lanes.
 __device__ __forceinline__ void f32_drain_frames(bool moving, uint8_t *dst, const uint8_t *warp_stage,
                                                  unsigned long long *warp_bars, int C, unsigned bytes, int nch,
-                                                 unsigned parity) {
+                                                 unsigned my_parity) {
     const int lane = threadIdx.x & 31;
     const unsigned mask = __ballot_sync(0xffffffffu, moving);
     for (int c = 0; c < C; ++c) {
+        const unsigned parity = __shfl_sync(0xffffffffu, my_parity, c);    // phase of the owning lane's barrier
         if (!((mask >> c) & 1u)) continue;
         for (int ch = 0; ch < nch; ++ch) {
             const unsigned bar_s = (unsigned)__cvta_generic_to_shared(warp_bars + c * kMaxChunks + ch);
@@ -270,13 +305,26 @@ gather_tma_kernel(RingView rv, GatherArgs ga, int per_cta, int32_t *status) {
 // index and metadata outputs.  Half draws as the unit of work balance the frames over the
 // SMs: a B=512, C=4 batch is 1024 units = 147 CTAs of 7 warps (28 frames, 193 KB of
 // staging each), one CTA per SM, every frame of the batch in flight at once.
-template <bool kPolled, bool kF32>
+constexpr int kDbgWords = 20;
+__device__ unsigned long long g_dbg_timeline[2048 * kDbgWords];      // written by the instrumented kernel only
+
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// kTimed: the same code plus per-warp timestamps in g_dbg_timeline (apexb200_set_gather_variant(3), measurement aid).
+template <bool kPolled, bool kF32, bool kTimed>
 __device__ __forceinline__ void sample_gather_body(const TreeView &tv, const RingView &rv, const SampleArgs &sa,
                                                    const GatherArgs &ga, int32_t *ctrl, const unsigned *ready,
                                                    unsigned ready_value) {
     extern __shared__ __align__(128) uint8_t smem[];
     unsigned long long *bars = (unsigned long long *)smem;
+    const unsigned long long g0 = kTimed ? gtimer() : 0ull;
+    const long long c0 = kTimed ? clock64() : 0ll;
     pdl_prologue();
+    const long long c1 = kTimed ? clock64() : 0ll;
     const int lane = threadIdx.x & 31;
     const int wl = threadIdx.x >> 5;
     const int wpc = blockDim.x >> 5;
@@ -313,17 +361,25 @@ __device__ __forceinline__ void sample_gather_body(const TreeView &tv, const Rin
         uw = __ldcg(sa.u + w);                               // bypass L1: written by DMA while this CTA was resident
     }
     unsigned long long leaf, total;
-    const long long node = warp_descend(tv, vtop, 0ull, true, uw, &leaf, &total, ctrl);
+    long long lv[6] = {0, 0, 0, 0, 0, 0};
+    const long long c1b = kTimed ? clock64() : 0ll;
+    const long long node = warp_descend(tv, vtop, 0ull, true, uw, &leaf, &total, ctrl, kTimed ? lv : nullptr);
+    const long long c2 = kTimed ? clock64() : 0ll;
     const int k = half * C + lane;                           // this lane's frame among the record's 2C
-    long long f = -1;
-    if (node >= 0 && lane < C) f = rv.fidx[node * twoC + k];
-    bool moving = false;
-    if (node >= 0 && lane < C) {
-        if (f < 0 || f >= rv.N * rv.fpr) atomicOr(ctrl, APEXB200_ST_BAD_INDEX);
-        else { moving = true; tma_load_frame(rv.frames + f * rv.F, stage, my_bars, (unsigned)rv.F, nch); }
+    // The record's frame-slot row sits in HBM: one more dependent round trip before the first frame byte could
+    // move.  The frame copy is therefore started on the slot the row holds in the common case (guess_frame_slot)
+    // while the row itself is in flight, and the row decides afterwards: a lane whose guess was wrong (a record
+    // next to an episode start) waits for the stray copy to land and fetches the right frame into the same
+    // staging buffer (second phase of its mbarriers).
+    long long f = -1, fg = -1, c3 = 0;
+    const bool mine = node >= 0 && lane < C;
+    if (mine) {
+        f = rv.fidx[node * twoC + k];                        // issued now, used after the speculative copy is on its way
+        fg = guess_frame_slot(rv, node, k);
+        if (kTimed) c3 = clock64();
+        tma_load_frame(rv.frames + fg * rv.F, stage, my_bars, (unsigned)rv.F, nch);
     }
     // bookkeeping overlaps the frame loads
-    if (lane < C && sa.fsel_out) sa.fsel_out[(long long)w * twoC + k] = (int32_t)f;
     if (half == 0) {
         if (lane == 0) {
             sa.idx_out[w] = (int32_t)node;
@@ -332,135 +388,72 @@ __device__ __forceinline__ void sample_gather_body(const TreeView &tv, const Rin
         }
         if (node >= 0 && lane == 16) copy_meta_row(rv, ga, w, node);
     }
+    if (lane < C && sa.fsel_out) sa.fsel_out[(long long)w * twoC + k] = (int32_t)f;
+    bool moving = mine;
+    unsigned parity = 0u;
+    if (mine && f != fg) {
+        const bool valid = f >= 0 && f < rv.N * rv.fpr;
+        if (!valid) atomicOr(ctrl, APEXB200_ST_BAD_INDEX);
+        tma_wait_frame(my_bars, nch, 0u);                    // the stray copy has landed: the buffer is free again
+        moving = valid;
+        if (valid) { tma_issue_frame(rv.frames + f * rv.F, stage, my_bars, (unsigned)rv.F, nch); parity = 1u; }
+    }
+    uint8_t *dst = moving ? item_dst(rv, ga, w, k) : nullptr;
+    long long c_land = 0;
     if (kF32)
-        f32_drain_frames(moving, moving ? item_dst(rv, ga, w, k) : nullptr, stage - (size_t)lane * rv.F,
-                         my_bars - lane * kMaxChunks, C, (unsigned)rv.F, nch, 0u);
+        f32_drain_frames(moving, dst, stage - (size_t)lane * rv.F, my_bars - lane * kMaxChunks, C, (unsigned)rv.F, nch, parity);
     else
-        tma_drain_frames(moving, moving ? item_dst(rv, ga, w, k) : nullptr, stage, my_bars, (unsigned)rv.F, nch);
+        tma_drain_frames(moving, dst, stage, my_bars, (unsigned)rv.F, nch, parity, kTimed ? &c_land : nullptr);
+    if (kTimed) {
+        const long long c5 = clock64();
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        const long long c6 = clock64();
+        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");        // writes complete (measurement only)
+        const long long c7 = clock64();
+        long long lmin = moving ? c_land - c0 : (1ll << 60), lmax = moving ? c_land - c0 : 0, i3 = mine ? c3 - c0 : (1ll << 60);
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lmin = min(lmin, __shfl_xor_sync(0xffffffffu, lmin, o));
+            lmax = max(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
+            i3 = min(i3, __shfl_xor_sync(0xffffffffu, i3, o));
+        }
+        const unsigned wrong = __popc(__ballot_sync(0xffffffffu, mine && f != fg));
+        if (lane == 0 && unit < 2048) {
+            unsigned long long *d = g_dbg_timeline + (size_t)unit * kDbgWords;
+            d[0] = g0; d[1] = (unsigned long long)(c1 - c0); d[2] = (unsigned long long)(c2 - c0); d[3] = (unsigned long long)i3;
+            d[4] = (unsigned long long)lmin; d[5] = (unsigned long long)lmax; d[6] = (unsigned long long)(c5 - c0);
+            d[7] = (unsigned long long)(c6 - c0); d[8] = (unsigned long long)(c7 - c0); d[9] = gtimer();
+            unsigned smid;
+            asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+            d[10] = smid; d[11] = (unsigned long long)blockIdx.x | ((unsigned long long)wrong << 32);
+            d[12] = (unsigned long long)(c1b - c0);
+            for (int q = 0; q < 6; ++q) d[13 + q] = lv[q] ? (unsigned long long)(lv[q] - c0) : 0ull;
+        }
+    }
 }
 
 __global__ void __launch_bounds__(512)
 sample_gather_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int32_t *ctrl) {
-    sample_gather_body<false, false>(tv, rv, sa, ga, ctrl, nullptr, 0u);
+    sample_gather_body<false, false, false>(tv, rv, sa, ga, ctrl, nullptr, 0u);
 }
 
-// ---- instrumented copy of the fused kernel (apexb200_set_gather_variant(3)): same work, plus per-warp timestamps
-// (SM clock, relative to the warp's first instruction; global timer at entry and exit) in a static debug array
-// read back with apexb200_debug_timeline.  Measurement aid only.
-constexpr int kDbgWords = 12;
-__device__ unsigned long long g_dbg_timeline[2048 * kDbgWords];
-
-__device__ __forceinline__ unsigned long long gtimer() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-    return t;
-}
-
+// Instrumented instantiation of the same body (apexb200_set_gather_variant(3)); read back with apexb200_debug_timeline.
 __global__ void __launch_bounds__(512)
 sample_gather_timed_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int32_t *ctrl) {
-    extern __shared__ __align__(128) uint8_t smem[];
-    unsigned long long *bars = (unsigned long long *)smem;
-    const unsigned long long g0 = gtimer();
-    const long long c0 = clock64();
-    pdl_prologue();
-    const long long c1 = clock64();
-    const int lane = threadIdx.x & 31;
-    const int wl = threadIdx.x >> 5;
-    const int wpc = blockDim.x >> 5;
-    const int nch = frame_chunks(rv.F);
-    const int unit = blockIdx.x * wpc + wl;
-    const int w = unit >> 1, half = unit & 1;
-    const int count = ga.count;
-    const int C = rv.C, twoC = 2 * rv.C;
-    if (w >= count) return;
-    uint8_t *stage = smem + (size_t)wpc * 8 * kMaxChunks * 8 + (size_t)(wl * C + lane) * rv.F;
-    unsigned long long *my_bars = bars + (wl * 8 + lane) * kMaxChunks;
-    const TopValues vtop = top_level_value(tv);
-    double uw;
-    if (sa.u == nullptr) {
-        uw = strat_uniform(sa.seed, read_epoch(ctrl), sa.call, w, count);
-        if (sa.u_out && lane == 0 && half == 0) sa.u_out[w] = uw;
-    } else {
-        uw = sa.u[w];
-    }
-    unsigned long long leaf, total;
-    const long long node = warp_descend(tv, vtop, 0ull, true, uw, &leaf, &total, ctrl);
-    const long long c2 = clock64();
-    const int k = half * C + lane;
-    long long f = -1;
-    if (node >= 0 && lane < C) f = rv.fidx[node * twoC + k];
-    bool moving = false;
-    long long c3 = 0;
-    if (node >= 0 && lane < C) {
-        if (f < 0 || f >= rv.N * rv.fpr) atomicOr(ctrl, APEXB200_ST_BAD_INDEX);
-        else { moving = true; c3 = clock64(); tma_load_frame(rv.frames + f * rv.F, stage, my_bars, (unsigned)rv.F, nch); }
-    }
-    if (lane < C && sa.fsel_out) sa.fsel_out[(long long)w * twoC + k] = (int32_t)f;
-    if (half == 0) {
-        if (lane == 0) {
-            sa.idx_out[w] = (int32_t)node;
-            if (sa.leaf_out) sa.leaf_out[w] = node >= 0 ? leaf : 0ull;
-            if (sa.total_out && w == 0) *sa.total_out = total;
-        }
-        if (node >= 0 && lane == 16) copy_meta_row(rv, ga, w, node);
-    }
-    // drain with a landing timestamp per frame (frames up to 16 KB move as one chunk)
-    uint8_t *dst = moving ? item_dst(rv, ga, w, k) : nullptr;
-    long long c_land = 0;
-    {
-        const unsigned buf_s = (unsigned)__cvta_generic_to_shared(stage);
-        bool pending = moving;
-        while (__any_sync(0xffffffffu, pending)) {
-            if (pending) {
-                const unsigned bar_s = (unsigned)__cvta_generic_to_shared(my_bars);
-                unsigned done;
-                asm volatile("{\n .reg .pred p;\n mbarrier.test_wait.parity.shared::cta.b64 p, [%1], 0;\n"
-                             " selp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(bar_s) : "memory");
-                if (done) {
-                    c_land = clock64();
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
-                                 ::"l"(dst), "r"(buf_s), "r"((unsigned)rv.F) : "memory");
-                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-                    pending = false;
-                }
-            }
-        }
-    }
-    const long long c5 = clock64();
-    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-    const long long c6 = clock64();
-    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");        // writes complete (measurement only)
-    const long long c7 = clock64();
-    long long lmin = moving ? c_land - c0 : (1ll << 60), lmax = moving ? c_land - c0 : 0, i3 = moving ? c3 - c0 : (1ll << 60);
-    #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        lmin = min(lmin, __shfl_xor_sync(0xffffffffu, lmin, o));
-        lmax = max(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
-        i3 = min(i3, __shfl_xor_sync(0xffffffffu, i3, o));
-    }
-    if (lane == 0 && unit < 2048) {
-        unsigned long long *d = g_dbg_timeline + (size_t)unit * kDbgWords;
-        d[0] = g0; d[1] = (unsigned long long)(c1 - c0); d[2] = (unsigned long long)(c2 - c0); d[3] = (unsigned long long)i3;
-        d[4] = (unsigned long long)lmin; d[5] = (unsigned long long)lmax; d[6] = (unsigned long long)(c5 - c0);
-        d[7] = (unsigned long long)(c6 - c0); d[8] = (unsigned long long)(c7 - c0); d[9] = gtimer();
-        unsigned smid;
-        asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
-        d[10] = smid; d[11] = (unsigned long long)blockIdx.x;
-    }
+    sample_gather_body<false, false, true>(tv, rv, sa, ga, ctrl, nullptr, 0u);
 }
 
 // The same search + gather writing float32 batches (the network's input dtype) instead of uint8.
 __global__ void __launch_bounds__(512)
 sample_gather_f32_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int32_t *ctrl) {
-    sample_gather_body<false, true>(tv, rv, sa, ga, ctrl, nullptr, 0u);
+    sample_gather_body<false, true, false>(tv, rv, sa, ga, ctrl, nullptr, 0u);
 }
 
 // Same kernel for the host-facing step: waits in-kernel for the arrival word of its draws.
 __global__ void __launch_bounds__(512)
 sample_gather_polled_kernel(TreeView tv, RingView rv, SampleArgs sa, GatherArgs ga, int32_t *ctrl,
                             const unsigned *ready, unsigned ready_value) {
-    sample_gather_body<true, false>(tv, rv, sa, ga, ctrl, ready, ready_value);
+    sample_gather_body<true, false, false>(tv, rv, sa, ga, ctrl, ready, ready_value);
 }
 
 // ---- fused K8 + K3 + K4 for one rank of a sharded replay (after shard_exchange_kernel).
@@ -642,8 +635,6 @@ sample_gather_sharded_polled_kernel(TreeView tv, RingView rv, SampleArgs sa, Gat
     sample_gather_sharded_body<true, false>(tv, rv, sa, ga, sh, pv, ctrl, ready, ready_value);
 }
 
-static inline bool nch_is_one(int frame_bytes) { return frame_bytes <= 16384; }
-
 static int ensure_smem(const void *fn, size_t smem, int device) {
     constexpr int kKernels = 8;
     static const void *known[kKernels] = {};
@@ -783,7 +774,7 @@ int run_sample_gather(apexb200_replay *h, const double *u, uint64_t seed, int32_
                            dim3((unsigned)((units + wpc - 1) / wpc)), dim3(wpc * 32), smem, st, h->tree, rv, sa, ga,
                            h->status, ready, ready_value);
     }
-    if (g_gather_variant == 3 && nch_is_one(rv.F)) {
+    if (g_gather_variant == 3) {
         rc = ensure_smem((const void *)sample_gather_timed_kernel, smem, h->cfg.device);
         if (rc) return rc;
         return launch_step("sample_gather_timed_kernel", sample_gather_timed_kernel, dim3((unsigned)((units + wpc - 1) / wpc)),

@@ -196,9 +196,10 @@ int apexb200_gather(apexb200_replay_t h, const int32_t *idx, const int32_t *fsel
                     float *Gamma, float *q_t, float *q_tpn, void *stream);
 /* 0 = per-warp 16-byte vector copy, 1 (default) = TMA bulk copy staged through shared memory.
  * Measurement aid for the fused kernel only: 3 = the default kernel with per-warp timestamps, read back
- * (synchronously) with apexb200_debug_timeline: out_host [units][12] u64 = global timer at entry, SM-clock
+ * (synchronously) with apexb200_debug_timeline: out_host [units][20] u64 = global timer at entry, SM-clock
  * offsets of {dependency wait done, search done, loads issued, first / last frame landed, stores issued,
- * staging free, writes complete}, global timer at exit, SM id, CTA id (units = half draws, <= 2048). */
+ * staging free, writes complete}, global timer at exit, SM id, CTA id, then SM-clock offsets of {draw formed,
+ * top level(s) searched, each further tree level searched (up to 5, 0 = unused)} (units = half draws, <= 2048). */
 int apexb200_set_gather_variant(int32_t variant);
 int apexb200_debug_timeline(uint64_t *out_host, int32_t units);
 /* out_host [8] u64: global-timer stamps of the last single-CTA TD/update launch — [0] entry, [1] dependency wait

@@ -57,9 +57,9 @@ def main():
             g.replay()
         torch.cuda.synchronize()
         units = 2 * B
-        buf = (C.c_uint64 * (units * 12))()
+        buf = (C.c_uint64 * (units * 20))()
         apex_b200._C.call("apexb200_debug_timeline", buf, units)
-        d = np.frombuffer(buf, dtype=np.uint64).reshape(units, 12).astype(np.int64)
+        d = np.frombuffer(buf, dtype=np.uint64).reshape(units, 20).astype(np.int64)
         td = (C.c_uint64 * 8)()
         apex_b200._C.call("apexb200_debug_td_timeline", td)
         td = [int(x) for x in td]
@@ -70,6 +70,13 @@ def main():
             v = d[:, 1 + j] / a.mhz
             print("  %-28s min %6.2f  p10 %6.2f  median %6.2f  p90 %6.2f  max %6.2f us" %
                   (nme, v.min(), np.percentile(v, 10), np.median(v), np.percentile(v, 90), v.max()))
+        lv = ["draw formed", "top level(s) searched"] + ["level %d searched" % k for k in range(1, 6)]
+        for j, nme in enumerate(lv):
+            v = d[:, 12 + j] / a.mhz
+            if v.max() > 0:
+                print("    . %-26s min %6.2f  p10 %6.2f  median %6.2f  p90 %6.2f  max %6.2f us" %
+                      (nme, v.min(), np.percentile(v, 10), np.median(v), np.percentile(v, 90), v.max()))
+        print("    . frame slots guessed wrong: %d of %d" % (int((d[:, 11] >> 32).sum()), units * 4))
         g0, g9 = d[:, 0], d[:, 9]
         print("  global timer: entry spread %.2f us, first entry -> last exit %.2f us" %
               ((g0.max() - g0.min()) / 1e3, (g9.max() - g0.min()) / 1e3))
