@@ -96,6 +96,7 @@ SIGNATURES = {
     "apexb200_shard_exchange": [_P, _P, _P],
     "apexb200_shard_push": [_P, _P],
     "apexb200_peer_push_on_update": [_P, _I32],
+    "apexb200_peer_wait_stats": [_P, _P, _I32, _P],
     "apexb200_sample_gather_sharded": [_P, C.c_uint64, _I32, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P],
     "apexb200_params_create": [_I32, _P, _I32, C.c_uint64, C.POINTER(_P)],
     "apexb200_params_destroy": [_P],

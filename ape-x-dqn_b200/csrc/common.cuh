@@ -125,7 +125,9 @@ __device__ __forceinline__ float prio_pow(float abs_td, float alpha, float eps) 
 }
 
 // Device control block of a handle: int32 words [0] status, [4..5] u64 update epoch,
-// [6..7] u64 exchange round, [16..47] u64 totals[kMaxShards] of the last exchange.
+// [6..7] u64 exchange round, [16..47] u64 totals[kMaxShards] of the last exchange, [48..51] arrival words of the
+// host-facing step, [52..53] u64 SM clocks the sharded sampling kernel spent waiting for its peers' totals (CTA 0,
+// slowest peer, summed over launches), [54..55] u64 number of such launches (apexb200_peer_wait_stats).
 __device__ __forceinline__ unsigned long long read_round(const int32_t *ctrl) {
     return *(const volatile unsigned long long *)(ctrl + 6);
 }
@@ -182,8 +184,9 @@ __device__ __forceinline__ void warp_propagate_adjacent(const TreeView &tv, long
 // peer's round-r word (peer_wait_round), which proves the peers are done with round r-1,
 // whose slot the push overwrites; hence a slot sees tags r, r+2, r+4, ... and the 4-bit
 // tag cannot alias.  Both helpers are called by the lanes g < world of one warp.
+// `waited` (nullable): SM clocks from the first look at the word until it carried the round's tag.
 __device__ __forceinline__ unsigned long long peer_wait_round(const PeerView &pv, unsigned long long round, int g,
-                                                              int32_t *ctrl) {
+                                                              int32_t *ctrl, long long *waited = nullptr) {
     volatile unsigned long long *in = pv.xbuf[pv.rank] + (size_t)((int)(round & 1ull) * kMaxShards + g);
     const unsigned long long tag = round & 15ull;
     const long long t0 = clock64();
@@ -192,6 +195,7 @@ __device__ __forceinline__ unsigned long long peer_wait_round(const PeerView &pv
         if (clock64() - t0 > (5ll << 31)) { atomicOr(ctrl, APEXB200_ST_PEER_TIMEOUT); return 0ull; }   // ~5 s: peer gone
         w = *in;
     }
+    if (waited) *waited = clock64() - t0;
     return w >> 4;
 }
 __device__ __forceinline__ void peer_push_round(const PeerView &pv, unsigned long long round, int g,

@@ -538,7 +538,18 @@ __device__ __forceinline__ void sample_gather_sharded_body(const TreeView &tv, c
     // CTA polls the exchange buffer; the others take the words from shared memory.
     __shared__ unsigned long long s_totals[kMaxShards];
     const unsigned long long round = read_round(ctrl);
-    if (wl == 0 && lane < world) s_totals[lane] = peer_wait_round(pv, round, lane, ctrl);
+    if (wl == 0) {
+        long long waited = 0;
+        if (lane < world) s_totals[lane] = peer_wait_round(pv, round, lane, ctrl, &waited);
+        if (blockIdx.x == 0) {                               // attribution of the multi-GPU step: how long the peers' words took
+            #pragma unroll
+            for (int o = 16; o > 0; o >>= 1) waited = max(waited, __shfl_xor_sync(0xffffffffu, waited, o));
+            if (lane == 0) {
+                atomicAdd((unsigned long long *)(ctrl + 52), (unsigned long long)waited);
+                atomicAdd((unsigned long long *)(ctrl + 54), 1ull);
+            }
+        }
+    }
     if (kPolled && wl == 0 && lane == 0) {
         // apexb200_host_step_sharded: the Q rows of the following TD kernel arrive by an H2D copy on another
         // stream, followed by a stream-ordered write of `ready_value`; waiting for it here (the copy was issued

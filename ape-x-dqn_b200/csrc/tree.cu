@@ -393,6 +393,15 @@ int apexb200_shard_push(apexb200_replay_t h, void *stream) {
     return run_peer_push(h, (cudaStream_t)stream);
 }
 
+int apexb200_peer_wait_stats(apexb200_replay_t h, uint64_t *stats_host, int32_t reset, void *stream) {
+    APEX_REQUIRE(h && stats_host, APEXB200_EINVAL, "peer_wait_stats: null argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    APEX_CUDA(cudaMemcpyAsync(stats_host, h->status + 52, 16, cudaMemcpyDeviceToHost, st));
+    if (reset) APEX_CUDA(cudaMemsetAsync(h->status + 52, 0, 16, st));
+    APEX_CUDA(cudaStreamSynchronize(st));
+    return APEXB200_OK;
+}
+
 int apexb200_peer_push_on_update(apexb200_replay_t h, int32_t enabled) {
     APEX_REQUIRE(h, APEXB200_EINVAL, "peer_push_on_update: null handle");
     h->push_on_update = enabled ? 1 : 0;

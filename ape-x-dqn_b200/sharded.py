@@ -94,6 +94,16 @@ class ShardedSampler:
         from . import _C
         _C.call("apexb200_shard_push", self.mem._h, _C.stream_ptr())
 
+    def peer_wait_stats(self, reset=True):
+        """(mean microseconds at 1965 MHz, launches): how long the fused sharded kernels waited in-kernel for the
+        slowest peer's total since the last reset (synchronises)."""
+        import ctypes as C
+        from . import _C
+        st = (C.c_uint64 * 2)()
+        _C.call("apexb200_peer_wait_stats", self.mem._h, st, 1 if reset else 0, _C.stream_ptr())
+        n = int(st[1])
+        return (int(st[0]) / n / 1965.0 if n else 0.0), n
+
     def exchange(self, totals_out=None):
         """One-launch all-gather of the shard totals over peer memory (collective: every rank
         calls it once per step, before sample_fused)."""

@@ -154,6 +154,20 @@ def fill_shard(torch, apex, mem, args, dev, seed):
     torch.cuda.synchronize()
 
 
+def r_literal_quote():
+    """R-literal: the unmodified reference replay.py cannot run at 2M records (O(N^2) per update) and
+    its source is not on the GPU box; the committed build-container measurement + N^2 fit is quoted, labelled as such."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02_r_literal_fit.json")) as f:
+            d = json.load(f)
+        return {"source": "profiles/r02_r_literal_fit.json (tools/r_literal_fit.py, build container, 1 Python thread)",
+                "measured_transitions_per_s": {str(r["N"]): r["transitions_per_s"] for r in d["measured"]},
+                "extrapolated_transitions_per_s_at_2M_B512": d["extrapolated"]["2097152"]["transitions_per_s_B512"],
+                "label": "not timed in this run; the 2M figure is EXTRAPOLATED from the measured N^2 law"}
+    except Exception:
+        return None
+
+
 def config_dict(args, world):
     """The workload description both arms print (a function of the command line and the rank count only)."""
     N, B, C = args.capacity, args.batch, args.frames_per_state
@@ -299,7 +313,10 @@ def run_ours(args):
 
     pilot = max_over_ranks([timed_block()])[0]
     n_blocks = int(min(400, max(3, -(-args.min_ms // max(pilot, 1e-3)))))
+    if peer_path:
+        sampler.peer_wait_stats(reset=True)
     blocks = max_over_ranks([timed_block() for _ in range(n_blocks)])
+    peer_wait_us = max_over_ranks([sampler.peer_wait_stats(reset=True)[0]])[0] if peer_path else None
     ms, ms_min, ms_max = block_stats(blocks)
     launches_per_step = (2 if fused else 3) if world == 1 else (2 if peer_path else 5 + (1 if Bg > 1024 else 0))
     value = K * Bg / (ms * 1e-3)
@@ -357,7 +374,10 @@ def run_ours(args):
                               "replays of a CUDA graph of 16 back-to-back launches; traffic: ncu is single-GPU only, see the "
                               "N=1 line for the DRAM byte count of the same gather",
                     "share_of_step": round(s_us / (ms / K * 1e3), 3)}
-        multi = {"shard_exchange_us": round(x_us, 3), "sample_gather_sharded_us": round(s_us, 3)}
+        multi = {"shard_exchange_us": round(x_us, 3), "sample_gather_sharded_us": round(s_us, 3),
+                 "peer_wait_us": round(peer_wait_us, 3),
+                 "peer_wait_note": "mean time per step, inside the timed region, that the sharded sampling kernel spent polling for "
+                                   "the slowest peer's total (pushed over NVLink by that peer's TD/update kernel); max over ranks"}
     if world == 1:
         o = mem._outputs(B, False)
 
@@ -538,7 +558,7 @@ def run_ours(args):
                                                       "value_ratio": ref(value, cpu_c["value"]),
                                                       "note": "ours / the hand-written C+OpenMP port on this box's cores "
                                                               "(a stricter baseline than the reference's numpy/torch path)"},
-            "learner_loop": learner_loop,
+            "learner_loop": learner_loop, "cpu_baseline_r_literal": r_literal_quote(),
         }
         print(json.dumps(line))
     if world > 1:
@@ -801,7 +821,7 @@ def run_reference(args):
                    "block_ms_max": round(ms_max, 3), "how": "wall clock around blocks of K steps, median block"},
         "cpu_baseline": {"value": value, "unit": "transitions/s", "cores": ref.threads, "kind": "port", "sample": sample,
                          "host_records": n_cpu, "draws_per_step": Bg},
-        "cpu_baseline_c_openmp": extra,
+        "cpu_baseline_c_openmp": extra, "cpu_baseline_r_literal": r_literal_quote(),
         "e2e": {"value": value, "unit": "transitions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))

@@ -413,6 +413,10 @@ int apexb200_shard_exchange(apexb200_replay_t h, uint64_t *totals_out, void *str
 /* The publishing half of shard_exchange alone: start a new exchange round and write this shard's total
  * into every peer's buffer without waiting for theirs (what td_fwd_update does with push-on-update). */
 int apexb200_shard_push(apexb200_replay_t h, void *stream);
+/* Attribution of the multi-GPU step: stats_host [2] u64 = {SM clocks the sharded sampling kernels of this handle
+ * spent waiting for their peers' totals (slowest peer per launch, summed), number of launches}; reset != 0 clears
+ * the counters.  Synchronises `stream`. */
+int apexb200_peer_wait_stats(apexb200_replay_t h, uint64_t *stats_host, int32_t reset, void *stream);
 /* Fused compute + collective: with this enabled every apexb200_td_fwd_update on the handle
  * also publishes the shard's new total to all peers from the kernel that produced it (as a
  * new exchange round), so the steady-state step is sample_gather_sharded -> model ->

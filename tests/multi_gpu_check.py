@@ -86,7 +86,7 @@ def sharded_learner_check(rank, world, dev):
     for step in range(2):
         q_before, qd_before = copy.deepcopy(L.Q), copy.deepcopy(L.Q_double)
         loss = L.step_sharded()
-        o = mem._outputs(rows, False)
+        o = mem._outputs(rows, False, L._f32())                      # the learner's batch (float32 straight from the gather)
         cnt = o["count"].clone()
         parts = []
         for name in ("S_t", "S_tpn", "A", "R", "Gamma"):
