@@ -582,8 +582,8 @@ __device__ __forceinline__ void sample_gather_sharded_body(const TreeView &tv, c
     unsigned long long *my_bars = bars + (wl * 8 + lane) * kMaxChunks;
     if (lane < C) tma_init_bars(my_bars, nch);
     const int wave_units = gridDim.x * wpc;
-    unsigned wave = 0u;
-    for (int unit = unit0;; unit += wave_units, ++wave) {
+    unsigned phase = 0u;                                     // completed phases of this lane's mbarriers
+    for (int unit = unit0;; unit += wave_units) {
         const int row = unit >> 1, half = unit & 1;
         const int j = j_lo + row;
         double uw = 0.0;
@@ -595,14 +595,14 @@ __device__ __forceinline__ void sample_gather_sharded_body(const TreeView &tv, c
         unsigned long long leaf, total;
         const long long node = warp_descend(tv, vtop, t - lo, false, 0.0, &leaf, &total, ctrl);
         const int k = half * C + lane;
-        long long f = -1;
-        if (node >= 0 && lane < C) f = rv.fidx[node * twoC + k];
-        bool moving = false;
-        if (node >= 0 && lane < C) {
-            if (f < 0 || f >= rv.N * rv.fpr) atomicOr(ctrl, APEXB200_ST_BAD_INDEX);
-            else { moving = true; tma_issue_frame(rv.frames + f * rv.F, stage, my_bars, (unsigned)rv.F, nch); }
+        // frame copy on the guessed slot while the frame-slot row is in flight; the row decides (see sample_gather_body)
+        long long f = -1, fg = -1;
+        const bool mine = node >= 0 && lane < C;
+        if (mine) {
+            f = rv.fidx[node * twoC + k];
+            fg = guess_frame_slot(rv, node, k);
+            tma_issue_frame(rv.frames + fg * rv.F, stage, my_bars, (unsigned)rv.F, nch);
         }
-        if (lane < C && sa.fsel_out) sa.fsel_out[(long long)row * twoC + k] = (int32_t)f;
         if (half == 0) {
             if (lane == 0) {
                 sa.idx_out[row] = (int32_t)node;
@@ -618,12 +618,23 @@ __device__ __forceinline__ void sample_gather_sharded_body(const TreeView &tv, c
             if (cnt > sh.max_rows) { cnt = sh.max_rows; if (lane == 0) atomicOr(ctrl, APEXB200_ST_QUOTA); }
             if (lane == 0) *sh.count_out = cnt;
         }
+        if (lane < C && sa.fsel_out) sa.fsel_out[(long long)row * twoC + k] = (int32_t)f;
+        bool moving = mine;
+        if (mine && f != fg) {                               // wrong guess: let the stray copy land, fetch the right frame
+            const bool valid = f >= 0 && f < rv.N * rv.fpr;
+            if (!valid) atomicOr(ctrl, APEXB200_ST_BAD_INDEX);
+            tma_wait_frame(my_bars, nch, phase & 1u);
+            ++phase;                                         // the stray copy's phase is complete
+            moving = valid;
+            if (valid) tma_issue_frame(rv.frames + f * rv.F, stage, my_bars, (unsigned)rv.F, nch);
+        }
         if (kF32)
             f32_drain_frames(moving, moving ? item_dst(rv, ga, row, k) : nullptr, stage - (size_t)lane * rv.F,
-                             my_bars - lane * kMaxChunks, C, (unsigned)rv.F, nch, wave & 1u);
+                             my_bars - lane * kMaxChunks, C, (unsigned)rv.F, nch, phase & 1u);
         else
             tma_drain_frames(moving, moving ? item_dst(rv, ga, row, k) : nullptr, stage, my_bars, (unsigned)rv.F, nch,
-                             wave & 1u);
+                             phase & 1u);
+        if (moving) ++phase;                                 // the drained copy completed one more phase of this lane's mbarriers
     }
 }
 

@@ -69,6 +69,18 @@ def main():
         b = mem.sample_tensors(B)
         mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma, out=out)
     res["full step (fused + td)"] = timed_graph(step)
+    # the sharded form of the two kernels with a group of one (self exchange): what the multi-GPU step runs per rank
+    sampler = apex_b200.ShardedSampler(mem, rank=0, world_size=1)
+    sampler.connect_peers()
+    sampler.exchange()
+    res["sample_gather_sharded (world 1)"] = timed_graph(lambda: sampler.sample_fused(B))
+    sampler.push_on_update(True)
+
+    def sharded_step():
+        b, _pos, cnt = sampler.sample_fused(B)
+        mem.td_update(b.idx, q[0], q[1], q[2], b.A, b.R, b.Gamma, out=out, count_dev=cnt, mean_divisor=float(B))
+    res["full sharded step (world 1)"] = timed_graph(sharded_step)
+    sampler.push_on_update(False)
     for k, v in res.items():
         print("%-32s %8.2f us" % (k, v))
     mem.check_status()
