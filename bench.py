@@ -41,9 +41,9 @@ if ROOT not in sys.path:
 F_BYTES = 7056          # 84 x 84 uint8
 ALPHA = 0.6
 GAMMA_N = 0.99 ** 3
-NCU_DRAM_BYTES_PER_LAUNCH = 26_050_000      # sample_gather_kernel, B=512, C=4 (profiles/r01_ncu_full_sample_gather_final.csv)
-NCU_TRAFFIC_SOURCE = ("profiles/r01_ncu_full_sample_gather_final.csv (ncu --set full, B=512, C=4: "
-                      "dram__bytes_read.sum 25.8 MB + dram__bytes_write.sum 0.27 MB per launch)")
+NCU_DRAM_BYTES_PER_LAUNCH = 26_140_000      # sample_gather_kernel, B=512, C=4 (profiles/r02_ncu_full_sample_gather.csv)
+NCU_TRAFFIC_SOURCE = ("profiles/r02_ncu_full_sample_gather.csv (ncu --set full, B=512, C=4, three launches: "
+                      "dram__bytes_read.sum 25.92 MB + dram__bytes_write.sum 0.20-0.26 MB per launch)")
 METRIC = "prioritized sample+update transitions/s (2M cap, B=512)"
 DTYPE = "u8 frames / u64 fixed-point tree / f32 TD"
 
