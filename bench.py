@@ -74,6 +74,8 @@ def parse():
     ap.add_argument("--no-push", action="store_true",
                     help="multi-GPU: exchange the totals with one shard_exchange launch per step instead of "
                          "publishing them from the TD/update kernel")
+    ap.add_argument("--ring-fed", action="store_true",
+                    help="--workload learner (sharded): the actors' steps arrive through shared-memory staging rings")
     ap.add_argument("--sharded-loop", action="store_true",
                     help="--workload learner at N=1: run the eager sharded-learner loop (the N>1 code path) on one GPU")
     ap.add_argument("--workload", default="replay", choices=["replay", "learner"],
@@ -924,7 +926,18 @@ def run_learner_sharded(args, world):
     L.setup()
     # 256 actors over the box = 256 / world per GPU, one ring lane each, T env steps per learner step
     E, T, every = min(max(256 // world, 1), args.lanes), 8, 4        # chunks of 8 env steps every 4th learner step
-    ingest = apex_b200.VectorActorIngest(mem, E, n_step=3, gamma=0.99, lanes=list(range(E)))
+    rings, ring_ingest = [], None
+    if args.ring_fed:
+        # the actors' transport of SURVEY 8(f).1: one shared-memory staging ring per actor (written here by this process
+        # the way an actor process writes it: plain memcpys, no CUDA), drained by RingIngest.poll
+        names = ["apexring_bench_%d_%d_%d" % (os.getpid(), rank, e) for e in range(E)]
+        rings = [apex_b200.ActorStagingRing(nm, 4, T, F_BYTES, nA, create=True) for nm in names]
+        ring_ingest = apex_b200.RingIngest(mem, rings, n_step=3, gamma=0.99)
+        rrng = np.random.default_rng(5 + rank)
+        payload = (rrng.integers(0, 256, (T, F_BYTES), dtype=np.uint8), rrng.integers(0, nA, T).astype(np.int32),
+                   np.clip(rrng.standard_normal(T), -1, 1).astype(np.float32), np.zeros(T, bool),
+                   rrng.standard_normal((T, nA)).astype(np.float32))
+    ingest = None if args.ring_fed else apex_b200.VectorActorIngest(mem, E, n_step=3, gamma=0.99, lanes=list(range(E)))
     gen = torch.Generator(device=dev).manual_seed(77 + rank)
     pool = [(torch.randint(0, 256, (E, T, F_BYTES), dtype=torch.uint8, device=dev, generator=gen),
              torch.randint(0, nA, (E, T), dtype=torch.int32, device=dev, generator=gen),
@@ -933,7 +946,12 @@ def run_learner_sharded(args, world):
 
     def step(k):
         if k % every == 0:
-            ingest.push(*pool[(k // every) % 4])                  # K7 + initial priority + K6 into E lanes
+            if ring_ingest is not None:
+                for r_ in rings:                                  # every actor has one more chunk of T steps ready
+                    r_.push(*payload)
+                ring_ingest.poll()                                # one pack kernel + the three ingest launches for all rings
+            else:
+                ingest.push(*pool[(k // every) % 4])              # n-step + initial priority + insert into E lanes (device inputs)
             L.after_insert()                                      # totals changed at different rates: one exchange launch
         return L.step_sharded()
 
@@ -954,6 +972,11 @@ def run_learner_sharded(args, world):
     both = [torch.zeros_like(csum) for _ in range(world)]
     if world > 1:
         dist.all_gather(both, csum)
+    if ring_ingest is not None:
+        ring_ingest.flush()
+        torch.cuda.synchronize()
+        for r_ in rings:
+            r_.close(unlink=True)
     if rank == 0:
         ms = float(ms)
         print(json.dumps({"metric": "Ape-X sharded learner loop transitions/s (2M cap per GPU, B=512 per GPU, duelling net fp32)",
@@ -961,6 +984,8 @@ def run_learner_sharded(args, world):
                           "ms_per_step": round(ms / K, 4), "final_global_loss": float(total), "scaling": "weak",
                           "replicas_equal": len({float(x) for x in both}) == 1,
                           "inserted_per_step_per_gpu": E * T / every, "higher_is_better": True, "data": "synthetic",
+                          "actor_transport": ("%d shared-memory staging rings per GPU -> RingIngest.poll (apexb200_ingest_push_blobs)" % E)
+                          if args.ring_fed else "device tensors -> VectorActorIngest.push (apexb200_ingest_push)",
                           "config": {"workload": "sharded learner loop: %d actors x %d env steps inserted per GPU every 4th step (K7+K6) -> "
                                                  "shard exchange -> fused sharded sample+gather (peer memory) -> 3 forwards + backward "
                                                  "(cuDNN fp32) -> flat gradient all-reduce (NCCL) -> RMSprop -> fused TD/priority "
