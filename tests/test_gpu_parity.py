@@ -901,6 +901,60 @@ def test_host_step_pipeline(apex, use_graph, depth):
     mem.check_status()
 
 
+@pytest.mark.parametrize("depth,max_rows", [(1, None), (3, None), (3, 160)])
+def test_sharded_host_step_pipeline_world1(apex, depth, max_rows):
+    """apexb200_host_step_sharded / ShardedHostStepPipeline with a group of one: host Q rows in; loss part, priorities,
+    record indices, global draw positions and the row count out — equal, step after step, to the oracle's
+    sample -> TD -> write-back on the draws the kernel generates (restated by kernel_stratified_uniforms).
+    max_rows larger than the batch: rows beyond the count are ignored."""
+    rng = np.random.default_rng(43)
+    N, C_, F, B, nA = 1 << 13, 2, 256, 96, 4
+    mem = make_mem(apex, N, C=C_, F=F, layout="stream", lanes=2, n=3)
+    mem.seed = 4242
+    ring = ro.RingOracle(N, C_, F, lanes=2, fpr=1, lookback=C_ - 1 + 3, alpha=0.6)
+    for lane in range(2):
+        m = N // 2 - 8
+        args = (lane, rng.integers(0, 256, (m, F), dtype=np.uint8), apex.stream_offsets(C_, np.full(m, 3), np.arange(m) % 97),
+                rng.integers(0, nA, m).astype(np.int32), rng.standard_normal(m).astype(np.float32), np.full(m, 0.97, np.float32))
+        prio = (np.abs(rng.standard_normal(m)) + 1e-3).astype(np.float32)
+        mem.insert(*args, prio=prio)
+        ring.insert(*args, prio=prio)
+    ring.leaves[:] = u64(mem.buffer(apex._C.BUF_LEAVES))
+    sampler = apex.ShardedSampler(mem, rank=0, world_size=1)
+    sampler.connect_peers()
+    sampler.push_on_update(True)
+    sampler.exchange()                                                   # round 1
+    pipe = apex.ShardedHostStepPipeline(sampler, B, nA, max_rows=max_rows, depth=depth)
+    M = pipe.M
+    tickets, inputs, steps, checked = [], [], 9, 0
+
+    def check(k):
+        loss_part, prio, idx, pos, n = pipe.result(tickets[k])
+        q0 = inputs[k]
+        assert n == B and (pos == np.arange(B)).all()
+        u = ro.kernel_stratified_uniforms(4242, 1 + k, k, B)             # exchange round advances with every update
+        want = ring.sample(u)
+        np.testing.assert_array_equal(idx, want)
+        g = ring.gather(want)
+        o = to.td_forward(q0[0][:B], q0[1][:B], q0[2][:B], g["A"], g["R"], g["G"], alpha=0.6)
+        np.testing.assert_allclose(prio, o["prio"], rtol=RTOL, atol=1e-7)
+        assert loss_part == pytest.approx(o["loss_mean"], rel=RTOL)
+        ring.set_leaves(want, ro.priority_to_leaf(prio.copy()))
+
+    for k in range(steps):
+        q = rng.standard_normal((3, M, nA)).astype(np.float32)
+        tickets.append(pipe.submit(q))
+        inputs.append(q)
+        if k >= depth - 1:
+            check(checked)
+            checked += 1
+    while checked < steps:
+        check(checked)
+        checked += 1
+    assert mem.total() == ring.total()
+    mem.check_status()
+
+
 def test_vector_actor_ingest_matches_sliding_buffer(apex):
     """K7 + K6 ingest of E lock-stepped environments == the host ExperienceBuffer(semantics="sliding")
     fed the same steps, record by record (a10/a11/a3 on the device, frames stored once)."""
