@@ -135,7 +135,7 @@ __device__ __forceinline__ const unsigned long long *exchanged_totals(const int3
     return (const unsigned long long *)(ctrl + 16);
 }
 __device__ __forceinline__ unsigned long long read_epoch(const int32_t *ctrl) {
-    return *(const volatile unsigned long long *)(ctrl + 4);
+    return __ldcg((const unsigned long long *)(ctrl + 4));     // L2 (never a stale L1 line); written by earlier kernels only
 }
 __device__ __forceinline__ void bump_epoch(int32_t *ctrl) {        // one thread of a tree-changing kernel
     // a reduction without return value: the issuing warp does not wait for the round trip a volatile read-modify-

@@ -537,10 +537,21 @@ __device__ __forceinline__ void sample_gather_sharded_body(const TreeView &tv, c
     // td_small_kernel) -> global total T and this rank's prefix interval [lo, hi).  One warp per
     // CTA polls the exchange buffer; the others take the words from shared memory.
     __shared__ unsigned long long s_totals[kMaxShards];
-    const unsigned long long round = read_round(ctrl);
+    // Both exchange slots are fetched together with the round word (which slot is current depends on the round):
+    // one round trip instead of two dependent ones; only a word that has not arrived yet is polled for.
+    unsigned long long w0 = 0ull, w1 = 0ull;
+    if (wl == 0 && lane < world) {
+        const unsigned long long *xb = pv.xbuf[rank];
+        w0 = __ldcg(xb + lane);
+        w1 = __ldcg(xb + kMaxShards + lane);
+    }
+    const unsigned long long round = __ldcg((const unsigned long long *)(ctrl + 6));
     if (wl == 0) {
         long long waited = 0;
-        if (lane < world) s_totals[lane] = peer_wait_round(pv, round, lane, ctrl, &waited);
+        if (lane < world) {
+            const unsigned long long w = (round & 1ull) ? w1 : w0;
+            s_totals[lane] = (w & 15ull) == (round & 15ull) ? (w >> 4) : peer_wait_round(pv, round, lane, ctrl, &waited);
+        }
         if (blockIdx.x == 0) {                               // attribution of the multi-GPU step: how long the peers' words took
             #pragma unroll
             for (int o = 16; o > 0; o >>= 1) waited = max(waited, __shfl_xor_sync(0xffffffffu, waited, o));
