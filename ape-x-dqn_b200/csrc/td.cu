@@ -209,6 +209,10 @@ td_small_kernel(TdArgs a, TreeView tv, const int32_t *__restrict__ idx, uint32_t
             }
             if (vec4) pr = td_row_finish4(a, b, row, &l);
             else td_one(a, b, &l, &pr);
+            if (status != nullptr) {                              // an action outside [0, nA) was clamped: say so
+                const int act = vec4 ? row.act : a.A[b];
+                if (act < 0 || act >= a.nA) atomicOr(status, APEXB200_ST_BAD_ACTION);
+            }
         }
         l_acc += l;
         TD_STAMP(3);

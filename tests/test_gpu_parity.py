@@ -606,6 +606,27 @@ def test_td_update_writes_priorities_in_place(apex, B, cluster):
         apex._C.call("apexb200_set_td_cluster", 0)
 
 
+def test_out_of_range_action_is_clamped_consistently_and_reported(apex):
+    """An action outside [0, num_actions) is clamped the same way by the forward and the backward kernel (loss and
+    gradient refer to the same column) and the handle-bound call raises the status bit."""
+    rng = np.random.default_rng(12)
+    B, nA, N = 64, 4, 1024
+    mem = make_mem(apex, N)
+    load_leaves(apex, mem, rng.integers(1, 1 << 20, N, dtype=np.uint64))
+    q = [dev(rng.standard_normal((B, nA)).astype(np.float32)) for _ in range(3)]
+    A = rng.integers(0, nA, B).astype(np.int32)
+    A[5], A[9] = 7, -2                                                            # clamped to nA-1 and 0
+    R, G = dev(rng.standard_normal(B).astype(np.float32)), dev(np.full(B, 0.9, np.float32))
+    idx = dev(np.sort(rng.integers(0, N, B)).astype(np.int32))
+    delta, prio, loss, mean = mem.td_update(idx, q[0], q[1], q[2], dev(A), R, G)
+    o = to.td_forward(*(x.cpu().numpy() for x in q), np.clip(A, 0, nA - 1), R.cpu().numpy(), G.cpu().numpy(), alpha=0.6)
+    np.testing.assert_allclose(delta.cpu().numpy(), o["delta"], rtol=RTOL, atol=1e-6)
+    g = apex.ops.td_backward(delta, dev(A), torch.ones(1, device="cuda"), nA).cpu().numpy()
+    np.testing.assert_allclose(g, to.td_backward(o["delta"], np.clip(A, 0, nA - 1), nA), rtol=RTOL, atol=1e-7)
+    with pytest.raises(apex._C.ApexError, match="action"):
+        mem.check_status()
+
+
 def _td_update_case(apex, B, sorted_idx):
     rng = np.random.default_rng(B)
     N, nA = 1 << 16, 4
