@@ -236,7 +236,7 @@ using namespace apexb200;
 struct apexb200_ingest {
     apexb200_replay *h = nullptr;
     IngestState st{};
-    int E = 0, t_max = 0;
+    int E = 0, t_max = 0, device = 0;        // device ordinal kept here: destroy must not touch the replay handle
     void *block = nullptr;                    // one allocation for the whole state
     std::vector<int> lane_of_env;
     // staging of the shared-memory transport: [E, t_max, ...] per field
@@ -275,6 +275,7 @@ int apexb200_ingest_create(apexb200_replay_t h, int32_t num_envs, const int32_t 
     apexb200_ingest *g = new (std::nothrow) apexb200_ingest();
     APEX_REQUIRE(g, APEXB200_ENOMEM, "ingest_create: host allocation failed");
     g->h = h;
+    g->device = h->cfg.device;
     g->E = num_envs;
     g->t_max = max_chunk_steps;
     g->lane_of_env.assign(lanes_host, lanes_host + num_envs);
@@ -323,7 +324,7 @@ int apexb200_ingest_create(apexb200_replay_t h, int32_t num_envs, const int32_t 
 
 int apexb200_ingest_destroy(apexb200_ingest_t g) {
     if (!g) return APEXB200_OK;
-    if (g->h) cudaSetDevice(g->h->cfg.device);
+    cudaSetDevice(g->device);                 // (the replay handle may already be gone)
     void *ptrs[] = {g->block, g->sg_frames, g->sg_actions, g->sg_rewards, g->sg_dones, g->sg_q};
     for (void *p : ptrs) if (p) cudaFree(p);
     delete g;
