@@ -288,7 +288,12 @@ int apexb200_td_bwd(const float *delta, const int32_t *A, const float *grad_loss
  * Sharded batches: count_dev (nullable) is a device int32 with the
  * number of live rows <= B (the rank's data-dependent quota; rows beyond it are
  * ignored) and mean_divisor (0 = B) is the GLOBAL batch size, so that summing
- * loss_mean / gradients over ranks gives the single-batch mean. */
+ * loss_mean / gradients over ranks gives the single-batch mean.  With count_dev and
+ * mean_divisor the arrays may hold the whole global batch (B up to the global count):
+ * the single-CTA kernel is sized for the rank's fair share (mean_divisor / world) and
+ * takes further passes when the rank owns more, in batch order ("last row wins" holds
+ * across passes).  An action outside [0, num_actions) is evaluated for the clamped column
+ * (forward and backward alike) and raises APEXB200_ST_BAD_ACTION. */
 int apexb200_td_fwd_update(apexb200_replay_t h, const int32_t *idx,
                            const float *q_on_t, const float *q_on_tpn, const float *q_tg_tpn,
                            const int32_t *A, const float *R, const float *Gamma, int32_t B,
