@@ -107,6 +107,9 @@ SIGNATURES = {
     "apexb200_host_register": [_P, C.c_uint64],
     "apexb200_host_unregister": [_P],
     "apexb200_replay_buffer": [_P, _I32, C.POINTER(_P), C.POINTER(_I64)],
+    "apexb200_frames_pack_sizes": [_P, _I64, _I32, _P, _P],
+    "apexb200_frames_pack": [_P, _I64, _I32, _P, _P, _P],
+    "apexb200_frames_unpack": [_P, _I64, _I32, _P, _P, _P],
     "apexb200_replay_get_heads": [_P, C.POINTER(_I64)],
     "apexb200_replay_set_heads": [_P, C.POINTER(_I64)],
 }

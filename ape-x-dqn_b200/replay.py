@@ -448,14 +448,52 @@ class ReplayMemory(object):
             return None
         return torch.as_tensor(_RawCuda(p.value, n.value, self.device.index), device=self.device).view(dt)
 
-    def state_dict(self):
-        """Checkpoint of the whole shard (device -> host copies of ring, metadata, leaves, heads)."""
+    def pack_frames(self, first_slot=0, count=None):
+        """Lossless packing of frame slots [first_slot, first_slot + count) on the device (XOR with the previous
+        frame, key frame every 64, only non-zero 16-byte blocks stored; apexb200_frames_pack*).  Returns
+        (sizes int32-viewed u32 [count], offsets int64 [count], packed uint8 [total]) as CUDA tensors."""
+        import torch
+        self._ensure()
+        if count is None:
+            count = self.capacity * self.fpr - int(first_slot)
+        count = int(count)
+        sizes = torch.empty(count, dtype=torch.int32, device=self.device)
+        _C.call("apexb200_frames_pack_sizes", self._h, int(first_slot), count, _C.ptr(sizes), self._stream())
+        ends = torch.cumsum(sizes.to(torch.int64), 0)
+        offsets = (ends - sizes).contiguous()
+        total = int(ends[-1].item()) if count else 0
+        packed = torch.empty(max(total, 16), dtype=torch.uint8, device=self.device)
+        _C.call("apexb200_frames_pack", self._h, int(first_slot), count, _C.ptr(offsets), _C.ptr(packed), self._stream())
+        return sizes, offsets, packed[:total]
+
+    def unpack_frames(self, offsets, packed, first_slot=0):
+        """Inverse of pack_frames: writes the frames back into the store (device tensors, or host tensors that are
+        copied first)."""
+        self._ensure()
+        offsets = offsets.to(self.device).contiguous()
+        packed = packed.to(self.device).contiguous()
+        _C.call("apexb200_frames_unpack", self._h, int(first_slot), int(offsets.numel()), _C.ptr(offsets), _C.ptr(packed),
+                self._stream())
+
+    def state_dict(self, pack_frames=False):
+        """Checkpoint of the whole shard (device -> host copies of ring, metadata, leaves, heads).
+        pack_frames=True: the frame store travels losslessly packed (see pack_frames; frames of consecutive env
+        steps differ in a few sprites, so Atari-like streams shrink by an order of magnitude)."""
         heads = (C.c_int64 * self.lanes)()
         _C.call("apexb200_replay_get_heads", self._h, heads)
         out = {"heads": list(heads), "config": dict(capacity=self.capacity, lanes=self.lanes, layout=self.layout,
                                                     state_shape=self.state_shape, alpha=self.alpha)}
         for name, which in (("frames", _C.BUF_FRAMES), ("fidx", _C.BUF_FIDX), ("A", _C.BUF_ACTION), ("R", _C.BUF_REWARD),
                             ("Gamma", _C.BUF_GAMMA), ("q_t", _C.BUF_QT), ("q_tpn", _C.BUF_QTPN), ("leaves", _C.BUF_LEAVES)):
+            if name == "frames" and pack_frames:
+                chunks, step = [], 1 << 16                       # a chunk of frame slots at a time: bounded scratch
+                for lo in range(0, self.capacity * self.fpr, step):
+                    n = min(step, self.capacity * self.fpr - lo)
+                    _sizes, offsets, packed = self.pack_frames(lo, n)
+                    chunks.append((lo, offsets.cpu(), packed.cpu()))
+                out["frames"] = None
+                out["frames_packed"] = chunks
+                continue
             t = self.buffer(which)
             out[name] = None if t is None else t.cpu()
         return out
@@ -467,6 +505,8 @@ class ReplayMemory(object):
             t = self.buffer(which)
             if t is not None and sd.get(name) is not None:
                 t.copy_(sd[name])
+        for lo, offsets, packed in sd.get("frames_packed") or ():
+            self.unpack_frames(offsets, packed, lo)
         heads = (C.c_int64 * self.lanes)(*sd["heads"])
         _C.call("apexb200_replay_set_heads", self._h, heads)
         self.update_sample_probabilities()

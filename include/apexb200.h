@@ -518,6 +518,19 @@ int apexb200_host_unregister(void *address_host);
 #define APEXB200_BUF_QTPN   6
 #define APEXB200_BUF_LEAVES 7
 int apexb200_replay_buffer(apexb200_replay_t h, int32_t which, void **ptr_host, int64_t *bytes_host);
+/* ---- lossless packing of the frame store for checkpoints (README.md:24 of the reference lists
+ * "observation compression" as a TODO, the reference never persists its replay).  Not on the sampling path: the
+ * ring stays raw.  Frames [first_slot, first_slot + count) of the store, in slot order; every frame is XORed with
+ * its predecessor (every 64th frame of the range is a key frame, kept as is) and only the 16-byte blocks with a
+ * non-zero byte are stored behind a bitmap: 4*ceil(nb/32) bytes (rounded up to 16) + 16 bytes per stored block,
+ * nb = frame_bytes/16.  pack_sizes writes the encoded size of every frame (multiples of 16); the caller forms the
+ * exclusive prefix sum `offsets` [count] (u64) and allocates the output; pack encodes; unpack writes the frames
+ * back into the store (one CTA per 64-frame segment).  All device pointers, enqueue only. */
+int apexb200_frames_pack_sizes(apexb200_replay_t h, int64_t first_slot, int32_t count, uint32_t *sizes, void *stream);
+int apexb200_frames_pack(apexb200_replay_t h, int64_t first_slot, int32_t count, const uint64_t *offsets, uint8_t *out,
+                         void *stream);
+int apexb200_frames_unpack(apexb200_replay_t h, int64_t first_slot, int32_t count, const uint64_t *offsets,
+                           const uint8_t *packed, void *stream);
 /* Host-side ring heads: total records ever inserted per lane ([lanes] int64). */
 int apexb200_replay_get_heads(apexb200_replay_t h, int64_t *lane_count_host);
 int apexb200_replay_set_heads(apexb200_replay_t h, const int64_t *lane_count_host);

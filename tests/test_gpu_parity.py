@@ -511,6 +511,64 @@ def test_checkpoint_round_trip(apex):
     assert mem2.size() == mem.size() and mem2.total() == mem.total()
 
 
+def _sprite_frames(rng, count, F, change=40):
+    """Atari-like stream: every frame equals its predecessor except for a short run of bytes."""
+    fr = np.zeros((count, F), np.uint8)
+    fr[0] = rng.integers(0, 256, F)
+    for j in range(1, count):
+        fr[j] = fr[j - 1]
+        if j % 17:                                                       # some frames do not change at all
+            k = int(rng.integers(0, max(1, F - change)))
+            fr[j, k:k + change] = rng.integers(0, 256, min(change, F - k))
+    return fr
+
+
+@pytest.mark.parametrize("F,count,first", [(7056, 200, 0), (64, 65, 3), (16, 1, 0), (528, 130, 64), (7056, 64, 128)])
+def test_frame_packing_equals_oracle_and_round_trips(apex, F, count, first):
+    """apexb200_frames_pack_sizes / _pack / _unpack ((f).4, lossless checkpoint packing) against oracle/pack_oracle.py:
+    sizes and packed bytes identical, unpack restores the store byte for byte (also over random, incompressible
+    frames)."""
+    from oracle import pack_oracle as po
+    rng = np.random.default_rng(F + count)
+    N = 512
+    mem = make_mem(apex, N, C=1, F=F, layout="stream", lanes=1, n=1)
+    store = mem.buffer(apex._C.BUF_FRAMES).view(N, F)
+    for kind in ("sprites", "random"):
+        fr = _sprite_frames(rng, N, F) if kind == "sprites" else rng.integers(0, 256, (N, F), dtype=np.uint8)
+        store.copy_(dev(fr))
+        sizes, offsets, packed = mem.pack_frames(first, count)
+        w_sizes, w_off, w_packed = po.pack_frames(fr[first:first + count])
+        np.testing.assert_array_equal(sizes.cpu().numpy().view(np.uint32), w_sizes)
+        np.testing.assert_array_equal(offsets.cpu().numpy().astype(np.uint64), w_off)
+        np.testing.assert_array_equal(packed.cpu().numpy(), w_packed)
+        if kind == "sprites" and F >= 528 and count >= 64:
+            assert packed.numel() * 4 < count * F                        # a sprite stream shrinks well below a quarter
+        store[first:first + count].zero_()
+        mem.unpack_frames(offsets, packed, first)
+        assert torch.equal(store, dev(fr))
+    mem.check_status()
+
+
+def test_checkpoint_round_trip_with_packed_frames(apex):
+    rng = np.random.default_rng(13)
+    C_, F, lanes, cap = 2, 528, 2, 512
+    mem = make_mem(apex, cap, C=C_, F=F, layout="stream", lanes=lanes, n=2)
+    for lane in range(lanes):
+        m = 200
+        mem.insert(lane, _sprite_frames(rng, m, F), apex.stream_offsets(C_, np.full(m, 2), np.arange(m)),
+                   np.zeros(m, np.int32), np.ones(m, np.float32), np.ones(m, np.float32),
+                   prio=(np.abs(rng.standard_normal(m)) + 0.1).astype(np.float32))
+    sd = mem.state_dict(pack_frames=True)
+    assert sd["frames"] is None and sum(p.numel() for _, _, p in sd["frames_packed"]) * 3 < cap * F
+    mem2 = apex.ReplayMemory(cap, {"priority_exponent": 0.6, "layout": "stream", "lanes": lanes, "n_step": 2})
+    mem2.load_state_dict(sd)
+    assert torch.equal(mem.buffer(apex._C.BUF_FRAMES), mem2.buffer(apex._C.BUF_FRAMES))
+    u = dev(rng.random(64))
+    a, b = mem.sample_tensors(64, u=u), mem2.sample_tensors(64, u=u)
+    assert torch.equal(a.idx, b.idx) and torch.equal(a.S_t, b.S_t) and torch.equal(a.S_tpn, b.S_tpn)
+    assert mem2.size() == mem.size() and mem2.total() == mem.total()
+
+
 # ------------------------------------------------------------------ K5 TD / loss
 @pytest.mark.parametrize("B", [1, 32, 512, 1024, 1025, 4096, 10000])
 @pytest.mark.parametrize("kind", [to.LOSS_HALF_SQ, to.LOSS_HUBER])

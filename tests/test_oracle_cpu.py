@@ -245,3 +245,21 @@ def test_c_oracle_matches_numpy_oracle():
         np.testing.assert_allclose(o["loss_mean"], t["loss_mean"], rtol=1e-6)
         ring.set_leaves(want_idx, ro.priority_to_leaf(o["prio"]))
         np.testing.assert_array_equal(cpu.leaves, ring.leaves)
+
+
+def test_pack_oracle_round_trip_and_format():
+    """oracle/pack_oracle.py ((f).4 lossless frame packing): unpack(pack(x)) == x; a frame equal to its predecessor
+    costs only its bitmap; key frames every 64 frames are stored whole; random frames grow by the bitmap only."""
+    from oracle import pack_oracle as po
+    rng = np.random.default_rng(3)
+    for F, count in ((7056, 130), (16, 5), (528, 64)):
+        nb = F // 16
+        head = ((nb + 31) // 32 * 4 + 15) // 16 * 16
+        fr = rng.integers(0, 256, (count, F), dtype=np.uint8)
+        fr[3] = fr[2]                                                    # an unchanged frame
+        sizes, offsets, packed = po.pack_frames(fr)
+        assert (po.unpack_frames(sizes, offsets, packed, F) == fr).all()
+        assert sizes[0] == head + F and sizes[3] == head
+        if count > 64:
+            assert sizes[64] == head + F
+        assert (offsets % 16 == 0).all() and packed.size == int(sizes.sum())
