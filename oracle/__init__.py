@@ -23,6 +23,9 @@ Parity status ("pinned" vs "unpinned"), per function:
 * The batched actor policy (``policy_oracle``: duelling combine at batch 1, epsilon-greedy) is PINNED
   against the reference model run at batch 1 and ``Actor.epsilon_greedy_Q`` run on its own ``random``
   stream (``tests/golden/policy_reference.npz``).
+* The lossless checkpoint packing (``pack_oracle``) has no counterpart in the reference (README.md:24 lists
+  observation compression as a TODO): it restates this repository's own format, so there is nothing upstream to
+  pin it against; it is checked by round trips and the kernels are checked byte for byte against it.
 * The reference ships no tests, so there are no upstream golden vectors.
 """
 
