@@ -60,6 +60,24 @@ def test_argument_validation_without_a_gpu():
     assert lib.apexb200_actor_policy(None, None, None, None, None, 0, 0, 4, 4, None, None, None, None) == _C.EINVAL
     assert lib.apexb200_host_register(None, 0) == _C.EINVAL and lib.apexb200_host_unregister(None) == _C.EINVAL
     assert _C.HOST_STEP_SLOTS == 4
+    # round-2 entry points: sharded groups, host-facing sharded step, device-side ingest, checkpoint packing
+    g = ctypes.c_void_p()
+    assert lib.apexb200_ingest_create(None, 1, None, 3, 0.99, 4, 0, ctypes.byref(g)) == _C.EINVAL and not g.value
+    assert lib.apexb200_ingest_destroy(None) == 0
+    assert lib.apexb200_ingest_push(None, None, 1, 1, None, None, None, None, None, None) == _C.EINVAL
+    assert lib.apexb200_ingest_push_blobs(None, None, None, 1, 1, 0, 0, 0, 0, None) == _C.EINVAL
+    assert lib.apexb200_ingest_sync_heads(None, None) == _C.EINVAL
+    assert lib.apexb200_host_register_mapped(None, 0, ctypes.byref(g)) == _C.EINVAL
+    assert lib.apexb200_peer_connect_local(None, 0, 1, None) == _C.EINVAL
+    assert lib.apexb200_shard_push(None, None) == _C.EINVAL
+    assert lib.apexb200_peer_wait_stats(None, None, 0, None) == _C.EINVAL
+    assert lib.apexb200_host_step_sharded(None, 0, 0, 512, 512, None, 4, 0.0, 0, 1.0, None, None, None, None, None, None, None,
+                                          None) == _C.EINVAL
+    assert lib.apexb200_frames_pack_sizes(None, 0, 1, None, None) == _C.EINVAL
+    assert lib.apexb200_frames_pack(None, 0, 1, None, None, None) == _C.EINVAL
+    assert lib.apexb200_frames_unpack(None, 0, 1, None, None, None) == _C.EINVAL
+    assert lib.apexb200_debug_timeline(None, 4) == _C.EINVAL
+    assert (_C.FMT_U8, _C.FMT_F32) == (0, 1)
 
 
 def test_product_does_not_import_the_oracle():
