@@ -44,6 +44,10 @@ GAMMA_N = 0.99 ** 3
 NCU_DRAM_BYTES_PER_LAUNCH = 26_140_000      # sample_gather_kernel, B=512, C=4 (profiles/r02_ncu_full_sample_gather.csv)
 NCU_TRAFFIC_SOURCE = ("profiles/r02_ncu_full_sample_gather.csv (ncu --set full, B=512, C=4, three launches: "
                       "dram__bytes_read.sum 25.92 MB + dram__bytes_write.sum 0.20-0.26 MB per launch)")
+NCU_DRAM_BYTES_SHARDED = 26_230_000         # sample_gather_sharded_kernel, 512 rows, group of one (ncu is single-GPU only)
+NCU_TRAFFIC_SOURCE_SHARDED = ("profiles/r02_ncu_full_sample_gather_sharded_world1.csv (ncu --set full of the same kernel run as "
+                              "a group of one on one GPU, 512 rows, C=4: dram__bytes_read.sum 25.93 MB + dram__bytes_write.sum "
+                              "0.22-0.41 MB per launch; a rank of an N-GPU run does the same per-rank work)")
 METRIC = "prioritized sample+update transitions/s (2M cap, B=512)"
 DTYPE = "u8 frames / u64 fixed-point tree / f32 TD"
 
@@ -368,13 +372,15 @@ def run_ours(args):
         rows_all = max_over_ranks([rows_owned])[0]
         ach = bytes_per_rec * rows_owned / (s_us * 1e-6) / 1e9
         roofline = {"kernel": "sample_gather_sharded_kernel", "bound": "hbm", "achieved": round(ach, 1), "peak": peak,
-                    "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": None,
+                    "unit": "GB/s", "frac": round(ach / peak, 4),
+                    "traffic": NCU_DRAM_BYTES_SHARDED if (B == 512 and C == 4) else None,
+                    "traffic_source": NCU_TRAFFIC_SOURCE_SHARDED,
+                    "dram_frac": round(NCU_DRAM_BYTES_SHARDED / (s_us * 1e-6) / 1e9 / peak, 4) if (B == 512 and C == 4) else None,
                     "algorithmic_bytes_per_launch": int(bytes_per_rec * rows_owned), "rows_owned_mean_rank0": rows_owned,
                     "rows_owned_max_over_ranks": rows_all, "launch_us_mean": round(s_us, 3),
                     "launches_timed": 16 * 25, "peak_source": peak_src,
                     "timing": "rank 0's rows x SURVEY 8(d) bytes / launch duration (max over ranks) from CUDA events around 25 "
-                              "replays of a CUDA graph of 16 back-to-back launches; traffic: ncu is single-GPU only, see the "
-                              "N=1 line for the DRAM byte count of the same gather",
+                              "replays of a CUDA graph of 16 back-to-back launches",
                     "share_of_step": round(s_us / (ms / K * 1e3), 3)}
         multi = {"shard_exchange_us": round(x_us, 3), "sample_gather_sharded_us": round(s_us, 3),
                  "peer_wait_us": round(peer_wait_us, 3),
