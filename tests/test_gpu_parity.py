@@ -821,8 +821,26 @@ def test_sharded_group_on_one_gpu_returns_every_draw_whatever_the_skew(apex, ske
     bit-exact, batches byte-exact, no draw lost or duplicated), the loss parts must add up to the global mean,
     and every tree level must equal a rebuild after the updates."""
     rng = np.random.default_rng(int(skew) + 77)
-    G_, n, C_, F, lanes, nA = 4, 4096, 2, 256, 2, 4
-    Bg = 1024
+    _run_sharded_group(apex, rng, G_=4, n=4096, C_=2, F=256, lanes=2, Bg=1024, scales=[skew ** (1 / 0.6), 1.0, 1.0, 0.0],
+                       steps=3, expect_heavy_first=skew >= 8)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_sharded_group_random_configurations(apex, seed):
+    """The same checks over random group sizes, shard sizes, frame shapes, batch sizes and priority splits
+    (including shards without any mass)."""
+    rng = np.random.default_rng(1000 + seed)
+    G_ = int(rng.choice([2, 3, 5, 7]))
+    scales = [float(x) for x in rng.choice([0.0, 0.3, 1.0, 1.0, 4.0, 60.0], G_)]
+    if not any(scales):
+        scales[int(rng.integers(G_))] = 1.0
+    _run_sharded_group(apex, rng, G_=G_, n=int(rng.choice([512, 2048, 4096])), C_=int(rng.choice([1, 2, 3])),
+                       F=int(rng.choice([64, 208])), lanes=int(rng.choice([1, 2, 4])), Bg=int(rng.choice([64, 300, 1000])),
+                       scales=scales, steps=2, expect_heavy_first=False)
+
+
+def _run_sharded_group(apex, rng, G_, n, C_, F, lanes, Bg, scales, steps, expect_heavy_first):
+    nA = 4
     W = C_ - 1 + 3
     mems, rings, samplers = [], [], []
     for g in range(G_):
@@ -835,8 +853,7 @@ def test_sharded_group_on_one_gpu_returns_every_draw_whatever_the_skew(apex, ske
                     apex.stream_offsets(C_, np.full(m, 3), np.minimum(np.arange(m), 300)),
                     rng.integers(0, nA, m).astype(np.int32), rng.standard_normal(m).astype(np.float32),
                     np.where(rng.random(m) < 0.05, 0, 0.97).astype(np.float32))
-            scale = (skew ** (1 / 0.6) if g == 0 else 1.0) if g != 3 else 0.0
-            prio = ((np.abs(rng.standard_normal(m)) + 1e-2) * scale).astype(np.float32)
+            prio = ((np.abs(rng.standard_normal(m)) + 1e-2) * scales[g]).astype(np.float32)
             mem.insert(*args, prio=prio)
             ring.insert(*args, prio=prio)
         ring.leaves[:] = u64(mem.buffer(apex._C.BUF_LEAVES))
@@ -849,7 +866,7 @@ def test_sharded_group_on_one_gpu_returns_every_draw_whatever_the_skew(apex, ske
     for s_ in samplers:
         s_.push()                                                              # round 1, nobody waits
     rnd = 1
-    for step in range(3):
+    for step in range(steps):
         concat = np.concatenate([r.leaves for r in rings])
         seen = np.zeros(Bg, np.int64)
         u_glob = np.zeros(Bg)
@@ -869,8 +886,10 @@ def test_sharded_group_on_one_gpu_returns_every_draw_whatever_the_skew(apex, ske
         np.testing.assert_array_equal(u_glob, ro.kernel_stratified_uniforms(1234, rnd, step, Bg))
         whole = ro.tree_sample(concat, u_glob)
         np.testing.assert_array_equal(got_idx, whole)
-        assert outs[3][2] == 0                                                 # the empty shard owns nothing
-        if skew >= 8:
+        for g in range(G_):
+            if scales[g] == 0.0:
+                assert outs[g][2] == 0                                         # a shard without mass owns nothing
+        if expect_heavy_first:
             assert outs[0][2] > Bg // 2                                        # far beyond one wave of the fair share
         qrng = np.random.default_rng(100 + step)
         qg = [qrng.standard_normal((Bg, nA)).astype(np.float32) for _ in range(3)]
